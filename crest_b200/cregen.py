@@ -1,0 +1,231 @@
+"""Host-side mirror of the reference's CREGEN sorting interface, on top of the C ABI.
+
+    cregen_CRE(env, nat, nall, at, xyz, energies, nosort)  <->  src/cregen.f90:1125-1506
+    CregenContext                                           <->  device-resident path used by
+                                                                 bench.py / multi-GPU sharding
+
+`env` carries the same scalars the reference reads from type(systemdata)
+(src/classes.f90:332-345, 426, 557, 607, 547): ethr, rthr, bthr2, bthrmax, bthrshift, heavyrmsd,
+subRMSD + includeRMSD, entropic.  Indices returned are 1-based like the reference's arrays.
+Nothing here computes on the CPU: every number comes from libcrest_cuda.so.
+"""
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Optional
+
+import numpy as np
+
+from . import _lib
+from ._lib import Thresholds, CrestCudaError, c_dp, c_ip, c_fp, c_llp  # noqa: F401
+
+
+@dataclass
+class Env:
+    """The slice of type(systemdata) that crosses the boundary; defaults = confparse.f90:162-174."""
+    ethr: float = 0.05
+    rthr: float = 0.125
+    bthr2: float = 0.01
+    bthrmax: float = 0.025
+    bthrshift: float = 0.5
+    heavyrmsd: bool = False
+    subRMSD: bool = False
+    includeRMSD: Optional[np.ndarray] = None   # (nat,) >0 = atom used; with subRMSD
+    rednat: Optional[int] = None
+    entropic: bool = False
+
+    def thresholds(self):
+        return Thresholds(self.ethr, self.rthr, self.bthr2, self.bthrmax, self.bthrshift)
+
+
+def _dp(a):
+    return a.ctypes.data_as(c_dp) if a is not None else None
+
+
+def _ip(a):
+    return a.ctypes.data_as(c_ip) if a is not None else None
+
+
+def rmsd_mask(env: Env, nat: int, at: np.ndarray):
+    """(mask or None, rot_from_mask) as cregen_CRE derives them (cregen.f90:1199-1202,1293-1299)."""
+    rednat = env.rednat if env.rednat is not None else nat
+    substruc = (nat != rednat) and env.subRMSD
+    if substruc:
+        m = (np.asarray(env.includeRMSD) > 0).astype(np.int32)
+        return np.ascontiguousarray(m), 1
+    if env.heavyrmsd:
+        return np.ascontiguousarray((np.asarray(at) != 1).astype(np.int32)), 0
+    return None, 0
+
+
+@dataclass
+class CreResult:
+    nallout: int
+    group: np.ndarray          # (nall+1,), group[0] = number of groups
+    order: np.ndarray          # (nall,) new 1-based position of input structure i
+    rot: np.ndarray            # (nall,3) MHz, permuted
+    xyz: np.ndarray            # (nall,nat,3) principal-axis frame, permuted
+    er: np.ndarray             # permuted energies
+    npairs: int
+
+
+def cregen_CRE(env: Env, nat, nall, at, xyz, er, nosort=False) -> CreResult:
+    """Whole cregen_CRE (duplicates + rotamer groups) through crest_cuda_cregen_cre."""
+    L = _lib.lib()
+    at = np.ascontiguousarray(at, np.int32)
+    xyz = np.array(xyz, np.float64, order="C", copy=True).reshape(nall, nat, 3)
+    er = np.array(er, np.float64, copy=True)
+    mask, rfm = rmsd_mask(env, nat, at)
+    rot = np.zeros((max(nall, 1), 3))
+    order = np.zeros(max(nall, 1), np.int32)
+    group = np.zeros(nall + 1, np.int32)
+    nout = C.c_int(0)
+    npairs = C.c_longlong(0)
+    thr = env.thresholds()
+    _lib.check(L.crest_cuda_cregen_cre(nat, nall, _ip(at), _dp(xyz), _dp(er), _ip(mask), rfm,
+                                       0 if env.entropic else 1, 1 if nosort else 0, C.byref(thr),
+                                       _dp(rot), _ip(order), _ip(group), C.byref(nout),
+                                       C.byref(npairs)))
+    return CreResult(nout.value, group, order[:nall], rot[:nall], xyz, er, npairs.value)
+
+
+def cregen_dup(env: Env, nat, nall, at, xyz, er, want_xyz=True):
+    """Stage A only (K0-K4): returns dict(rot, xyz_axis, dup, npairs)."""
+    L = _lib.lib()
+    at = np.ascontiguousarray(at, np.int32)
+    xyz = np.ascontiguousarray(xyz, np.float64).reshape(nall, nat, 3)
+    er = np.ascontiguousarray(er, np.float64)
+    mask, rfm = rmsd_mask(env, nat, at)
+    rot = np.zeros((max(nall, 1), 3))
+    xa = np.zeros_like(xyz) if want_xyz else None
+    dup = np.zeros(max(nall, 1), np.int32)
+    npairs = C.c_longlong(0)
+    thr = env.thresholds()
+    _lib.check(L.crest_cuda_cregen_dup(nat, nall, _ip(at), _dp(xyz), _dp(er), _ip(mask), rfm,
+                                       0 if env.entropic else 1, C.byref(thr), _dp(rot), _dp(xa),
+                                       _ip(dup), C.byref(npairs)))
+    return dict(rot=rot[:nall], xyz_axis=xa, dup=dup[:nall], npairs=npairs.value)
+
+
+def cregen_group(env: Env, nat, nkept, at, xyz, er, rot):
+    L = _lib.lib()
+    at = np.ascontiguousarray(at, np.int32)
+    xyz = np.ascontiguousarray(xyz, np.float64)
+    er = np.ascontiguousarray(er, np.float64)
+    rot = np.ascontiguousarray(rot, np.float64)
+    group = np.zeros(nkept + 1, np.int32)
+    enuc = np.zeros(max(nkept, 1))
+    thr = env.thresholds()
+    _lib.check(L.crest_cuda_cregen_group(nat, nkept, _ip(at), _dp(xyz), _dp(er), _dp(rot),
+                                         C.byref(thr), _ip(group), _dp(enuc)))
+    return group, enuc[:nkept]
+
+
+def rmsd_pairs(packed, i_idx, j_idx):
+    """packed (n,A,3); returns (rmsd, rmsd_mirror) for the listed 0-based pairs."""
+    L = _lib.lib()
+    packed = np.ascontiguousarray(packed, np.float64)
+    n, A, _ = packed.shape
+    i_idx = np.ascontiguousarray(i_idx, np.int32)
+    j_idx = np.ascontiguousarray(j_idx, np.int32)
+    r = np.zeros(len(i_idx))
+    rm = np.zeros(len(i_idx))
+    _lib.check(L.crest_cuda_rmsd_pairs(A, n, _dp(packed), len(i_idx), _ip(i_idx), _ip(j_idx),
+                                       _dp(r), _dp(rm)))
+    return r, rm
+
+
+def rotconst(at, xyz):
+    L = _lib.lib()
+    at = np.ascontiguousarray(at, np.int32)
+    xyz = np.ascontiguousarray(xyz, np.float64)
+    n, nat, _ = xyz.shape
+    rot = np.zeros((n, 3))
+    _lib.check(L.crest_cuda_rotconst(nat, n, _ip(at), _dp(xyz), _dp(rot)))
+    return rot
+
+
+def rmat_allpairs(env: Env, at, xyz):
+    """float32 band as the reference's rmat with ethr=inf: row i at offset i*(i-1)/2."""
+    L = _lib.lib()
+    at = np.ascontiguousarray(at, np.int32)
+    xyz = np.ascontiguousarray(xyz, np.float64)
+    n, nat, _ = xyz.shape
+    mask, _ = rmsd_mask(env, nat, at)
+    rmat = np.zeros(max(n * (n - 1) // 2, 1), np.float32)
+    _lib.check(L.crest_cuda_rmat_allpairs(nat, n, _ip(at), _dp(xyz), _ip(mask),
+                                          0 if env.entropic else 1, rmat.ctypes.data_as(c_fp)))
+    return rmat[: n * (n - 1) // 2]
+
+
+class CregenContext:
+    """Device-resident ensemble; stages are launched on a caller-supplied CUDA stream so that
+    bench.py can time them with events and shard the tile space over ranks."""
+
+    def __init__(self, device=-1):
+        self._L = _lib.lib()
+        self._h = C.c_void_p()
+        _lib.check(self._L.crest_cuda_ctx_create(C.byref(self._h), device))
+        self.nall = 0
+        self.nat = 0
+
+    def close(self):
+        if self._h:
+            self._L.crest_cuda_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, env: Env, at, xyz, er):
+        at = np.ascontiguousarray(at, np.int32)
+        xyz = np.ascontiguousarray(xyz, np.float64)
+        er = np.ascontiguousarray(er, np.float64)
+        nall, nat, _ = xyz.shape
+        mask, rfm = rmsd_mask(env, nat, at)
+        _lib.check(self._L.crest_cuda_ctx_upload(self._h, nat, nall, _ip(at), _dp(xyz), _dp(er),
+                                                 _ip(mask), rfm))
+        self.nall, self.nat = nall, nat
+
+    def pack(self, stream=0):
+        _lib.check(self._L.crest_cuda_ctx_pack(self._h, C.c_void_p(stream)))
+
+    def pairs(self, env: Env, rank=0, nranks=1, want_mask=False, stream=0):
+        thr = env.thresholds()
+        _lib.check(self._L.crest_cuda_ctx_pairs(self._h, 0 if env.entropic else 1, C.byref(thr),
+                                                rank, nranks, 1 if want_mask else 0,
+                                                C.c_void_p(stream)))
+
+    def sweep(self, stream=0):
+        _lib.check(self._L.crest_cuda_ctx_sweep(self._h, C.c_void_p(stream)))
+
+    def dup_devptr(self):
+        return self._L.crest_cuda_ctx_dup_devptr(self._h)
+
+    def npairs_devptr(self):
+        return self._L.crest_cuda_ctx_npairs_devptr(self._h)
+
+    def info(self, env: Env, rank=0, nranks=1):
+        thr = env.thresholds()
+        buf = (C.c_longlong * 8)()
+        _lib.check(self._L.crest_cuda_ctx_info(self._h, C.byref(thr), rank, nranks, buf))
+        keys = ["tiles_shard", "tiles_total", "A", "A_padded", "grid", "smem", "launches"]
+        return dict(zip(keys, list(buf)[:7]))
+
+    def download(self, want_xyz=False, stream=0):
+        rot = np.zeros((max(self.nall, 1), 3))
+        dup = np.zeros(max(self.nall, 1), np.int32)
+        xa = np.zeros((self.nall, self.nat, 3)) if want_xyz else None
+        npairs = C.c_longlong(0)
+        _lib.check(self._L.crest_cuda_ctx_download(self._h, _dp(rot), _dp(xa), _ip(dup),
+                                                   C.byref(npairs), C.c_void_p(stream)))
+        return dict(rot=rot[: self.nall], dup=dup[: self.nall], xyz_axis=xa, npairs=npairs.value)
+
+    def download_mask(self, stream=0):
+        n8 = (self.nall + 7) // 8
+        m = np.zeros((n8, n8), np.uint64)
+        _lib.check(self._L.crest_cuda_ctx_download_mask(
+            self._h, m.ctypes.data_as(_lib.c_ullp), C.c_void_p(stream)))
+        return m

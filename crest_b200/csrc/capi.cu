@@ -1,0 +1,558 @@
+// C ABI of the CREGEN CUDA path (include/crest_cuda.h): argument checks, context, host<->device
+// copies, the host-side band/tile bookkeeping (reference src/cregen.f90:1240-1256) and the exact
+// float32-threshold emulation (cregen.f90:1286,1359-1367).  No CPU fallback lives here: every
+// compute entry point needs a CUDA device and fails otherwise.
+#include "../../include/crest_cuda.h"
+#include "common.cuh"
+#include <cmath>
+#include <cstdarg>
+#include <cstring>
+#include <limits>
+#include <vector>
+
+namespace crest {
+
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+// Smallest e such that NOT ( real( sqrt(max(0,e)/n), sp ) < thr ).  All operations involved are
+// monotone non-decreasing in e, so `e < E` reproduces the reference's comparison of the
+// float32-rounded RMSD (rmat is real(sp), cregen.f90:1176,1286) with the double threshold bit
+// for bit, without a sqrt or a division per pair.
+static double e_threshold(double thr, int n) {
+  if (!(thr > 0.0)) return -std::numeric_limits<double>::infinity();
+  auto below = [&](double e) {
+    const double r = std::sqrt(std::max(0.0, e) / (double)n);
+    return (double)(float)r < thr;
+  };
+  uint64_t lo = 0, hi;                       // bit patterns of non-negative doubles are ordered
+  double big = std::numeric_limits<double>::max();
+  if (below(big)) return std::numeric_limits<double>::infinity();
+  std::memcpy(&hi, &big, 8);
+  // invariant: below(lo) true, below(hi) false
+  while (hi - lo > 1) {
+    const uint64_t mid = lo + (hi - lo) / 2;
+    double m;
+    std::memcpy(&m, &mid, 8);
+    if (below(m)) lo = mid; else hi = mid;
+  }
+  double E;
+  std::memcpy(&E, &hi, 8);
+  return E;
+}
+
+static Gates make_gates(const crest_cuda_thresholds& t, int enantio, int A) {
+  Gates g;
+  g.ethr = t.ethr;
+  g.E1 = e_threshold(t.rthr, A);
+  g.E2 = e_threshold(2.0 * t.rthr, A);
+  g.bthr_half = 0.5 * t.bthr;
+  g.bthrmax = t.bthrmax;
+  g.bthrshift = t.bthrshift;
+  g.enantio = enantio ? 1 : 0;
+  return g;
+}
+
+}  // namespace crest
+
+using namespace crest;
+
+struct crest_cuda_ctx {
+  int device = 0;
+  int nat = 0, nall = 0, nsel = 0, rot_from_mask = 0;
+  PackLayout L{};
+  std::vector<double> h_er;
+  // device buffers
+  int* d_at = nullptr;
+  int* d_sel = nullptr;
+  double* d_xyz = nullptr;
+  double* d_xyz_axis = nullptr;
+  double* d_er = nullptr;
+  double* d_rot = nullptr;
+  double* d_aniso = nullptr;
+  double* d_X = nullptr;
+  double* d_xn = nullptr;
+  int* d_dup = nullptr;
+  unsigned long long* d_npairs = nullptr;
+  long long* d_rowstart = nullptr;
+  int* d_jfirst = nullptr;
+  unsigned long long* d_mask = nullptr;
+  float* d_rmat = nullptr;
+  size_t cap_xyz = 0, cap_conf = 0, cap_X = 0, cap_at = 0, cap_rows = 0, cap_mask = 0;
+  // tile list (host)
+  std::vector<long long> rowstart;
+  std::vector<int> jfirst;
+  double tiles_ethr = std::numeric_limits<double>::quiet_NaN();
+  long long launches = 0;
+  int last_grid = 0, last_smem = 0;
+};
+
+namespace {
+
+// In-band tile list: for i-panel I the j-tiles [jfirst, jlast]; energies ascend, so the first
+// in-band j of the panel's first row bounds the whole panel (cregen.f90:1245-1255 rmap2).
+void build_tiles(crest_cuda_ctx* c, double ethr) {
+  const int n = c->nall;
+  const int nI = (n + kTileI - 1) / kTileI;
+  c->rowstart.assign(nI + 1, 0);
+  c->jfirst.assign(nI > 0 ? nI : 1, 0);
+  const double* er = c->h_er.data();
+  long long acc = 0;
+  for (int I = 0; I < nI; ++I) {
+    c->rowstart[I] = acc;
+    const int ifirst = I * kTileI;
+    const int ilast = std::min(ifirst + kTileI - 1, n - 1);
+    const int jmax = ilast - 1;
+    // first j in [0, ifirst] with (er[ifirst]-er[j])*autokcal < ethr ; predicate is monotone in j
+    int lo = 0, hi = ifirst;   // answer in [0, ifirst]
+    while (lo < hi) {
+      const int mid = (lo + hi) / 2;
+      const double de = (er[ifirst] - er[mid]) * kAutokcal;
+      if (de < ethr) hi = mid; else lo = mid + 1;
+    }
+    const int jlo = lo;
+    if (jmax >= 0 && jlo <= jmax) {
+      c->jfirst[I] = jlo / kTileJ;
+      acc += (long long)(jmax / kTileJ - c->jfirst[I] + 1);
+    } else {
+      c->jfirst[I] = 0;
+    }
+  }
+  c->rowstart[nI] = acc;
+  c->tiles_ethr = ethr;
+}
+
+int upload_tiles(crest_cuda_ctx* c, cudaStream_t st) {
+  const size_t nI = c->jfirst.size();
+  if (nI + 1 > c->cap_rows) {
+    if (c->d_rowstart) cudaFree(c->d_rowstart);
+    if (c->d_jfirst) cudaFree(c->d_jfirst);
+    c->d_rowstart = nullptr; c->d_jfirst = nullptr;
+    CREST_CUDA_TRY(cudaMalloc(&c->d_rowstart, sizeof(long long) * (nI + 1)));
+    CREST_CUDA_TRY(cudaMalloc(&c->d_jfirst, sizeof(int) * nI));
+    c->cap_rows = nI + 1;
+  }
+  CREST_CUDA_TRY(cudaMemcpyAsync(c->d_rowstart, c->rowstart.data(),
+                                 sizeof(long long) * c->rowstart.size(), cudaMemcpyHostToDevice, st));
+  CREST_CUDA_TRY(cudaMemcpyAsync(c->d_jfirst, c->jfirst.data(), sizeof(int) * nI,
+                                 cudaMemcpyHostToDevice, st));
+  return 0;
+}
+
+int check_thr(const crest_cuda_thresholds* t) {
+  if (!t) { set_error("thresholds pointer is NULL"); return 1; }
+  if (!(t->rthr == t->rthr) || !(t->ethr == t->ethr)) { set_error("NaN threshold"); return 1; }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* crest_cuda_last_error(void) { return g_err; }
+
+int crest_cuda_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int crest_cuda_ctx_create(crest_cuda_ctx** out, int device) {
+  if (!out) { set_error("ctx out pointer is NULL"); return 1; }
+  *out = nullptr;
+  int ndev = 0;
+  CREST_CUDA_TRY(cudaGetDeviceCount(&ndev));
+  if (ndev <= 0) { set_error("no CUDA device available (there is no CPU fallback)"); return 1; }
+  if (device < 0) CREST_CUDA_TRY(cudaGetDevice(&device));
+  if (device >= ndev) { set_error("device %d out of range (%d devices)", device, ndev); return 1; }
+  CREST_CUDA_TRY(cudaSetDevice(device));
+  crest_cuda_ctx* c = new crest_cuda_ctx();
+  c->device = device;
+  if (cudaMalloc(&c->d_npairs, sizeof(unsigned long long)) != cudaSuccess) {
+    set_error("cudaMalloc failed: %s", cudaGetErrorString(cudaGetLastError()));
+    delete c;
+    return 1;
+  }
+  *out = c;
+  return 0;
+}
+
+void crest_cuda_ctx_destroy(crest_cuda_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaFree(c->d_at); cudaFree(c->d_sel); cudaFree(c->d_xyz); cudaFree(c->d_xyz_axis);
+  cudaFree(c->d_er); cudaFree(c->d_rot); cudaFree(c->d_aniso); cudaFree(c->d_X); cudaFree(c->d_xn);
+  cudaFree(c->d_dup); cudaFree(c->d_npairs); cudaFree(c->d_rowstart); cudaFree(c->d_jfirst);
+  cudaFree(c->d_mask); cudaFree(c->d_rmat);
+  delete c;
+}
+
+int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, const double* xyz,
+                          const double* er, const int* rmsd_mask, int rot_from_mask) {
+  if (!c) { set_error("ctx is NULL"); return 1; }
+  if (nat <= 0 || nall < 0) { set_error("bad sizes nat=%d nall=%d", nat, nall); return 1; }
+  if (!at || (!xyz && nall > 0) || (!er && nall > 0)) { set_error("NULL input array"); return 1; }
+  for (int i = 1; i < nall; ++i)
+    if (er[i] < er[i - 1]) {
+      set_error("energies must ascend (cregen_esort post-condition): er[%d] < er[%d]", i, i - 1);
+      return 1;
+    }
+  CREST_CUDA_TRY(cudaSetDevice(c->device));
+  std::vector<int> sel;
+  sel.reserve(nat);
+  for (int k = 0; k < nat; ++k)
+    if (!rmsd_mask || rmsd_mask[k] > 0) sel.push_back(k);
+  if (sel.empty()) { set_error("RMSD atom mask selects no atom"); return 1; }
+  c->nat = nat; c->nall = nall; c->nsel = (int)sel.size(); c->rot_from_mask = rot_from_mask ? 1 : 0;
+  c->L = make_layout(c->nsel, nall);
+  c->h_er.assign(er, er + nall);
+  c->tiles_ethr = std::numeric_limits<double>::quiet_NaN();
+
+  const size_t nxyz = (size_t)3 * nat * nall;
+  if ((size_t)nat > c->cap_at) {
+    cudaFree(c->d_at); cudaFree(c->d_sel);
+    c->d_at = nullptr; c->d_sel = nullptr; c->cap_at = 0;
+    CREST_CUDA_TRY(cudaMalloc(&c->d_at, sizeof(int) * nat));
+    CREST_CUDA_TRY(cudaMalloc(&c->d_sel, sizeof(int) * nat));
+    c->cap_at = nat;
+  }
+  if (nxyz > c->cap_xyz) {
+    cudaFree(c->d_xyz); cudaFree(c->d_xyz_axis);
+    c->d_xyz = nullptr; c->d_xyz_axis = nullptr; c->cap_xyz = 0;
+    CREST_CUDA_TRY(cudaMalloc(&c->d_xyz, sizeof(double) * (nxyz ? nxyz : 1)));
+    CREST_CUDA_TRY(cudaMalloc(&c->d_xyz_axis, sizeof(double) * (nxyz ? nxyz : 1)));
+    c->cap_xyz = nxyz;
+  }
+  if ((size_t)nall > c->cap_conf) {
+    cudaFree(c->d_er); cudaFree(c->d_rot); cudaFree(c->d_aniso); cudaFree(c->d_xn); cudaFree(c->d_dup);
+    c->d_er = c->d_rot = c->d_aniso = c->d_xn = nullptr; c->d_dup = nullptr; c->cap_conf = 0;
+    const size_t m = nall ? nall : 1;
+    CREST_CUDA_TRY(cudaMalloc(&c->d_er, sizeof(double) * m));
+    CREST_CUDA_TRY(cudaMalloc(&c->d_rot, sizeof(double) * 3 * m));
+    CREST_CUDA_TRY(cudaMalloc(&c->d_aniso, sizeof(double) * m));
+    CREST_CUDA_TRY(cudaMalloc(&c->d_xn, sizeof(double) * m));
+    CREST_CUDA_TRY(cudaMalloc(&c->d_dup, sizeof(int) * m));
+    c->cap_conf = nall;
+  }
+  const size_t nX = c->L.total_doubles();
+  if (nX > c->cap_X) {
+    cudaFree(c->d_X); c->d_X = nullptr; c->cap_X = 0;
+    CREST_CUDA_TRY(cudaMalloc(&c->d_X, sizeof(double) * nX));
+    c->cap_X = nX;
+  }
+  CREST_CUDA_TRY(cudaMemcpy(c->d_at, at, sizeof(int) * nat, cudaMemcpyHostToDevice));
+  CREST_CUDA_TRY(cudaMemcpy(c->d_sel, sel.data(), sizeof(int) * sel.size(), cudaMemcpyHostToDevice));
+  if (nall > 0) {
+    CREST_CUDA_TRY(cudaMemcpy(c->d_xyz, xyz, sizeof(double) * nxyz, cudaMemcpyHostToDevice));
+    CREST_CUDA_TRY(cudaMemcpy(c->d_er, er, sizeof(double) * nall, cudaMemcpyHostToDevice));
+  }
+  return 0;
+}
+
+int crest_cuda_ctx_pack(crest_cuda_ctx* c, void* stream) {
+  if (!c) { set_error("ctx is NULL"); return 1; }
+  cudaStream_t st = (cudaStream_t)stream;
+  CREST_CUDA_TRY(cudaSetDevice(c->device));
+  // padding rows / atoms of X must be zero: they enter the MMA (atoms) or are masked (rows)
+  CREST_CUDA_TRY(cudaMemsetAsync(c->d_X, 0, sizeof(double) * c->L.total_doubles(), st));
+  CREST_CUDA_TRY(cudaMemsetAsync(c->d_dup, 0, sizeof(int) * (size_t)(c->nall ? c->nall : 1), st));
+  CREST_CUDA_TRY(cudaMemsetAsync(c->d_npairs, 0, sizeof(unsigned long long), st));
+  c->launches = 0;
+  if (launch_pack_axis(c->nat, c->nall, c->d_at, c->d_xyz, c->d_sel, c->nsel, c->rot_from_mask,
+                       c->L, c->d_xyz_axis, c->d_rot, c->d_aniso, c->d_X, c->d_xn, st))
+    return 1;
+  if (c->nall > 0) c->launches += 1;
+  return 0;
+}
+
+static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_thresholds* thr, int rank,
+                      int nranks, int want_mask, float* d_rmat, cudaStream_t st) {
+  if (check_thr(thr)) return 1;
+  if (nranks < 1 || rank < 0 || rank >= nranks) { set_error("bad shard %d/%d", rank, nranks); return 1; }
+  CREST_CUDA_TRY(cudaSetDevice(c->device));
+  if (c->nall < 2) return 0;
+  if (!(c->tiles_ethr == thr->ethr)) {
+    build_tiles(c, thr->ethr);
+    if (upload_tiles(c, st)) return 1;
+  }
+  const long long T = c->rowstart.back();
+  PairArgs a{};
+  a.X = c->d_X; a.xn = c->d_xn; a.er = c->d_er; a.rot = c->d_rot; a.aniso = c->d_aniso;
+  a.rowstart = c->d_rowstart; a.jfirst = c->d_jfirst;
+  a.nI = (int)c->jfirst.size(); a.nall = c->nall;
+  a.tile_begin = T * rank / nranks;
+  a.tile_end = T * (rank + 1) / nranks;
+  a.dup = c->d_dup; a.npairs = c->d_npairs;
+  a.mask = nullptr; a.n8 = (c->nall + 7) / 8;
+  if (want_mask) {
+    const size_t need = (size_t)a.n8 * a.n8;
+    if (need > c->cap_mask) {
+      cudaFree(c->d_mask); c->d_mask = nullptr; c->cap_mask = 0;
+      CREST_CUDA_TRY(cudaMalloc(&c->d_mask, sizeof(unsigned long long) * need));
+      c->cap_mask = need;
+    }
+    CREST_CUDA_TRY(cudaMemsetAsync(c->d_mask, 0, sizeof(unsigned long long) * need, st));
+    a.mask = c->d_mask;
+  }
+  a.rmat = d_rmat;
+  a.g = make_gates(*thr, enantio, c->nsel);
+  a.L = c->L;
+  int ns = 0;
+  pair_smem_bytes(c->L, &ns);
+  if (launch_pair_tiles(a, ns, st, &c->last_grid, &c->last_smem)) return 1;
+  if (c->last_grid > 0) c->launches += 1;
+  return 0;
+}
+
+int crest_cuda_ctx_pairs(crest_cuda_ctx* c, int enantio, const crest_cuda_thresholds* thr,
+                         int rank, int nranks, int want_mask, void* stream) {
+  if (!c) { set_error("ctx is NULL"); return 1; }
+  return pairs_impl(c, enantio, thr, rank, nranks, want_mask, nullptr, (cudaStream_t)stream);
+}
+
+void* crest_cuda_ctx_dup_devptr(crest_cuda_ctx* c) { return c ? (void*)c->d_dup : nullptr; }
+void* crest_cuda_ctx_npairs_devptr(crest_cuda_ctx* c) { return c ? (void*)c->d_npairs : nullptr; }
+
+int crest_cuda_ctx_sweep(crest_cuda_ctx* c, void* stream) {
+  if (!c) { set_error("ctx is NULL"); return 1; }
+  CREST_CUDA_TRY(cudaSetDevice(c->device));
+  if (launch_backtrack(c->nall, c->d_dup, (cudaStream_t)stream)) return 1;
+  if (c->nall > 0) c->launches += 1;
+  return 0;
+}
+
+int crest_cuda_ctx_download(crest_cuda_ctx* c, double* rot, double* xyz_axis, int* dup,
+                            long long* npairs, void* stream) {
+  if (!c) { set_error("ctx is NULL"); return 1; }
+  cudaStream_t st = (cudaStream_t)stream;
+  CREST_CUDA_TRY(cudaSetDevice(c->device));
+  const size_t n = c->nall;
+  if (rot && n)
+    CREST_CUDA_TRY(cudaMemcpyAsync(rot, c->d_rot, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost, st));
+  if (xyz_axis && n)
+    CREST_CUDA_TRY(cudaMemcpyAsync(xyz_axis, c->d_xyz_axis, sizeof(double) * 3 * c->nat * n,
+                                   cudaMemcpyDeviceToHost, st));
+  if (dup && n)
+    CREST_CUDA_TRY(cudaMemcpyAsync(dup, c->d_dup, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+  if (npairs)
+    CREST_CUDA_TRY(cudaMemcpyAsync(npairs, c->d_npairs, sizeof(long long), cudaMemcpyDeviceToHost, st));
+  CREST_CUDA_TRY(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int crest_cuda_ctx_info(crest_cuda_ctx* c, const crest_cuda_thresholds* thr, int rank, int nranks,
+                        long long* info) {
+  if (!c || !info) { set_error("NULL argument"); return 1; }
+  if (check_thr(thr)) return 1;
+  if (nranks < 1 || rank < 0 || rank >= nranks) { set_error("bad shard %d/%d", rank, nranks); return 1; }
+  if (c->nall >= 2 && !(c->tiles_ethr == thr->ethr)) {
+    build_tiles(c, thr->ethr);
+    CREST_CUDA_TRY(cudaSetDevice(c->device));
+    if (upload_tiles(c, 0)) return 1;
+    CREST_CUDA_TRY(cudaStreamSynchronize(0));
+  }
+  const long long T = c->rowstart.empty() ? 0 : c->rowstart.back();
+  info[0] = T * (rank + 1) / nranks - T * rank / nranks;
+  info[1] = T;
+  info[2] = c->nsel;
+  info[3] = (long long)c->L.nslab * c->L.KU;
+  info[4] = c->last_grid;
+  info[5] = c->last_smem;
+  info[6] = c->launches;
+  return 0;
+}
+
+// Copy of the device bitmask (tests): mask[n8*n8] 64-bit words, bit r*8+col of word (ti,tj).
+int crest_cuda_ctx_download_mask(crest_cuda_ctx* c, unsigned long long* mask, void* stream) {
+  if (!c || !c->d_mask || !mask) { set_error("no bitmask was requested"); return 1; }
+  const size_t n8 = (c->nall + 7) / 8;
+  CREST_CUDA_TRY(cudaMemcpyAsync(mask, c->d_mask, sizeof(unsigned long long) * n8 * n8,
+                                 cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  CREST_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// One-call entry points on a process-global context (device buffers are reused across the
+// 5-20 CREGEN calls of one conformer search).
+// ------------------------------------------------------------------------------------------
+static crest_cuda_ctx* g_ctx = nullptr;
+static int global_ctx(crest_cuda_ctx** out) {
+  if (!g_ctx && crest_cuda_ctx_create(&g_ctx, -1)) return 1;
+  *out = g_ctx;
+  return 0;
+}
+
+int crest_cuda_cregen_dup(int nat, int nall, const int* at, const double* xyz, const double* er,
+                          const int* rmsd_mask, int rot_from_mask, int enantio,
+                          const crest_cuda_thresholds* thr, double* rot, double* xyz_axis,
+                          int* dup, long long* npairs) {
+  crest_cuda_ctx* c;
+  if (check_thr(thr)) return 1;
+  if (global_ctx(&c)) return 1;
+  if (crest_cuda_ctx_upload(c, nat, nall, at, xyz, er, rmsd_mask, rot_from_mask)) return 1;
+  if (crest_cuda_ctx_pack(c, nullptr)) return 1;
+  if (crest_cuda_ctx_pairs(c, enantio, thr, 0, 1, 0, nullptr)) return 1;
+  if (crest_cuda_ctx_sweep(c, nullptr)) return 1;
+  return crest_cuda_ctx_download(c, rot, xyz_axis, dup, npairs, nullptr);
+}
+
+int crest_cuda_cregen_group(int nat, int nkept, const int* at, const double* xyz,
+                            const double* er, const double* rot,
+                            const crest_cuda_thresholds* thr, int* group, double* enuc) {
+  if (check_thr(thr)) return 1;
+  if (nat <= 0 || nkept < 0 || !at || !group) { set_error("bad argument"); return 1; }
+  crest_cuda_ctx* c;
+  if (global_ctx(&c)) return 1;
+  CREST_CUDA_TRY(cudaSetDevice(c->device));
+  if (nkept == 0) { group[0] = 0; return 0; }
+  if (!xyz || !er || !rot) { set_error("NULL input array"); return 1; }
+  int* d_at = nullptr; double *d_xyz = nullptr, *d_er = nullptr, *d_rot = nullptr, *d_enuc = nullptr;
+  int* d_group = nullptr;
+  const size_t n = nkept;
+  int rc = 1;
+  do {
+    if (cudaMalloc(&d_at, sizeof(int) * nat) != cudaSuccess) break;
+    if (cudaMalloc(&d_xyz, sizeof(double) * 3 * nat * n) != cudaSuccess) break;
+    if (cudaMalloc(&d_er, sizeof(double) * n) != cudaSuccess) break;
+    if (cudaMalloc(&d_rot, sizeof(double) * 3 * n) != cudaSuccess) break;
+    if (cudaMalloc(&d_enuc, sizeof(double) * n) != cudaSuccess) break;
+    if (cudaMalloc(&d_group, sizeof(int) * (n + 1)) != cudaSuccess) break;
+    if (cudaMemcpy(d_at, at, sizeof(int) * nat, cudaMemcpyHostToDevice) != cudaSuccess) break;
+    if (cudaMemcpy(d_xyz, xyz, sizeof(double) * 3 * nat * n, cudaMemcpyHostToDevice) != cudaSuccess) break;
+    if (cudaMemcpy(d_er, er, sizeof(double) * n, cudaMemcpyHostToDevice) != cudaSuccess) break;
+    if (cudaMemcpy(d_rot, rot, sizeof(double) * 3 * n, cudaMemcpyHostToDevice) != cudaSuccess) break;
+    if (launch_enuc(nat, nkept, d_at, d_xyz, d_enuc, 0)) { rc = 2; break; }
+    if (launch_group(nkept, d_er, d_rot, d_enuc, thr->ethr, thr->bthr, thr->bthrmax,
+                     thr->bthrshift, d_group, 0)) { rc = 2; break; }
+    if (cudaMemcpy(group, d_group, sizeof(int) * (n + 1), cudaMemcpyDeviceToHost) != cudaSuccess) break;
+    if (enuc && cudaMemcpy(enuc, d_enuc, sizeof(double) * n, cudaMemcpyDeviceToHost) != cudaSuccess) break;
+    rc = 0;
+  } while (0);
+  if (rc == 1) set_error("CUDA error in cregen_group: %s", cudaGetErrorString(cudaGetLastError()));
+  cudaFree(d_at); cudaFree(d_xyz); cudaFree(d_er); cudaFree(d_rot); cudaFree(d_enuc); cudaFree(d_group);
+  return rc;
+}
+
+int crest_cuda_cregen_cre(int nat, int nall, const int* at, double* xyz, double* er,
+                          const int* rmsd_mask, int rot_from_mask, int enantio, int nosort,
+                          const crest_cuda_thresholds* thr, double* rot, int* order, int* group,
+                          int* nallout, long long* npairs) {
+  if (!rot || !order || !group || !nallout) { set_error("NULL output array"); return 1; }
+  std::vector<int> dup((size_t)(nall > 0 ? nall : 1));
+  std::vector<double> xa((size_t)3 * nat * (nall > 0 ? nall : 1));
+  if (crest_cuda_cregen_dup(nat, nall, at, xyz, er, rmsd_mask, rot_from_mask, enantio, thr, rot,
+                            xa.data(), dup.data(), npairs))
+    return 1;
+  // kept-first partition, duplicates appended in reverse encounter order (cregen.f90:1397-1419)
+  int ndup = 0;
+  for (int i = 0; i < nall; ++i) ndup += dup[i] != 0;
+  int nout = nall - ndup;
+  if (nosort) {
+    nout = nall;
+    for (int i = 0; i < nall; ++i) order[i] = i + 1;
+    std::memcpy(xyz, xa.data(), sizeof(double) * 3 * nat * (size_t)nall);
+  } else {
+    int j = 0, l = nall + 1;
+    for (int i = 0; i < nall; ++i) order[i] = (dup[i] == 0) ? ++j : --l;
+    std::vector<double> e2(nall), r2((size_t)3 * nall);
+    const size_t rec = (size_t)3 * nat;
+    for (int i = 0; i < nall; ++i) {
+      const size_t d = (size_t)order[i] - 1;
+      std::memcpy(xyz + d * rec, xa.data() + (size_t)i * rec, rec * sizeof(double));
+      e2[d] = er[i];
+      r2[3 * d] = rot[3 * i]; r2[3 * d + 1] = rot[3 * i + 1]; r2[3 * d + 2] = rot[3 * i + 2];
+    }
+    std::memcpy(er, e2.data(), sizeof(double) * nall);
+    std::memcpy(rot, r2.data(), sizeof(double) * 3 * nall);
+  }
+  for (int i = 0; i <= nall; ++i) group[i] = 0;
+  if (crest_cuda_cregen_group(nat, nout, at, xyz, er, rot, thr, group, nullptr)) return 1;
+  if (nosort) nout = group[0];
+  *nallout = nout;
+  return 0;
+}
+
+int crest_cuda_rotconst(int nat, int n, const int* at, const double* xyz, double* rot) {
+  if (nat <= 0 || n < 0 || !at || !rot || (!xyz && n)) { set_error("bad argument"); return 1; }
+  crest_cuda_ctx* c;
+  if (global_ctx(&c)) return 1;
+  CREST_CUDA_TRY(cudaSetDevice(c->device));
+  if (n == 0) return 0;
+  int* d_at = nullptr; double *d_xyz = nullptr, *d_rot = nullptr;
+  CREST_CUDA_TRY(cudaMalloc(&d_at, sizeof(int) * nat));
+  CREST_CUDA_TRY(cudaMalloc(&d_xyz, sizeof(double) * 3 * nat * (size_t)n));
+  CREST_CUDA_TRY(cudaMalloc(&d_rot, sizeof(double) * 3 * (size_t)n));
+  CREST_CUDA_TRY(cudaMemcpy(d_at, at, sizeof(int) * nat, cudaMemcpyHostToDevice));
+  CREST_CUDA_TRY(cudaMemcpy(d_xyz, xyz, sizeof(double) * 3 * nat * (size_t)n, cudaMemcpyHostToDevice));
+  int rc = launch_rotconst(nat, n, d_at, d_xyz, d_rot, 0);
+  if (!rc && cudaMemcpy(rot, d_rot, sizeof(double) * 3 * (size_t)n, cudaMemcpyDeviceToHost) != cudaSuccess) {
+    set_error("D2H failed: %s", cudaGetErrorString(cudaGetLastError()));
+    rc = 1;
+  }
+  cudaFree(d_at); cudaFree(d_xyz); cudaFree(d_rot);
+  return rc;
+}
+
+int crest_cuda_rmsd_pairs(int A, int n, const double* packed, long long npairs, const int* i_idx,
+                          const int* j_idx, double* rmsd, double* rmsd_mirror) {
+  if (A <= 0 || n <= 0 || npairs < 0 || !packed || !rmsd || !rmsd_mirror) {
+    set_error("bad argument"); return 1;
+  }
+  crest_cuda_ctx* c;
+  if (global_ctx(&c)) return 1;
+  CREST_CUDA_TRY(cudaSetDevice(c->device));
+  if (npairs == 0) return 0;
+  for (long long p = 0; p < npairs; ++p)
+    if (i_idx[p] < 0 || i_idx[p] >= n || j_idx[p] < 0 || j_idx[p] >= n) {
+      set_error("pair %lld index out of range", p); return 1;
+    }
+  double *d_p = nullptr, *d_r = nullptr, *d_m = nullptr; int *d_i = nullptr, *d_j = nullptr;
+  CREST_CUDA_TRY(cudaMalloc(&d_p, sizeof(double) * 3 * A * (size_t)n));
+  CREST_CUDA_TRY(cudaMalloc(&d_r, sizeof(double) * npairs));
+  CREST_CUDA_TRY(cudaMalloc(&d_m, sizeof(double) * npairs));
+  CREST_CUDA_TRY(cudaMalloc(&d_i, sizeof(int) * npairs));
+  CREST_CUDA_TRY(cudaMalloc(&d_j, sizeof(int) * npairs));
+  CREST_CUDA_TRY(cudaMemcpy(d_p, packed, sizeof(double) * 3 * A * (size_t)n, cudaMemcpyHostToDevice));
+  CREST_CUDA_TRY(cudaMemcpy(d_i, i_idx, sizeof(int) * npairs, cudaMemcpyHostToDevice));
+  CREST_CUDA_TRY(cudaMemcpy(d_j, j_idx, sizeof(int) * npairs, cudaMemcpyHostToDevice));
+  int rc = launch_rmsd_pairs(A, n, d_p, npairs, d_i, d_j, d_r, d_m, 0);
+  if (!rc) {
+    if (cudaMemcpy(rmsd, d_r, sizeof(double) * npairs, cudaMemcpyDeviceToHost) != cudaSuccess ||
+        cudaMemcpy(rmsd_mirror, d_m, sizeof(double) * npairs, cudaMemcpyDeviceToHost) != cudaSuccess) {
+      set_error("D2H failed: %s", cudaGetErrorString(cudaGetLastError()));
+      rc = 1;
+    }
+  }
+  cudaFree(d_p); cudaFree(d_r); cudaFree(d_m); cudaFree(d_i); cudaFree(d_j);
+  return rc;
+}
+
+int crest_cuda_rmat_allpairs(int nat, int nall, const int* at, const double* xyz,
+                             const int* rmsd_mask, int enantio, float* rmat) {
+  if (!rmat) { set_error("rmat is NULL"); return 1; }
+  crest_cuda_ctx* c;
+  if (global_ctx(&c)) return 1;
+  std::vector<double> er((size_t)(nall > 0 ? nall : 1), 0.0);
+  if (crest_cuda_ctx_upload(c, nat, nall, at, xyz, er.data(), rmsd_mask, 0)) return 1;
+  if (crest_cuda_ctx_pack(c, nullptr)) return 1;
+  const size_t np = (size_t)nall * (nall > 0 ? nall - 1 : 0) / 2;
+  if (np == 0) return 0;
+  float* d_rmat = nullptr;
+  CREST_CUDA_TRY(cudaMalloc(&d_rmat, sizeof(float) * np));
+  crest_cuda_thresholds t{1e300, 0.0, 0.0, 0.0, 0.0};
+  int rc = pairs_impl(c, enantio, &t, 0, 1, 0, d_rmat, nullptr);
+  if (!rc && cudaMemcpy(rmat, d_rmat, sizeof(float) * np, cudaMemcpyDeviceToHost) != cudaSuccess) {
+    set_error("D2H failed: %s", cudaGetErrorString(cudaGetLastError()));
+    rc = 1;
+  }
+  cudaFree(d_rmat);
+  return rc;
+}
+
+}  // extern "C"

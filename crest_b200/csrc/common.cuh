@@ -1,0 +1,109 @@
+// Shared declarations of the CREGEN CUDA path (sm_100a).  See DESIGN.md §3 for the HBM layout.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+
+namespace crest {
+
+constexpr int kPanel = 32;        // conformers per panel (= i-tile height)
+constexpr int kJPanels = 2;       // panels per j-tile (j-tile width 64)
+constexpr int kTileI = kPanel;
+constexpr int kTileJ = kPanel * kJPanels;
+constexpr int kConsumerWarps = 8; // 2 (i) x 4 (j) warps, each 16x16 pairs
+constexpr int kPairThreads = kConsumerWarps * 32;   // producer duty folded into warp 0
+constexpr double kAutokcal = 627.50947428;               // reference src/crest_pars.f90:23
+
+// Packed-coordinate layout in HBM (written by pack_axis, read by pair_tile through bulk copies):
+//   X[panel][slab][comp(3)][conf(32)][KS] doubles; one (panel,slab) chunk is contiguous.
+// KU atoms of each slab are used by the MMA loop (multiple of 8, zero padded), KS >= KU is the
+// row stride with KS % 16 == 8 so that 128-bit fragment loads are bank-conflict free.
+struct PackLayout {
+  int A;        // atoms entering the RMSD
+  int nslab;    // K slabs
+  int KU;       // atoms used per slab
+  int KS;       // row stride (doubles)
+  int npanel;   // panels (even, >= ceil(nall/32))
+  __host__ __device__ size_t chunk_doubles() const { return (size_t)3 * kPanel * KS; }
+  __host__ __device__ size_t total_doubles() const { return chunk_doubles() * nslab * npanel; }
+};
+
+inline PackLayout make_layout(int A, int nall) {
+  PackLayout L;
+  L.A = A;
+  const int a8 = ((A + 7) / 8) * 8;
+  L.nslab = (a8 + 39) / 40;
+  if (L.nslab < 1) L.nslab = 1;
+  const int blocks = (a8 / 8 + L.nslab - 1) / L.nslab;
+  L.KU = blocks * 8;
+  if (L.KU < 8) L.KU = 8;
+  L.KS = (L.KU % 16 == 8) ? L.KU : L.KU + 8;
+  int np = (nall + kPanel - 1) / kPanel;
+  if (np % kJPanels) np += kJPanels - (np % kJPanels);
+  if (np < kJPanels) np = kJPanels;
+  L.npanel = np;
+  return L;
+}
+
+// per-launch gate constants, precomputed on the host (capi.cu: make_gates)
+struct Gates {
+  double ethr;       // kcal/mol
+  double E1;         // e < E1  <=>  real(rmsd,sp) < rthr        (e = xn+yn-2*lambda)
+  double E2;         // e < E2  <=>  real(rmsd,sp) < 2*rthr
+  double bthr_half;  // 0.5*bthr (cregen.f90:1368)
+  double bthrmax, bthrshift;
+  int enantio;
+};
+
+}  // namespace crest
+
+#define CREST_CUDA_TRY(expr)                                                          \
+  do {                                                                                \
+    cudaError_t _e = (expr);                                                          \
+    if (_e != cudaSuccess) {                                                          \
+      crest::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return 1;                                                                       \
+    }                                                                                 \
+  } while (0)
+
+namespace crest {
+void set_error(const char* fmt, ...);
+
+// kernel launchers (implemented in the .cu files)
+int launch_pack_axis(int nat, int nall, const int* d_at, const double* d_xyz, const int* d_sel,
+                     int nsel, int rot_from_mask, const PackLayout& L, double* d_xyz_axis,
+                     double* d_rot, double* d_aniso, double* d_X, double* d_xn,
+                     cudaStream_t stream);
+int launch_rotconst(int nat, int n, const int* d_at, const double* d_xyz, double* d_rot,
+                    cudaStream_t stream);
+struct PairArgs {
+  const double* X;       // packed coordinates
+  const double* xn;      // centred squared norms
+  const double* er;      // energies (Hartree, ascending)
+  const double* rot;     // (3,nall) MHz
+  const double* aniso;   // rotaniso per structure
+  const long long* rowstart;  // [nI+1] prefix of tiles per i-panel
+  const int* jfirst;     // [nI] first j-tile of each i-panel
+  int nI;
+  int nall;
+  long long tile_begin, tile_end;   // this shard's slice of the tile list
+  int* dup;              // out, atomicMax of (j+1)
+  unsigned long long* npairs;       // out, atomicAdd
+  unsigned long long* mask;         // optional 8x8-tile bitmask [N8][N8]
+  int n8;
+  float* rmat;           // optional all-pairs float32 band (diagnostics)
+  Gates g;
+  PackLayout L;
+};
+int launch_pair_tiles(const PairArgs& a, int nstage, cudaStream_t stream, int* grid_out,
+                      int* smem_out);
+int pair_smem_bytes(const PackLayout& L, int* nstage_out);
+int launch_backtrack(int nall, int* d_dup, cudaStream_t stream);
+int launch_rmsd_pairs(int A, int n, const double* d_packed, long long npairs, const int* d_i,
+                      const int* d_j, double* d_rmsd, double* d_rmsd_m, cudaStream_t stream);
+int launch_enuc(int nat, int n, const int* d_at, const double* d_xyz, double* d_enuc,
+                cudaStream_t stream);
+int launch_group(int n, const double* d_er, const double* d_rot, const double* d_enuc,
+                 double ethr, double bthr, double bthrmax, double bthrshift, int* d_group,
+                 cudaStream_t stream);
+}  // namespace crest

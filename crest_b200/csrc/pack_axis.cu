@@ -1,0 +1,320 @@
+// Kernel (1): centring, principal-axis frame, rotational constants, RMSD-subset packing.
+//
+// Replaces the serial per-structure loop of the reference
+//   src/cregen.f90:1223-1231    call axis(nat,at,xyz(:,:,i)); call axis(nat0,at0,c1,rot(1:3,i),bdum)
+// i.e. axis_4 -> axis_3 (src/axis_module.f90:249-316): CMA shift (384-412), inertia tensor with
+// the t(k)=k*1e-10 seed (130-133), analytic eigenvectors (1088-1266), chirality fix (273-278),
+// rotation coordout = coord*evec; then axis_1 -> axis_0 (96-176) on the rotated (sub)structure for
+// rot(1:3) in MHz.  It also hoists what the reference redoes per pair: the heavy/subset masking
+// (cregen.f90:1293-1299, 2056-2101) and rmsd()'s unweighted centroid removal + norms
+// (src/ls_rmsd.f90:105-119), writing the packed operand X of the covariance contraction.
+//
+// One warp per conformer; lanes stride over atoms (24-byte records => fully coalesced), warp
+// shuffles reduce, every lane redoes the 3x3 eigenproblem redundantly (uniform control flow).
+// This file is compiled with -fmad=false: the eigen-solver follows the reference's operation
+// order so rot. constants agree to ~1e-12 relative away from degenerate moments.
+#include "common.cuh"
+#include "atmasses.cuh"
+#include "qcp.cuh"
+
+namespace crest {
+
+__constant__ double c_ams[CREST_NUM_ELEMENTS] = CREST_AMS_TABLE_INIT;
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ double mass_of(int z) {
+  return (z >= 1 && z <= CREST_NUM_ELEMENTS) ? c_ams[z - 1] : 0.0;
+}
+
+struct Sym3 { double a11, a12, a13, a22, a23, a33; };
+struct Mat3 { double m[3][3]; };   // m[row][col], 0-based
+
+// trigonometric eigenvalues of a symmetric 3x3 (reference axis_module.f90:1051-1083)
+__device__ void eigval_sym3(const Sym3& a, double w[3]) {
+  const double twothirdpi = 8.0 * atan(1.0) / 3.0;
+  double r = a.a12 * a.a12 + a.a13 * a.a13 + a.a23 * a.a23;
+  const double q = (a.a11 + a.a22 + a.a33) / 3.0;
+  w[0] = a.a11 - q;
+  w[1] = a.a22 - q;
+  w[2] = a.a33 - q;
+  const double p = sqrt((w[0] * w[0] + w[1] * w[1] + w[2] * w[2] + 2 * r) / 6.0);
+  r = (w[0] * (w[1] * w[2] - a.a23 * a.a23) - a.a12 * (a.a12 * w[2] - a.a23 * a.a13) +
+       a.a13 * (a.a12 * a.a23 - w[1] * a.a13)) / (p * p * p) * 0.5;
+  if (r <= -1.0) r = 0.5 * twothirdpi;
+  else if (r >= 1.0) r = 0.0;
+  else r = acos(r) / 3.0;
+  w[2] = q + 2 * p * cos(r);
+  w[0] = q + 2 * p * cos(r + twothirdpi);
+  w[1] = 3 * q - w[0] - w[2];
+}
+
+// analytic eigenvectors (reference axis_module.f90:1088-1266), columns of q
+__device__ void eigvec_sym3(Sym3 a, double w[3], Mat3& q) {
+  const double eps = 2.220446049250313e-16;
+  double norm, n1, n2, n3;
+  w[0] = fmax(fabs(a.a11), fabs(a.a12));
+  w[1] = fmax(fabs(a.a13), fabs(a.a22));
+  w[2] = fmax(fabs(a.a23), fabs(a.a33));
+  const double precon = fmax(w[0], fmax(w[1], w[2]));
+  if (precon < eps) {
+    w[0] = w[1] = w[2] = 0.0;
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) q.m[i][j] = (i == j) ? 1.0 : 0.0;
+    return;
+  }
+  norm = 1.0 / precon;
+  a.a11 *= norm; a.a12 *= norm; a.a22 *= norm; a.a13 *= norm; a.a23 *= norm; a.a33 *= norm;
+  eigval_sym3(a, w);
+
+  a.a11 -= w[0]; a.a22 -= w[0]; a.a33 -= w[0];
+  q.m[0][0] = a.a12 * a.a23 - a.a13 * a.a22;
+  q.m[1][0] = a.a13 * a.a12 - a.a11 * a.a23;
+  q.m[2][0] = a.a11 * a.a22 - a.a12 * a.a12;
+  q.m[0][1] = a.a12 * a.a33 - a.a13 * a.a23;
+  q.m[1][1] = a.a13 * a.a13 - a.a11 * a.a33;
+  q.m[2][1] = a.a11 * a.a23 - a.a12 * a.a13;
+  q.m[0][2] = a.a22 * a.a33 - a.a23 * a.a23;
+  q.m[1][2] = a.a23 * a.a13 - a.a12 * a.a33;
+  q.m[2][2] = a.a12 * a.a23 - a.a22 * a.a13;
+  n1 = q.m[0][0] * q.m[0][0] + q.m[1][0] * q.m[1][0] + q.m[2][0] * q.m[2][0];
+  n2 = q.m[0][1] * q.m[0][1] + q.m[1][1] * q.m[1][1] + q.m[2][1] * q.m[2][1];
+  n3 = q.m[0][2] * q.m[0][2] + q.m[1][2] * q.m[1][2] + q.m[2][2] * q.m[2][2];
+  // column choice exactly as written in the reference (1150-1158): the running maximum is NOT
+  // updated when column 2 is taken, so column 3 wins whenever n3 > n1
+  int pick = 0;
+  if (n2 > n1) pick = 1;
+  if (n3 > n1) pick = 2;
+  {
+    const double nn = (pick == 0) ? n1 : ((pick == 1) ? n2 : n3);
+    norm = sqrt(1.0 / nn);
+    const double v0 = q.m[0][pick] * norm, v1 = q.m[1][pick] * norm, v2 = q.m[2][pick] * norm;
+    q.m[0][0] = v0; q.m[1][0] = v1; q.m[2][0] = v2;
+  }
+  if (fabs(q.m[0][0]) > fabs(q.m[1][0])) {
+    norm = sqrt(1.0 / (q.m[0][0] * q.m[0][0] + q.m[2][0] * q.m[2][0]));
+    q.m[0][1] = -q.m[2][0] * norm; q.m[1][1] = 0.0; q.m[2][1] = +q.m[0][0] * norm;
+  } else {
+    norm = sqrt(1.0 / (q.m[1][0] * q.m[1][0] + q.m[2][0] * q.m[2][0]));
+    q.m[0][1] = 0.0; q.m[1][1] = +q.m[2][0] * norm; q.m[2][1] = -q.m[1][0] * norm;
+  }
+  q.m[0][2] = q.m[1][0] * q.m[2][1] - q.m[2][0] * q.m[1][1];
+  q.m[1][2] = q.m[2][0] * q.m[0][1] - q.m[0][0] * q.m[2][1];
+  q.m[2][2] = q.m[0][0] * q.m[1][1] - q.m[1][0] * q.m[0][1];
+
+  a.a11 += w[0]; a.a22 += w[0]; a.a33 += w[0];
+  // A*U
+  n1 = a.a11 * q.m[0][1] + a.a12 * q.m[1][1] + a.a13 * q.m[2][1];
+  n2 = a.a12 * q.m[0][1] + a.a22 * q.m[1][1] + a.a23 * q.m[2][1];
+  n3 = a.a13 * q.m[0][1] + a.a23 * q.m[1][1] + a.a33 * q.m[2][1];
+  // A*V, stored over a(:,3) in the reference's (deliberately) permuted order (1200-1203)
+  a.a33 = a.a13 * q.m[0][2] + a.a23 * q.m[1][2] + a.a33 * q.m[2][2];
+  a.a13 = a.a11 * q.m[0][2] + a.a12 * q.m[1][2] + a.a13 * q.m[2][2];
+  a.a23 = a.a12 * q.m[0][2] + a.a22 * q.m[1][2] + a.a23 * q.m[2][2];
+  n1 = q.m[0][1] * n1 + q.m[1][1] * n2 + q.m[2][1] * n3 - w[1];
+  n2 = q.m[0][1] * a.a13 + q.m[1][1] * a.a23 + q.m[2][1] * a.a33;
+  n3 = q.m[0][2] * a.a13 + q.m[1][2] * a.a23 + q.m[2][2] * a.a33 - w[1];
+
+  if (fabs(n1) >= fabs(n3)) {
+    norm = fmax(fabs(n1), fabs(n2));
+    if (norm > eps) {
+      if (fabs(n1) >= fabs(n2)) { n2 = n2 / n1; n1 = sqrt(1.0 / (1.0 + n2 * n2)); n2 = n2 * n1; }
+      else { n1 = n1 / n2; n2 = sqrt(1.0 / (1.0 + n1 * n1)); n1 = n1 * n2; }
+      q.m[0][1] = n2 * q.m[0][1] - n1 * q.m[0][2];
+      q.m[1][1] = n2 * q.m[1][1] - n1 * q.m[1][2];
+      q.m[2][1] = n2 * q.m[2][1] - n1 * q.m[2][2];
+    }
+  } else {
+    norm = fmax(fabs(n3), fabs(n2));
+    if (norm > eps) {
+      if (fabs(n3) >= fabs(n2)) { n2 = n2 / n3; n3 = sqrt(1.0 / (1.0 + n2 * n2)); n2 = n2 * n3; }
+      else { n3 = n3 / n2; n2 = sqrt(1.0 / (1.0 + n3 * n3)); n3 = n3 * n2; }
+      q.m[0][1] = n3 * q.m[0][1] - n2 * q.m[0][2];
+      q.m[1][1] = n3 * q.m[1][1] - n2 * q.m[1][2];
+      q.m[2][1] = n3 * q.m[2][1] - n2 * q.m[2][2];
+    }
+  }
+  q.m[0][2] = q.m[1][0] * q.m[2][1] - q.m[2][0] * q.m[1][1];
+  q.m[1][2] = q.m[2][0] * q.m[0][1] - q.m[0][0] * q.m[2][1];
+  q.m[2][2] = q.m[0][0] * q.m[1][1] - q.m[1][0] * q.m[0][1];
+  w[0] *= precon; w[1] *= precon; w[2] *= precon;
+}
+
+// axis_0 core on coordinates supplied through a functor: returns rot (MHz), evec, CMA.
+// `get(k, z, px,py,pz)` yields atom k of the (sub)structure.  Lanes stride over atoms.
+template <class Get>
+__device__ void axis0_warp(int n, Get get, int lane, double rot[3], Mat3& evec, double cma[3]) {
+  // CMA (axis_module.f90:384-412; sumw seeded with 1e-20)
+  double sw = 0.0, sx = 0.0, sy = 0.0, sz = 0.0;
+  for (int k = lane; k < n; k += 32) {
+    int z; double x, y, zc;
+    get(k, z, x, y, zc);
+    const double m = mass_of(z);
+    sw += m; sx += m * x; sy += m * y; sz += m * zc;
+  }
+  sw = warp_sum(sw) + 1.0e-20;
+  sx = warp_sum(sx) / sw; sy = warp_sum(sy) / sw; sz = warp_sum(sz) / sw;
+  cma[0] = sx; cma[1] = sy; cma[2] = sz;
+  // inertia tensor (axis_module.f90:130-141)
+  double t1 = 0, t2 = 0, t3 = 0, t4 = 0, t5 = 0, t6 = 0;
+  for (int k = lane; k < n; k += 32) {
+    int z; double x, y, zc;
+    get(k, z, x, y, zc);
+    const double m = mass_of(z);
+    x -= sx; y -= sy; zc -= sz;
+    t1 += m * (y * y + zc * zc);
+    t2 -= m * x * y;
+    t3 += m * (zc * zc + x * x);
+    t4 -= m * zc * x;
+    t5 -= m * y * zc;
+    t6 += m * (x * x + y * y);
+  }
+  Sym3 a;
+  a.a11 = warp_sum(t1) + 1.0e-10;
+  a.a12 = warp_sum(t2) + 2.0e-10;
+  a.a22 = warp_sum(t3) + 3.0e-10;
+  a.a13 = warp_sum(t4) + 4.0e-10;
+  a.a23 = warp_sum(t5) + 5.0e-10;
+  a.a33 = warp_sum(t6) + 6.0e-10;
+  double eig[3];
+  eigvec_sym3(a, eig, evec);
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j)
+      if (fabs(evec.m[i][j]) < 1e-9) evec.m[i][j] = 0.0;
+    if (eig[i] < 3.0e-4) rot[i] = 0.0;
+    else rot[i] = 2.9979245e+4 * 16.8576522 / eig[i];   // icm2MHz*Aamu2icm (axis_module.f90:25,34)
+  }
+}
+
+__global__ void __launch_bounds__(128)
+pack_axis_kernel(int nat, int nall, const int* __restrict__ at, const double* __restrict__ xyz,
+                 const int* __restrict__ sel, int nsel, int rot_from_mask, PackLayout L,
+                 double* __restrict__ xyz_axis, double* __restrict__ rot_out,
+                 double* __restrict__ aniso_out, double* __restrict__ X,
+                 double* __restrict__ xn_out) {
+  const int lane = threadIdx.x & 31;
+  const int conf = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (conf >= nall) return;
+  const double* src = xyz + (size_t)3 * nat * conf;
+  double* dst = xyz_axis + (size_t)3 * nat * conf;
+
+  // ---- pass 1: axis_4 = CMA shift + rotation into the principal-axis frame
+  double rot[3], cma[3];
+  Mat3 ev;
+  auto get_all = [&](int k, int& z, double& x, double& y, double& zc) {
+    z = at[k]; x = src[3 * k]; y = src[3 * k + 1]; zc = src[3 * k + 2];
+  };
+  axis0_warp(nat, get_all, lane, rot, ev, cma);
+  {
+    // calcxsum (axis_module.f90:372-378): keep a right-handed frame
+    const double xsum = ev.m[0][0] * (ev.m[1][1] * ev.m[2][2] - ev.m[2][1] * ev.m[1][2]) +
+                        ev.m[0][1] * (ev.m[1][2] * ev.m[2][0] - ev.m[1][0] * ev.m[2][2]) +
+                        ev.m[0][2] * (ev.m[1][0] * ev.m[2][1] - ev.m[1][1] * ev.m[2][0]);
+    if (xsum < 0.0) { ev.m[0][0] = -ev.m[0][0]; ev.m[1][0] = -ev.m[1][0]; ev.m[2][0] = -ev.m[2][0]; }
+  }
+  for (int k = lane; k < nat; k += 32) {
+    const double x = src[3 * k] - cma[0], y = src[3 * k + 1] - cma[1], z = src[3 * k + 2] - cma[2];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      double s = 0.0;
+      s = s + x * ev.m[0][j];
+      s = s + y * ev.m[1][j];
+      s = s + z * ev.m[2][j];
+      dst[3 * k + j] = s;
+    }
+  }
+  __syncwarp();
+
+  // ---- pass 2: axis_1 on the rotated structure (all atoms, or the subset if substruc)
+  Mat3 ev2;
+  double cma2[3];
+  if (rot_from_mask) {
+    auto get_sub = [&](int k, int& z, double& x, double& y, double& zc) {
+      const int a = sel[k];
+      z = at[a]; x = dst[3 * a]; y = dst[3 * a + 1]; zc = dst[3 * a + 2];
+    };
+    axis0_warp(nsel, get_sub, lane, rot, ev2, cma2);
+  } else {
+    auto get_rot = [&](int k, int& z, double& x, double& y, double& zc) {
+      z = at[k]; x = dst[3 * k]; y = dst[3 * k + 1]; zc = dst[3 * k + 2];
+    };
+    axis0_warp(nat, get_rot, lane, rot, ev2, cma2);
+  }
+  if (lane == 0) {
+    rot_out[3 * conf + 0] = rot[0];
+    rot_out[3 * conf + 1] = rot[1];
+    rot_out[3 * conf + 2] = rot[2];
+    aniso_out[conf] = rotaniso_dev(rot[0], rot[1], rot[2]);
+  }
+
+  // ---- pass 3: RMSD subset, unweighted centroid (ls_rmsd.f90:105-119), packed operand + norm
+  double cx = 0.0, cy = 0.0, cz = 0.0;
+  for (int k = lane; k < nsel; k += 32) {
+    const int a = sel[k];
+    cx += dst[3 * a]; cy += dst[3 * a + 1]; cz += dst[3 * a + 2];
+  }
+  const double inv_n = 1.0 / (double)nsel;
+  cx = warp_sum(cx) * inv_n; cy = warp_sum(cy) * inv_n; cz = warp_sum(cz) * inv_n;
+  const int panel = conf / kPanel, row = conf % kPanel;
+  double nrm = 0.0;
+  const int kpad = L.nslab * L.KU;
+  for (int k = lane; k < kpad; k += 32) {
+    double x = 0.0, y = 0.0, z = 0.0;
+    if (k < nsel) {
+      const int a = sel[k];
+      x = dst[3 * a] - cx; y = dst[3 * a + 1] - cy; z = dst[3 * a + 2] - cz;
+      nrm += x * x + y * y + z * z;
+    }
+    const int slab = k / L.KU, kk = k % L.KU;
+    double* chunk = X + ((size_t)panel * L.nslab + slab) * L.chunk_doubles();
+    chunk[((size_t)0 * kPanel + row) * L.KS + kk] = x;
+    chunk[((size_t)1 * kPanel + row) * L.KS + kk] = y;
+    chunk[((size_t)2 * kPanel + row) * L.KS + kk] = z;
+  }
+  nrm = warp_sum(nrm);
+  if (lane == 0) xn_out[conf] = nrm;
+}
+
+__global__ void __launch_bounds__(128)
+rotconst_kernel(int nat, int n, const int* __restrict__ at, const double* __restrict__ xyz,
+                double* __restrict__ rot_out) {
+  const int lane = threadIdx.x & 31;
+  const int conf = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (conf >= n) return;
+  const double* src = xyz + (size_t)3 * nat * conf;
+  double rot[3], cma[3];
+  Mat3 ev;
+  auto get_all = [&](int k, int& z, double& x, double& y, double& zc) {
+    z = at[k]; x = src[3 * k]; y = src[3 * k + 1]; zc = src[3 * k + 2];
+  };
+  axis0_warp(nat, get_all, lane, rot, ev, cma);
+  if (lane == 0) {
+    rot_out[3 * conf + 0] = rot[0]; rot_out[3 * conf + 1] = rot[1]; rot_out[3 * conf + 2] = rot[2];
+  }
+}
+
+int launch_pack_axis(int nat, int nall, const int* d_at, const double* d_xyz, const int* d_sel,
+                     int nsel, int rot_from_mask, const PackLayout& L, double* d_xyz_axis,
+                     double* d_rot, double* d_aniso, double* d_X, double* d_xn,
+                     cudaStream_t stream) {
+  if (nall <= 0) return 0;
+  const int wpb = 4;
+  pack_axis_kernel<<<(nall + wpb - 1) / wpb, wpb * 32, 0, stream>>>(
+      nat, nall, d_at, d_xyz, d_sel, nsel, rot_from_mask, L, d_xyz_axis, d_rot, d_aniso, d_X, d_xn);
+  CREST_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int launch_rotconst(int nat, int n, const int* d_at, const double* d_xyz, double* d_rot,
+                    cudaStream_t stream) {
+  if (n <= 0) return 0;
+  const int wpb = 4;
+  rotconst_kernel<<<(n + wpb - 1) / wpb, wpb * 32, 0, stream>>>(nat, n, d_at, d_xyz, d_rot);
+  CREST_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace crest

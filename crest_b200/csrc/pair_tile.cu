@@ -1,0 +1,290 @@
+// Kernels (2)+(3): all-pairs 3x3 covariance blocks on the FP64 tensor path (DMMA m8n8k4) with the
+// per-pair epilogue fused in registers.
+//
+// Replaces the reference's pair loops K1/K2/K3 (src/cregen.f90:1266-1349: serial i, OpenMP j,
+// two rmsd() calls per pair = src/ls_rmsd.f90:72-174) and the duplicate test of K4
+// (src/cregen.f90:1353-1373).  No float32 rmat band is materialised: the thresholds are applied
+// where the covariance lives.
+//
+// Tiling: a CTA owns a 32(i) x 64(j) pair tile; 8 consumer warps (2 x 4) each own 16 x 16 pairs =
+// 2 x 2 DMMA tiles x 9 covariance components (a,b in xyz) = 72 FP64 accumulators per lane, so a
+// lane ends the K loop holding the complete 3x3 R of its 8 pairs - no shuffle before the epilogue.
+// One producer warp streams (panel, slab) chunks of the packed operand X with 1-D bulk async
+// copies (TMA engine, cp.async.bulk -> UBLKCP) into an mbarrier ring; the ring runs across tile
+// boundaries so the next tile's operands land while the current epilogue executes.
+// tcgen05/UMMA has no FP64 kind, so the FP64 contraction is warp-level mma.sync (DMMA); the
+// microbenchmark (profiles/r01_fp64_pipes_microbench.txt) shows DMMA and DFMA share one pipe on
+// B200, which is why the epilogue is written to minimise FP64 instruction count.
+#include "common.cuh"
+#include "qcp.cuh"
+
+namespace crest {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {}
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1},{%2},{%3},{%0,%1};"
+               : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+constexpr int kMaxStages = 4;
+
+__device__ __forceinline__ void decode_tile(const PairArgs& a, long long t, int& I, int& J) {
+  int lo = 0, hi = a.nI - 1;           // largest I with rowstart[I] <= t
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (a.rowstart[mid] <= t) lo = mid; else hi = mid - 1;
+  }
+  I = lo;
+  J = a.jfirst[lo] + (int)(t - a.rowstart[lo]);
+}
+
+__global__ void __launch_bounds__(kPairThreads, 1)
+pair_tile_kernel(const PairArgs a, const int nstage) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[kMaxStages];
+  __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const PackLayout L = a.L;
+  const size_t chunk = L.chunk_doubles();
+  const uint32_t chunk_bytes = (uint32_t)(chunk * sizeof(double));
+  const size_t stage_doubles = chunk * (1 + kJPanels);
+  double* const sbase = reinterpret_cast<double*>(smem_raw);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < nstage; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], kConsumerWarps);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  // -------------------------------- consumer warps --------------------------------
+  const int wi = warp & 1;        // 16-row half of the i panel
+  const int wj = warp >> 1;       // 16-column quarter of the 64 j columns
+  const int c = lane >> 2, tq = lane & 3;
+  // fragment base offsets (doubles) inside a stage: row (conformer) * KS + 2*tq
+  const int KS = L.KS;
+  const int a_off = (wi * 16 + c) * KS + 2 * tq;                       // + mi*8*KS + comp*32*KS
+  const int jrow = wj * 16 + c;                                        // 0..63 (+ nj*8)
+  const int b_off0 = (int)chunk * (1 + (jrow >> 5)) + (jrow & 31) * KS + 2 * tq;
+  const int b_off1 = (int)chunk * (1 + ((jrow + 8) >> 5)) + ((jrow + 8) & 31) * KS + 2 * tq;
+  const int comp_stride = kPanel * KS;
+  const int nblk = L.KU >> 3;
+
+  // Producer duty is folded into lane 0 of warp 0 (a 9th warp would be accounted as 12 warps by
+  // the register allocator and cap the kernel at 168 registers): it keeps the ring nstage-1
+  // items ahead of the consumers.  An item = one K slab of one tile (3 bulk copies).
+  const bool is_producer = (threadIdx.x == 0);
+  long long p_tile = a.tile_begin + blockIdx.x;
+  int p_slab = 0, p_I = 0, p_J = 0;
+  uint32_t p_it = 0;
+  auto produce_one = [&]() {
+    if (p_tile >= a.tile_end) return;
+    if (p_slab == 0) decode_tile(a, p_tile, p_I, p_J);
+    const int st = p_it % nstage;
+    const uint32_t ph = (p_it / nstage) & 1;
+    mbar_wait(&empty_bar[st], ph ^ 1);
+    double* dst = sbase + (size_t)st * stage_doubles;
+    mbar_expect_tx(&full_bar[st], chunk_bytes * (1 + kJPanels));
+    bulk_g2s(dst, a.X + ((size_t)p_I * L.nslab + p_slab) * chunk, chunk_bytes, &full_bar[st]);
+#pragma unroll
+    for (int p = 0; p < kJPanels; ++p)
+      bulk_g2s(dst + chunk * (1 + p),
+               a.X + ((size_t)(p_J * kJPanels + p) * L.nslab + p_slab) * chunk, chunk_bytes,
+               &full_bar[st]);
+    ++p_it;
+    if (++p_slab == L.nslab) { p_slab = 0; p_tile += gridDim.x; }
+  };
+  if (is_producer)
+    for (int s = 0; s < nstage - 1; ++s) produce_one();
+
+  unsigned long long my_pairs = 0;
+  uint32_t it = 0;
+  for (long long t = a.tile_begin + blockIdx.x; t < a.tile_end; t += gridDim.x) {
+    int I, J;
+    decode_tile(a, t, I, J);
+    const int i0 = I * kTileI + wi * 16;       // first i of this warp
+    const int j0 = J * kTileJ + wj * 16;       // first j of this warp
+    // warp-level activity: any pair with j < i, i < nall
+    const bool active = (j0 < i0 + 16) && (i0 < a.nall) && (j0 < a.nall);
+
+    double acc[2][2][9][2];
+#pragma unroll
+    for (int x = 0; x < 2; ++x)
+#pragma unroll
+      for (int y = 0; y < 2; ++y)
+#pragma unroll
+        for (int z = 0; z < 9; ++z) { acc[x][y][z][0] = 0.0; acc[x][y][z][1] = 0.0; }
+
+    for (int s = 0; s < L.nslab; ++s, ++it) {
+      const int st = it % nstage;
+      const uint32_t ph = (it / nstage) & 1;
+      if (is_producer) produce_one();
+      __syncwarp();
+      mbar_wait(&full_bar[st], ph);
+      if (active) {
+        const double* sb = sbase + (size_t)st * stage_doubles;
+#pragma unroll 1
+        for (int kb = 0; kb < nblk; ++kb) {
+          double2 fa[2][3];
+#pragma unroll
+          for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+            for (int x = 0; x < 3; ++x)
+              fa[mi][x] = *reinterpret_cast<const double2*>(
+                  sb + a_off + mi * 8 * KS + x * comp_stride + kb * 8);
+#pragma unroll
+          for (int nj = 0; nj < 2; ++nj) {
+            double2 fb[3];
+            const int bo = nj ? b_off1 : b_off0;
+#pragma unroll
+            for (int y = 0; y < 3; ++y)
+              fb[y] = *reinterpret_cast<const double2*>(sb + bo + y * comp_stride + kb * 8);
+#pragma unroll
+            for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+              for (int x = 0; x < 3; ++x)
+#pragma unroll
+                for (int y = 0; y < 3; ++y) {
+                  dmma(acc[mi][nj][3 * x + y][0], acc[mi][nj][3 * x + y][1], fa[mi][x].x, fb[y].x);
+                  dmma(acc[mi][nj][3 * x + y][0], acc[mi][nj][3 * x + y][1], fa[mi][x].y, fb[y].y);
+                }
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_bar[st]);
+    }
+    if (!active) continue;
+
+    // ------------------------------ fused epilogue ------------------------------
+    // energy gate can only fail in tiles on the band edge: max de sits at (largest i, smallest j)
+    const int ti_last = min(I * kTileI + kTileI - 1, a.nall - 1);
+    const bool edge =
+        !(__dmul_rn(__dsub_rn(a.er[ti_last], a.er[J * kTileJ]), kAutokcal) < a.g.ethr);
+#pragma unroll
+    for (int mi = 0; mi < 2; ++mi) {
+      const int i = i0 + mi * 8 + c;
+      const bool iok = i < a.nall;
+      const double xni = iok ? a.xn[i] : 0.0;
+      const double eri = (edge && iok) ? a.er[i] : 0.0;
+#pragma unroll
+      for (int nj = 0; nj < 2; ++nj) {
+        unsigned hit[2] = {0u, 0u};
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+          const int j = j0 + nj * 8 + 2 * tq + p;
+          bool ok = iok && (j < i);
+          if (ok && edge) ok = __dmul_rn(__dsub_rn(eri, a.er[j]), kAutokcal) < a.g.ethr;
+          bool dupl = false;
+          if (ok) {
+            ++my_pairs;
+            double r[9];
+#pragma unroll
+            for (int z = 0; z < 9; ++z) r[z] = acc[mi][nj][z][p];
+            const double s = xni + a.xn[j];
+            const double e = pair_e(r, s, a.g.enantio, 0);
+            if (a.rmat) {
+              const double rr = sqrt(fmax(0.0, e) / (double)L.A);
+              a.rmat[(size_t)i * (i - 1) / 2 + j] = (float)rr;
+            }
+            if (e < a.g.E2) {
+              dupl = e < a.g.E1;
+              if (!dupl)
+                dupl = equalrotaniso_dev(a.rot + 3 * (size_t)i, a.rot + 3 * (size_t)j, a.aniso[i],
+                                         a.aniso[j], a.g.bthr_half, a.g.bthrmax, a.g.bthrshift);
+              if (dupl) atomicMax(a.dup + i, j + 1);
+            }
+          }
+          if (a.mask) hit[p] = __ballot_sync(0xffffffffu, dupl);
+        }
+        if (a.mask && lane == 0 && (hit[0] | hit[1])) {
+          // ballot bit (row*4 + tq) of parity p  ->  tile bit row*8 + 2*tq + p
+          unsigned long long w = 0;
+#pragma unroll
+          for (int p = 0; p < 2; ++p) {
+            unsigned long long x = hit[p];
+            x = (x | (x << 16)) & 0x0000FFFF0000FFFFull;
+            x = (x | (x << 8)) & 0x00FF00FF00FF00FFull;
+            x = (x | (x << 4)) & 0x0F0F0F0F0F0F0F0Full;
+            x = (x | (x << 2)) & 0x3333333333333333ull;
+            x = (x | (x << 1)) & 0x5555555555555555ull;
+            w |= x << p;
+          }
+          const int ti8 = (i0 + mi * 8) >> 3, tj8 = (j0 + nj * 8) >> 3;
+          a.mask[(size_t)ti8 * a.n8 + tj8] = w;
+        }
+      }
+    }
+  }
+  // one atomic per warp for the pair counter
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) my_pairs += __shfl_xor_sync(0xffffffffu, my_pairs, o);
+  if (lane == 0 && my_pairs) atomicAdd(a.npairs, my_pairs);
+}
+
+int pair_smem_bytes(const PackLayout& L, int* nstage_out) {
+  const size_t stage = L.chunk_doubles() * (1 + kJPanels) * sizeof(double);
+  int ns = (int)((size_t)(227 * 1024 - 1024) / stage);
+  if (ns > kMaxStages) ns = kMaxStages;
+  if (ns < 1) ns = 1;
+  if (nstage_out) *nstage_out = ns;
+  return (int)(stage * ns);
+}
+
+int launch_pair_tiles(const PairArgs& a, int nstage, cudaStream_t stream, int* grid_out,
+                      int* smem_out) {
+  const long long ntiles = a.tile_end - a.tile_begin;
+  if (grid_out) *grid_out = 0;
+  if (ntiles <= 0) return 0;
+  int dev = 0, nsm = 148;
+  CREST_CUDA_TRY(cudaGetDevice(&dev));
+  CREST_CUDA_TRY(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
+  int ns = nstage;
+  const int smem = pair_smem_bytes(a.L, nstage > 0 ? nullptr : &ns);
+  const size_t stage = a.L.chunk_doubles() * (1 + kJPanels) * sizeof(double);
+  const int smem_used = (int)(stage * ns);
+  (void)smem;
+  CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tile_kernel,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, smem_used));
+  const int grid = (int)(ntiles < nsm ? ntiles : nsm);   // persistent: one CTA per SM
+  pair_tile_kernel<<<grid, kPairThreads, smem_used, stream>>>(a, ns);
+  CREST_CUDA_TRY(cudaGetLastError());
+  if (grid_out) *grid_out = grid;
+  if (smem_out) *smem_out = smem_used;
+  return 0;
+}
+
+}  // namespace crest

@@ -1,0 +1,183 @@
+// Per-pair epilogue math, all in registers (FP64).
+//
+// The reference obtains lambda_max of the 4x4 key matrix S(R) by Givens tridiagonalisation + SVD
+// (reference src/ls_rmsd.f90:223-284).  Here lambda_max is the largest root of the characteristic
+// quartic of S written in the invariants of the 3x3 covariance R (sigma_k = singular values):
+//     P(l) = l^4 - 2*I1*l^2 - 8*det(R)*l + (I1^2 - 4*I2),
+//     I1 = ||R||_F^2 = sum sigma^2,   I2 = ||cof R||_F^2 = sum_{a<b} sigma_a^2 sigma_b^2,
+// whose roots are (+-sigma1 +-sigma2 +-sigma3) with an even number of minus signs times
+// sign(det R).  Negating x of the second structure (the reference's mirror test,
+// src/cregen.f90:1279-1284) flips the sign of det R only, so min(rmsd, rmsd_mirror) belongs to
+// the quartic with -8*|det R|: one Newton solve per pair instead of two eigen-decompositions.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace crest {
+
+__device__ __forceinline__ double rcp_approx(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));   // MUFU.RCP64H, ~20 bits
+  return r;
+}
+
+struct Quartic {
+  double c2, c1abs, c0;   // P(l) = l^4 + c2 l^2 -+ c1abs l + c0 ; c1abs = 8*|det R|
+  double det;
+};
+
+// R row-major r[3*a+b]
+__device__ __forceinline__ Quartic quartic_of(const double* r) {
+  const double i1 = fma(r[8], r[8], fma(r[7], r[7], fma(r[6], r[6], fma(r[5], r[5],
+                    fma(r[4], r[4], fma(r[3], r[3], fma(r[2], r[2], fma(r[1], r[1], r[0] * r[0]))))))));
+  const double k00 = fma(r[4], r[8], -r[5] * r[7]);
+  const double k01 = fma(r[5], r[6], -r[3] * r[8]);
+  const double k02 = fma(r[3], r[7], -r[4] * r[6]);
+  const double k10 = fma(r[2], r[7], -r[1] * r[8]);
+  const double k11 = fma(r[0], r[8], -r[2] * r[6]);
+  const double k12 = fma(r[1], r[6], -r[0] * r[7]);
+  const double k20 = fma(r[1], r[5], -r[2] * r[4]);
+  const double k21 = fma(r[2], r[3], -r[0] * r[5]);
+  const double k22 = fma(r[0], r[4], -r[1] * r[3]);
+  const double det = fma(r[0], k00, fma(r[1], k01, r[2] * k02));
+  const double i2 = fma(k22, k22, fma(k21, k21, fma(k20, k20, fma(k12, k12, fma(k11, k11,
+                    fma(k10, k10, fma(k02, k02, fma(k01, k01, k00 * k00))))))));
+  Quartic q;
+  q.c2 = -2.0 * i1;
+  q.det = det;
+  q.c1abs = 8.0 * fabs(det);
+  q.c0 = fma(i1, i1, -4.0 * i2);
+  return q;
+}
+
+// Cyclic Jacobi on the symmetric traceless 4x4 key matrix (ls_rmsd.f90:129-147); the rare,
+// exact path for (near-)degenerate lambda_max where Newton on the quartic stalls.
+static __device__ __noinline__ double lambda_max_jacobi(const double* r, double sign_x) {
+  // sign_x = -1 builds S for the mirrored second structure (column... row 1 of y negated)
+  double R[3][3];
+  for (int a = 0; a < 3; ++a) {
+    R[a][0] = r[3 * a + 0] * sign_x;   // y_x -> -y_x flips column 0 of R(a,b)=sum x_a y_b
+    R[a][1] = r[3 * a + 1];
+    R[a][2] = r[3 * a + 2];
+  }
+  double S[4][4];
+  S[0][0] = R[0][0] + R[1][1] + R[2][2];
+  S[1][0] = R[1][2] - R[2][1];
+  S[2][0] = R[2][0] - R[0][2];
+  S[3][0] = R[0][1] - R[1][0];
+  S[1][1] = R[0][0] - R[1][1] - R[2][2];
+  S[2][1] = R[0][1] + R[1][0];
+  S[3][1] = R[0][2] + R[2][0];
+  S[2][2] = -R[0][0] + R[1][1] - R[2][2];
+  S[3][2] = R[1][2] + R[2][1];
+  S[3][3] = -R[0][0] - R[1][1] + R[2][2];
+  for (int i = 0; i < 4; ++i)
+    for (int j = i + 1; j < 4; ++j) S[i][j] = S[j][i];
+  for (int sweep = 0; sweep < 50; ++sweep) {
+    double off = 0.0, diag = 0.0;
+    for (int i = 0; i < 4; ++i) {
+      diag += S[i][i] * S[i][i];
+      for (int j = i + 1; j < 4; ++j) off += S[i][j] * S[i][j];
+    }
+    if (off <= 1e-34 * diag || off == 0.0) break;
+    for (int p = 0; p < 3; ++p)
+      for (int q = p + 1; q < 4; ++q) {
+        const double apq = S[p][q];
+        if (apq == 0.0) continue;
+        const double theta = (S[q][q] - S[p][p]) / (2.0 * apq);
+        const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+        const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
+        for (int k = 0; k < 4; ++k) {
+          const double akp = S[k][p], akq = S[k][q];
+          S[k][p] = c * akp - s * akq;
+          S[k][q] = s * akp + c * akq;
+        }
+        for (int k = 0; k < 4; ++k) {
+          const double apk = S[p][k], aqk = S[q][k];
+          S[p][k] = c * apk - s * aqk;
+          S[q][k] = s * apk + c * aqk;
+        }
+      }
+  }
+  return fmax(fmax(S[0][0], S[1][1]), fmax(S[2][2], S[3][3]));
+}
+
+// Largest root of l^4 + c2 l^2 + c1 l + c0 by Newton from the upper bound l0 >= lambda_max.
+// Monotone from the right for a real-rooted quartic.  Returns false if not converged (caller
+// falls back to Jacobi).
+__device__ __forceinline__ bool newton_lambda(double c2, double c1, double c0, double l0,
+                                              double& lam_out) {
+  double l = l0;
+  const double tol = 1e-11 * l0;
+  bool ok = false;
+#pragma unroll 1
+  for (int it = 0; it < 40; ++it) {
+    const double x2 = l * l;
+    const double a = x2 + c2;
+    const double b = a * l;
+    const double t = b + c1;
+    const double f = fma(t, l, c0);
+    const double fp = fma(x2 + x2, l, b) + t;
+    const double d = f * rcp_approx(fp);
+    l -= d;
+    if (fabs(d) <= tol) { ok = true; break; }
+  }
+  // a (near-)double root shows as a derivative that vanished relative to its natural scale
+  {
+    const double x2 = l * l;
+    const double fp = fma(4.0 * x2, l, fma(2.0 * c2, l, c1));
+    if (!(fabs(fp) > 1e-6 * x2 * l)) ok = false;
+  }
+  lam_out = l;
+  return ok;
+}
+
+// e = xn + yn - 2*lambda for the minimum of proper / mirror RMSD (mirror only if enantio).
+// Also usable for a single chirality: pass enantio=0 (proper) or det-sign flipped via mirror=1.
+__device__ __forceinline__ double pair_e(const double* r, double s, int enantio, int mirror) {
+  const Quartic q = quartic_of(r);
+  double c1;
+  if (enantio) c1 = -q.c1abs;
+  else c1 = mirror ? 8.0 * q.det : -8.0 * q.det;
+  double lam;
+  if (!newton_lambda(q.c2, c1, q.c0, 0.5 * s, lam)) {
+    if (enantio) lam = fmax(lambda_max_jacobi(r, 1.0), lambda_max_jacobi(r, -1.0));
+    else lam = lambda_max_jacobi(r, mirror ? -1.0 : 1.0);
+  }
+  return fma(-2.0, lam, s);
+}
+
+// reference src/rotcompare.f90:109-122 (same operation order)
+__device__ __forceinline__ double rotaniso_dev(double a, double b, double c) {
+  const double av = __ddiv_rn(__dadd_rn(__dadd_rn(a, b), c), 3.0);
+  const double da = __dsub_rn(a, av), db = __dsub_rn(b, av), dc = __dsub_rn(c, av);
+  double r = sqrt(__dadd_rn(__dadd_rn(__dmul_rn(da, da), __dmul_rn(db, db)), __dmul_rn(dc, dc)));
+  r = __ddiv_rn(r, av);
+  r = __ddiv_rn(r, __dmul_rn(3.0, sqrt(__ddiv_rn(2.0, 3.0))));
+  return r;
+}
+
+// reference src/rotcompare.f90:127-142
+__device__ __forceinline__ double bthrerf_dev(double bthr, double aniso, double bthrmax,
+                                              double bthrshift) {
+  const double c = __ddiv_rn(__dsub_rn(__dmul_rn(bthrmax, 100.0), __dmul_rn(bthr, 100.0)), 2.0);
+  const double a = __dadd_rn(__dmul_rn(-erf(-2.5), c), __dmul_rn(bthr, 100.0));
+  const double b = __ddiv_rn(4.0, 0.8);
+  const double d = __ddiv_rn(bthrshift, 0.15);
+  double thr = __dadd_rn(__dmul_rn(erf(__dsub_rn(__dmul_rn(aniso, b), d)), c), a);
+  thr = __ddiv_rn(thr, 100.0);
+  return thr;
+}
+
+// reference src/rotcompare.f90:146-169 ; division by a zero rot. constant gives Inf/NaN => false
+__device__ __forceinline__ bool equalrotaniso_dev(const double* roti, const double* rotj,
+                                                  double anisoi, double anisoj, double bthr,
+                                                  double bthrmax, double bthrshift) {
+  const double av = __ddiv_rn(__dadd_rn(anisoi, anisoj), 2.0);
+  const double thr = bthrerf_dev(bthr, av, bthrmax, bthrshift);
+  const bool r1 = fabs(__dsub_rn(__ddiv_rn(roti[0], rotj[0]), 1.0)) <= thr;
+  const bool r2 = fabs(__dsub_rn(__ddiv_rn(roti[1], rotj[1]), 1.0)) <= thr;
+  const bool r3 = fabs(__dsub_rn(__ddiv_rn(roti[2], rotj[2]), 1.0)) <= thr;
+  return r1 && r2 && r3;
+}
+
+}  // namespace crest

@@ -1,0 +1,141 @@
+/* crest_cuda.h — C ABI of the B200-native CREGEN duplicate / rotamer sorting path.
+ *
+ * Drop-in boundary: the replacement sits INSIDE the reference's
+ *   cregen_CRE            /root/reference/src/cregen.f90:1125-1506
+ * taking over K0-K4 (lines 1222-1376: axis, pair RMSD loops, duplicate sweep) and K5-K6
+ * (lines 1421-1469: enuc, rotamer grouping).  Everything crossing the boundary is a plain
+ * pointer or scalar so that Fortran can bind it with iso_c_binding exactly the way the reference
+ * binds its own C code (src/symmetry2.f90:23-39 -> src/symmetry_i.c:1767).
+ *
+ * Conventions
+ *   - arrays are caller-owned, column-major as Fortran passes them: xyz(3,nat,nall) in Angstrom
+ *   - indices stored in dup[] / group[] are 1-based, 0 = "none" (as the reference's double()/group())
+ *   - energies er[] in Hartree, ASCENDING (the post-condition of cregen_esort, cregen.f90:1038-1121)
+ *   - every function returns 0 on success, non-zero on error; text via crest_cuda_last_error()
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails
+ *   - not re-entrant: call from one host thread (the reference calls from its serial region)
+ */
+#ifndef CREST_CUDA_H
+#define CREST_CUDA_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct crest_cuda_ctx crest_cuda_ctx;
+
+/* ---- thresholds of type(systemdata) that cross the boundary (src/classes.f90:332-345) ---- */
+typedef struct crest_cuda_thresholds {
+  double ethr;      /* env%ethr   kcal/mol, energy gate (cregen.f90:1275,1356,1444) */
+  double rthr;      /* env%rthr   Angstrom, RMSD threshold (cregen.f90:1364,1367)   */
+  double bthr;      /* env%bthr2  rot.-const. threshold (cregen.f90:1368 uses 0.5*bthr, 1446 bthr) */
+  double bthrmax;   /* env%bthrmax   (rotcompare.f90:127-142) */
+  double bthrshift; /* env%bthrshift (rotcompare.f90:127-142) */
+} crest_cuda_thresholds;
+
+/* ------------------------------------------------------------------------------------------
+ * One-call entry points (what the Fortran shim binds; 1 GPU = the current device)
+ * ------------------------------------------------------------------------------------------ */
+
+/* Replaces cregen.f90:1222-1376 (K0 axis + rot, K1-K3 pair RMSD incl. mirror, K4 sweep+backtrack).
+ *   at(nat)            atomic numbers
+ *   xyz(3,nat,nall)    input geometries (not modified)
+ *   er(nall)           energies, ascending
+ *   rmsd_mask(nat)     >0 = atom enters the RMSD (cregen.f90:1293-1299 heavy mask / includeRMSD);
+ *                      NULL = all atoms
+ *   rot_from_mask      != 0: rot. constants from the masked sub-structure (substruc,
+ *                      cregen.f90:1225-1230); 0: from all atoms
+ *   enantio            != 0: also compare the mirror image, keep the minimum (cregen.f90:1279-1284)
+ * outputs
+ *   rot(3,nall)        rot. constants in MHz (axis_module.f90:96-176)
+ *   xyz_axis(3,nat,nall) geometries shifted to CMA and rotated into the principal-axis frame
+ *                      (what axis() leaves in xyz, cregen.f90:1224); may be NULL
+ *   dup(nall)          double(i) after backtrack: 0 = kept, else 1-based root it duplicates
+ *   npairs             number of (i,j) pairs that passed the energy gate (= klong); may be NULL
+ */
+int crest_cuda_cregen_dup(int nat, int nall, const int* at, const double* xyz, const double* er,
+                          const int* rmsd_mask, int rot_from_mask, int enantio,
+                          const crest_cuda_thresholds* thr, double* rot, double* xyz_axis,
+                          int* dup, long long* npairs);
+
+/* Replaces cregen.f90:1421-1469 (K5 enuc, K6 greedy rotamer grouping, group ids) on the kept,
+ * already partitioned ensemble.  group(0:nkept): group[0] = number of groups. enuc may be NULL. */
+int crest_cuda_cregen_group(int nat, int nkept, const int* at, const double* xyz,
+                            const double* er, const double* rot,
+                            const crest_cuda_thresholds* thr, int* group, double* enuc);
+
+/* Whole cregen_CRE (cregen.f90:1195-1474) in one call, incl. the kept-first partition
+ * (cregen.f90:1397-1419).  xyz is rotated AND permuted in place, er permuted in place.
+ *   order(nall)  out: new 1-based position of input structure i (orderref); comments are permuted
+ *                by the Fortran caller with it (character data never crosses the boundary)
+ *   nallout      out: number of structures the caller keeps (cregen.f90:1393-1394,1470-1474)
+ *   nosort       cregen.f90:1133 flag */
+int crest_cuda_cregen_cre(int nat, int nall, const int* at, double* xyz, double* er,
+                          const int* rmsd_mask, int rot_from_mask, int enantio, int nosort,
+                          const crest_cuda_thresholds* thr, double* rot, int* order, int* group,
+                          int* nallout, long long* npairs);
+
+/* Diagnostics / parity: RMSD (ls_rmsd.f90:72-174, option 0) of explicit pairs of structures,
+ * proper and mirror (x of the second structure negated, cregen.f90:1280).  packed(3,A,n).
+ * i_idx/j_idx 0-based. */
+int crest_cuda_rmsd_pairs(int A, int n, const double* packed, long long npairs, const int* i_idx,
+                          const int* j_idx, double* rmsd, double* rmsd_mirror);
+
+/* Rot. constants only: axis(nat,at,coord,rot,avmom) = axis_1 -> axis_0 (axis_module.f90:96-176). */
+int crest_cuda_rotconst(int nat, int n, const int* at, const double* xyz, double* rot);
+
+/* All-pairs float32 RMSD band exactly as the reference's rmat (cregen.f90:1260-1349): row i holds
+ * j = 0..i-1 at offset i*(i-1)/2 (ethr = infinity layout).  For tests on small ensembles. */
+int crest_cuda_rmat_allpairs(int nat, int nall, const int* at, const double* xyz,
+                             const int* rmsd_mask, int enantio, float* rmat);
+
+/* ------------------------------------------------------------------------------------------
+ * Context API: device-resident ensemble, explicit stream, tile-space sharding for multi-GPU.
+ * One process per GPU; the caller owns the collective (NCCL all-reduce MAX on the dup buffer).
+ * ------------------------------------------------------------------------------------------ */
+int crest_cuda_ctx_create(crest_cuda_ctx** ctx, int device /* -1 = current */);
+void crest_cuda_ctx_destroy(crest_cuda_ctx* ctx);
+
+/* Copy the ensemble host->device (pinned staging) and keep it resident. Does not launch math. */
+int crest_cuda_ctx_upload(crest_cuda_ctx* ctx, int nat, int nall, const int* at,
+                          const double* xyz, const double* er, const int* rmsd_mask,
+                          int rot_from_mask);
+
+/* K0 on the device-resident ensemble: CMA shift, principal axes, rot, aniso, pack (kernel 1). */
+int crest_cuda_ctx_pack(crest_cuda_ctx* ctx, void* stream);
+
+/* Kernels (2)+(3): pair tiles of shard `rank` of `nranks` (contiguous slice of the in-band tile
+ * list).  Accumulates into the context's device dup buffer with max (zeroed by ctx_pack).
+ * want_mask != 0 additionally writes the packed 8x8-tile duplicate bitmask. */
+int crest_cuda_ctx_pairs(crest_cuda_ctx* ctx, int enantio, const crest_cuda_thresholds* thr,
+                         int rank, int nranks, int want_mask, void* stream);
+
+/* Device pointer (int32[nall], 1-based parents, 0 = none) for the caller's all-reduce(MAX). */
+void* crest_cuda_ctx_dup_devptr(crest_cuda_ctx* ctx);
+/* Device pointer of the pair counter (int64[1]) for the caller's all-reduce(SUM). */
+void* crest_cuda_ctx_npairs_devptr(crest_cuda_ctx* ctx);
+
+/* Kernel (4): backtrack (root chase) on the device dup buffer. */
+int crest_cuda_ctx_sweep(crest_cuda_ctx* ctx, void* stream);
+
+/* Results device->host. Any pointer may be NULL. Synchronises the stream. */
+int crest_cuda_ctx_download(crest_cuda_ctx* ctx, double* rot, double* xyz_axis, int* dup,
+                            long long* npairs, void* stream);
+
+/* Geometry of the launch that ctx_pairs would do (for bench/roofline bookkeeping):
+ * info[0]=tiles in shard, [1]=tiles total, [2]=atoms in RMSD (A), [3]=padded atoms used by MMA,
+ * [4]=grid, [5]=dynamic smem bytes, [6]=kernels launched by the last ctx_* call sequence. */
+int crest_cuda_ctx_info(crest_cuda_ctx* ctx, const crest_cuda_thresholds* thr, int rank,
+                        int nranks, long long* info);
+
+/* Copy of the device duplicate bitmask written by ctx_pairs(want_mask=1): n8*n8 64-bit words with
+ * n8 = ceil(nall/8); bit r*8+c of word (ti,tj) = pair (i=8*ti+r, j=8*tj+c) is a duplicate link. */
+int crest_cuda_ctx_download_mask(crest_cuda_ctx* ctx, unsigned long long* mask, void* stream);
+
+const char* crest_cuda_last_error(void);
+int crest_cuda_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CREST_CUDA_H */
