@@ -1,0 +1,340 @@
+#!/usr/bin/env python
+"""bench.py — RMSD pairs/s of the CREGEN duplicate-sorting hot path on N B200s.
+
+A step = one pass of the hot path over the whole synthetic ensemble, inputs resident in HBM:
+  kernel (1) pack/axis  ->  kernels (2)+(3) pair tiles of this rank's shard of the in-band tile
+  list  ->  all-reduce(MAX) of dup[] over ranks (NCCL, N>1 only)  ->  kernel (4) backtrack.
+`value` = pairs whose (proper+mirror) RMSD was evaluated by ALL ranks / device time (max over
+ranks).  `e2e` runs the same step from HOST buffers (H2D of xyz/er, D2H of rot/dup) every step.
+`--impl reference` times the CPU restatement of the reference loops (oracle/, OpenMP, all host
+cores) on a bounded row sample of the same workload; the reference itself is Fortran and cannot be
+built in this image.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "rmsd_pairs_per_sec"
+UNIT = "pairs/s"
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--workload", default="C3", choices=["C1", "C2", "C3", "C4", "C5"])
+    p.add_argument("--nall", type=int, default=None, help="override conformer count (debug)")
+    p.add_argument("--ethr", type=float, default=1e9, help="kcal/mol; 1e9 = all pairs")
+    p.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU-baseline sample time")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-e2e", action="store_true")
+    return p.parse_args()
+
+
+def workload_config(args, ens):
+    nall, nat, _ = ens["xyz"].shape
+    A = int((ens["at"] != 1).sum()) if ens["heavy"] else nat
+    return {
+        "workload": f"{args.workload}: {nall} conformers x {nat} atoms, RMSD over {A} "
+                    f"{'heavy ' if ens['heavy'] else ''}atoms, enantiomer check on, "
+                    f"{'all pairs (ethr=inf)' if args.ethr > 1e8 else f'ethr={args.ethr} kcal/mol'}",
+        "conformers": nall, "atoms": nat, "rmsd_atoms": A, "ethr_kcal": args.ethr,
+        "rthr": 0.125, "bthr": 0.01, "seed": 20261104,
+        "l2": "inputs (xyz + packed X + xyz_axis) exceed the 126 MB L2"
+              if nall * nat * 24 * 3 > 130e6 else "L2 flushed between timed steps",
+    }
+
+
+class ClockSampler:
+    """nvidia-smi clock / throttle sampling during the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, reasons, mx = [], set(), None
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx = float(parts[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        self.f.close()
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        if sm:
+            out["sm_mhz"] = float(np.median(sm))
+            out["sm_max_mhz"] = mx
+            out["samples"] = len(sm)
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def cpu_sample(ens, args, seconds):
+    """Time the oracle's reference-shaped pair loop (serial i, OpenMP j, two rmsd() per pair,
+    float32 store; oracle/oracle_capi.cpp: oracle_pair_rows <- reference src/cregen.f90:1269-1322)
+    on the LAST rows of the ensemble (rows are longest there, as in the real run's tail)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    xyz, er, at = ens["xyz"], ens["er"], ens["at"]
+    if ens["heavy"]:
+        xyz = np.ascontiguousarray(xyz[:, at != 1, :])
+    nall = xyz.shape[0]
+    cores = O.num_threads()
+    # calibrate on a few rows, then size the sample for ~`seconds`
+    r0 = max(1, min(8, nall - 1))
+    t0 = time.perf_counter()
+    n0, _ = O.pair_rows(xyz, er, nall - r0, nall, ethr=args.ethr, want=False)
+    dt0 = max(time.perf_counter() - t0, 1e-6)
+    rate0 = n0 / dt0
+    rows = int(min(nall - 1, max(r0, seconds * rate0 / max(nall, 1))))
+    t0 = time.perf_counter()
+    n1, _ = O.pair_rows(xyz, er, nall - rows, nall, ethr=args.ethr, want=False)
+    dt = time.perf_counter() - t0
+    return {"value": n1 / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"last {rows} rows of the pair triangle = {n1} pairs in {dt:.2f} s "
+                      f"(oracle/ C++ restatement of cregen.f90:1269-1322 + ls_rmsd.f90, OpenMP)",
+            "pairs": int(n1), "seconds": dt}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from crest_b200 import synth
+    ens = synth.make_config(args.workload, nall=args.nall)
+    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        cpu_sample(ens, args, per_step)
+    tot_pairs, tot_s, last = 0, 0.0, None
+    for _ in range(args.steps):
+        last = cpu_sample(ens, args, per_step)
+        tot_pairs += last["pairs"]
+        tot_s += last["seconds"]
+    val = tot_pairs / tot_s
+    cb = dict(last)
+    cb["value"] = val
+    cb.pop("pairs"), cb.pop("seconds")
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_s / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": workload_config(args, ens), "cpu_baseline": cb,
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+class _DevArray:
+    """Expose a raw device pointer to torch through __cuda_array_interface__ (no copy)."""
+
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False),
+                                         "version": 2}
+
+
+def fp64_peak_tflops(torch, dev):
+    """FP64 tensor roofline denominator: cuBLAS DGEMM 6144^3, best of 5 (MEASURED_PEAKS.json holds
+    only HBM and bf16 figures; an isolated run gave 35.5 TFLOP/s, profiles/r01_dgemm_peak.txt)."""
+    n = 6144
+    a = torch.randn(n, n, dtype=torch.float64, device=dev)
+    b = torch.randn(n, n, dtype=torch.float64, device=dev)
+    for _ in range(2):
+        a @ b
+    torch.cuda.synchronize()
+    best = 1e30
+    for _ in range(5):
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        a @ b
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    del a, b
+    return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import crest_b200 as cb
+    from crest_b200 import synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    ens = synth.make_config(args.workload, nall=args.nall)
+    at, xyz, er = ens["at"], ens["xyz"], ens["er"]
+    nall, nat, _ = xyz.shape
+    env = cb.Env(ethr=args.ethr, heavyrmsd=ens["heavy"])
+    ctx = cb.CregenContext(local)
+    ctx.upload(env, at, xyz, er)
+    stream = torch.cuda.current_stream().cuda_stream
+    dup_t = torch.as_tensor(_DevArray(ctx.dup_devptr(), nall, "<i4"), device=dev)
+    np_t = torch.as_tensor(_DevArray(ctx.npairs_devptr(), 1, "<i8"), device=dev)
+    flush = None
+    if nall * nat * 24 * 3 <= 130e6:
+        flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+
+    def step(ev=None):
+        if flush is not None:
+            flush.fill_(1)
+        ctx.pack(stream)
+        if ev:
+            ev[0].record()
+        ctx.pairs(env, rank, world, False, stream)
+        if ev:
+            ev[1].record()
+        if world > 1:
+            dist.all_reduce(dup_t, op=dist.ReduceOp.MAX)
+        ctx.sweep(stream)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    sync_all()
+    sampler = ClockSampler(local) if rank == 0 else None
+    t_beg = torch.cuda.Event(enable_timing=True)
+    t_end = torch.cuda.Event(enable_timing=True)
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+           for _ in range(args.steps)]
+    t_beg.record()
+    for s in range(args.steps):
+        step(kev[s])
+    t_end.record()
+    sync_all()
+    clocks = sampler.stop() if sampler else None
+    ms_total = t_beg.elapsed_time(t_end)
+    pair_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
+    # pairs evaluated in the last step (device counter is zeroed by pack), summed over ranks
+    if world > 1:
+        npl = np_t.clone()
+        dist.all_reduce(npl, op=dist.ReduceOp.SUM)
+        pairs_step = int(npl.item())
+        tt = torch.tensor([ms_total, pair_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total, pair_ms = float(tt[0]), float(tt[1])
+    else:
+        pairs_step = int(np_t.item())
+    my_pairs = int(np_t.item())
+    info = ctx.info(env, rank, world)
+    res = ctx.download()
+    ms_step = ms_total / args.steps
+    value = pairs_step / (ms_step * 1e-3)
+
+    # ---- end to end from host buffers through the context API (H2D + D2H inside the timed region)
+    e2e = None
+    if not args.no_e2e:
+        xyz_p = torch.from_numpy(xyz).pin_memory().numpy()
+        er_p = torch.from_numpy(er).pin_memory().numpy()
+
+        def e2e_step():
+            ctx.upload(env, at, xyz_p, er_p)
+            step()
+            return ctx.download()
+        e2e_step()
+        sync_all()
+        t0 = time.perf_counter()
+        n_e2e = max(1, min(args.steps, 3))
+        for _ in range(n_e2e):
+            r2 = e2e_step()
+        sync_all()
+        dt = (time.perf_counter() - t0) / n_e2e
+        if world > 1:
+            tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dt = float(tt[0])
+        e2e = {"value": pairs_step / dt, "unit": UNIT,
+               "h2d_bytes_per_step": int(xyz.nbytes + er.nbytes + at.nbytes),
+               "d2h_bytes_per_step": int(nall * 4 + nall * 24 + 8), "ms_per_step": dt * 1e3,
+               "api": "CregenContext.upload+pack+pairs+sweep+download (crest_cuda_ctx_*), host buffers"}
+        assert np.array_equal(r2["dup"], res["dup"])
+
+    if rank == 0:
+        A = info["A"]
+        peak = fp64_peak_tflops(torch, dev)
+        achieved = 18.0 * A * my_pairs / (pair_ms * 1e-3) / 1e12
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args, ens),
+            "pairs_per_step": pairs_step, "duplicates_found": int((res["dup"] != 0).sum()),
+            "gpu_launches": int(3 * args.steps),
+            "kernels": {"pair_tile_ms": pair_ms, "grid": info["grid"], "smem": info["smem"],
+                        "tiles_this_rank": info["tiles_shard"], "atoms_padded": info["A_padded"]},
+            "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                         "frac": achieved / peak, "traffic": None,
+                         "note": "FP64 tensor (DMMA) roofline: 18*A FLOP per pair x pairs of rank 0 "
+                                 "/ pair_tile kernel time (CUDA events); peak = cuBLAS DGEMM 6144^3 "
+                                 "measured in this run (MEASURED_PEAKS.json has no FP64 figure)"},
+            "clocks": clocks, "e2e": e2e,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            cbase = cpu_sample(ens, args, args.cpu_seconds)
+            cbase.pop("pairs"), cbase.pop("seconds")
+            line["cpu_baseline"] = cbase
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
