@@ -49,6 +49,10 @@ SYMBOLS = {
     "crest_cuda_ctx_download": (C.c_int, [C.c_void_p, c_dp, c_dp, c_ip, c_llp, C.c_void_p]),
     "crest_cuda_ctx_info": (C.c_int, [C.c_void_p, _THR, C.c_int, C.c_int, c_llp]),
     "crest_cuda_ctx_download_mask": (C.c_int, [C.c_void_p, c_ullp, C.c_void_p]),
+    "crest_cuda_e_threshold": (C.c_double, [C.c_double, C.c_int]),
+    "crest_cuda_tile_shape": (None, [c_ip, c_ip]),
+    "crest_cuda_band_tiles": (C.c_int, [C.c_int, c_dp, C.c_double, c_llp, c_ip, c_llp]),
+    "crest_cuda_shard_range": (C.c_int, [C.c_longlong, C.c_int, C.c_int, c_llp, c_llp]),
     "crest_cuda_last_error": (C.c_char_p, []),
     "crest_cuda_device_count": (C.c_int, []),
 }

@@ -57,6 +57,49 @@ def rmsd_mask(env: Env, nat: int, at: np.ndarray):
     return None, 0
 
 
+def _tile_shape():
+    ti, tj = C.c_int(0), C.c_int(0)
+    _lib.lib().crest_cuda_tile_shape(C.byref(ti), C.byref(tj))
+    return ti.value, tj.value
+
+
+def __getattr__(name):            # module-level lazy constants
+    if name == "TILE_I":
+        return _tile_shape()[0]
+    if name == "TILE_J":
+        return _tile_shape()[1]
+    raise AttributeError(name)
+
+
+def band_tiles(er, ethr):
+    """Host-only: the in-band tile list (i-tile, j-tile arrays, rowstart, jfirst) for ascending
+    energies er (Eh) and gate ethr (kcal/mol) — reference band cregen.f90:1240-1256 in tiles."""
+    L = _lib.lib()
+    er = np.ascontiguousarray(er, np.float64)
+    n = len(er)
+    ti_, _ = _tile_shape()
+    nI = (n + ti_ - 1) // ti_
+    rowstart = np.zeros(nI + 1, np.int64)
+    jfirst = np.zeros(max(nI, 1), np.int32)
+    nt = C.c_longlong(0)
+    _lib.check(L.crest_cuda_band_tiles(n, _dp(er), float(ethr), rowstart.ctypes.data_as(c_llp),
+                                       _ip(jfirst), C.byref(nt)))
+    ti, tj = [], []
+    for I in range(nI):
+        cnt = int(rowstart[I + 1] - rowstart[I])
+        ti += [I] * cnt
+        tj += list(range(int(jfirst[I]), int(jfirst[I]) + cnt))
+    assert len(ti) == nt.value
+    return np.array(ti, np.int64), np.array(tj, np.int64), rowstart, jfirst[:nI]
+
+
+def shard_range(ntiles, rank, nranks):
+    """Host-only: [begin, end) of the tile list owned by `rank` of `nranks`."""
+    b, e = C.c_longlong(0), C.c_longlong(0)
+    _lib.check(_lib.lib().crest_cuda_shard_range(ntiles, rank, nranks, C.byref(b), C.byref(e)))
+    return b.value, e.value
+
+
 @dataclass
 class CreResult:
     nallout: int

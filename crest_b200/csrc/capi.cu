@@ -96,19 +96,19 @@ namespace {
 
 // In-band tile list: for i-panel I the j-tiles [jfirst, jlast]; energies ascend, so the first
 // in-band j of the panel's first row bounds the whole panel (cregen.f90:1245-1255 rmap2).
-void build_tiles(crest_cuda_ctx* c, double ethr) {
-  const int n = c->nall;
+void band_tiles_host(int n, const double* er, double ethr, std::vector<long long>& rowstart,
+                     std::vector<int>& jfirst) {
   const int nI = (n + kTileI - 1) / kTileI;
-  c->rowstart.assign(nI + 1, 0);
-  c->jfirst.assign(nI > 0 ? nI : 1, 0);
-  const double* er = c->h_er.data();
+  rowstart.assign(nI + 1, 0);
+  jfirst.assign(nI > 0 ? nI : 1, 0);
   long long acc = 0;
   for (int I = 0; I < nI; ++I) {
-    c->rowstart[I] = acc;
+    rowstart[I] = acc;
     const int ifirst = I * kTileI;
     const int ilast = std::min(ifirst + kTileI - 1, n - 1);
     const int jmax = ilast - 1;
-    // first j in [0, ifirst] with (er[ifirst]-er[j])*autokcal < ethr ; predicate is monotone in j
+    // first j with (er[ifirst]-er[j])*autokcal < ethr (monotone in j).  de grows with i, so the
+    // panel's FIRST row admits the smallest j; the other rows are gated per pair in edge tiles.
     int lo = 0, hi = ifirst;   // answer in [0, ifirst]
     while (lo < hi) {
       const int mid = (lo + hi) / 2;
@@ -117,13 +117,17 @@ void build_tiles(crest_cuda_ctx* c, double ethr) {
     }
     const int jlo = lo;
     if (jmax >= 0 && jlo <= jmax) {
-      c->jfirst[I] = jlo / kTileJ;
-      acc += (long long)(jmax / kTileJ - c->jfirst[I] + 1);
+      jfirst[I] = jlo / kTileJ;
+      acc += (long long)(jmax / kTileJ - jfirst[I] + 1);
     } else {
-      c->jfirst[I] = 0;
+      jfirst[I] = 0;
     }
   }
-  c->rowstart[nI] = acc;
+  rowstart[nI] = acc;
+}
+
+void build_tiles(crest_cuda_ctx* c, double ethr) {
+  band_tiles_host(c->nall, c->h_er.data(), ethr, c->rowstart, c->jfirst);
   c->tiles_ethr = ethr;
 }
 
@@ -160,6 +164,35 @@ int crest_cuda_device_count(void) {
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
   return n;
+}
+
+// ---- host-only bookkeeping (no device needed; also what the CPU tests exercise) ----
+double crest_cuda_e_threshold(double thr, int n) { return e_threshold(thr, n > 0 ? n : 1); }
+
+void crest_cuda_tile_shape(int* tile_i, int* tile_j) {
+  if (tile_i) *tile_i = kTileI;
+  if (tile_j) *tile_j = kTileJ;
+}
+
+int crest_cuda_band_tiles(int nall, const double* er, double ethr, long long* rowstart,
+                          int* jfirst, long long* ntiles) {
+  if (nall < 0 || (!er && nall > 0)) { set_error("bad argument"); return 1; }
+  std::vector<long long> rs;
+  std::vector<int> jf;
+  band_tiles_host(nall, er, ethr, rs, jf);
+  const int nI = (nall + kTileI - 1) / kTileI;
+  if (rowstart) for (int i = 0; i <= nI; ++i) rowstart[i] = rs[i];
+  if (jfirst) for (int i = 0; i < nI; ++i) jfirst[i] = jf[i];
+  if (ntiles) *ntiles = rs[nI];
+  return 0;
+}
+
+int crest_cuda_shard_range(long long ntiles, int rank, int nranks, long long* begin,
+                           long long* end) {
+  if (nranks < 1 || rank < 0 || rank >= nranks || ntiles < 0) { set_error("bad shard"); return 1; }
+  if (begin) *begin = ntiles * rank / nranks;
+  if (end) *end = ntiles * (rank + 1) / nranks;
+  return 0;
 }
 
 int crest_cuda_ctx_create(crest_cuda_ctx** out, int device) {
@@ -285,8 +318,7 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
   a.X = c->d_X; a.xn = c->d_xn; a.er = c->d_er; a.rot = c->d_rot; a.aniso = c->d_aniso;
   a.rowstart = c->d_rowstart; a.jfirst = c->d_jfirst;
   a.nI = (int)c->jfirst.size(); a.nall = c->nall;
-  a.tile_begin = T * rank / nranks;
-  a.tile_end = T * (rank + 1) / nranks;
+  crest_cuda_shard_range(T, rank, nranks, &a.tile_begin, &a.tile_end);
   a.dup = c->d_dup; a.npairs = c->d_npairs;
   a.mask = nullptr; a.n8 = (c->nall + 7) / 8;
   if (want_mask) {
@@ -357,7 +389,9 @@ int crest_cuda_ctx_info(crest_cuda_ctx* c, const crest_cuda_thresholds* thr, int
     CREST_CUDA_TRY(cudaStreamSynchronize(0));
   }
   const long long T = c->rowstart.empty() ? 0 : c->rowstart.back();
-  info[0] = T * (rank + 1) / nranks - T * rank / nranks;
+  long long tb = 0, te = 0;
+  crest_cuda_shard_range(T, rank, nranks, &tb, &te);
+  info[0] = te - tb;
   info[1] = T;
   info[2] = c->nsel;
   info[3] = (long long)c->L.nslab * c->L.KU;

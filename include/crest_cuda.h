@@ -132,6 +132,22 @@ int crest_cuda_ctx_info(crest_cuda_ctx* ctx, const crest_cuda_thresholds* thr, i
  * n8 = ceil(nall/8); bit r*8+c of word (ti,tj) = pair (i=8*ti+r, j=8*tj+c) is a duplicate link. */
 int crest_cuda_ctx_download_mask(crest_cuda_ctx* ctx, unsigned long long* mask, void* stream);
 
+/* ---- host-only bookkeeping: no device is touched (used by the multi-rank driver and tests) ----
+ * e_threshold: the double E with  e < E  <=>  real(sqrt(max(0,e)/n),sp) < thr, i.e. the
+ *   reference's test of the float32-stored RMSD against rthr / 2*rthr (cregen.f90:1176,1286,
+ *   1359-1367) moved onto e = |x|^2+|y|^2-2*lambda so the kernel needs no sqrt/div per pair.
+ * band_tiles: in-band tile list of the pair triangle for ascending energies (the reference's
+ *   rmap1/rmap2 band, cregen.f90:1240-1256, at tile granularity): i-panel I owns the j-tiles
+ *   jfirst[I] .. jfirst[I]+(rowstart[I+1]-rowstart[I])-1.  rowstart has ceil(nall/tile_i)+1
+ *   entries, jfirst ceil(nall/tile_i).
+ * shard_range: the contiguous slice [begin,end) of the tile list that `rank` of `nranks` owns. */
+double crest_cuda_e_threshold(double thr, int n);
+void crest_cuda_tile_shape(int* tile_i, int* tile_j);
+int crest_cuda_band_tiles(int nall, const double* er, double ethr, long long* rowstart,
+                          int* jfirst, long long* ntiles);
+int crest_cuda_shard_range(long long ntiles, int rank, int nranks, long long* begin,
+                           long long* end);
+
 const char* crest_cuda_last_error(void);
 int crest_cuda_device_count(void);
 

@@ -1,0 +1,102 @@
+"""CPU-side checks of the C-ABI library (no compute call needs a GPU here):
+every symbol include/crest_cuda.h declares is exported, the ctypes table matches the header, and
+compute entry points FAIL LOUDLY without a device (there is no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, has_gpu
+
+
+def header_symbols():
+    txt = open(os.path.join(ROOT, "include", "crest_cuda.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(crest_cuda_[a-z0-9_]+)\s*\(", txt)))
+
+
+def test_header_symbols_exported(cuda_lib):
+    syms = header_symbols()
+    assert len(syms) >= 19
+    for s in syms:
+        assert hasattr(cuda_lib, s), f"{s} declared in include/crest_cuda.h but not exported"
+
+
+def test_ctypes_table_covers_header():
+    from crest_b200 import _lib
+    assert sorted(_lib.SYMBOLS) == header_symbols()
+
+
+def test_thresholds_struct_layout():
+    from crest_b200 import _lib
+    assert C.sizeof(_lib.Thresholds) == 5 * 8
+    t = _lib.Thresholds()
+    # defaults of the reference: src/confparse.f90:162-170
+    assert (t.ethr, t.rthr, t.bthr, t.bthrmax, t.bthrshift) == (0.05, 0.125, 0.01, 0.025, 0.5)
+
+
+@pytest.mark.skipif(has_gpu(), reason="checks the no-device behaviour")
+def test_no_cpu_fallback(cuda_lib):
+    import crest_b200 as cb
+    assert cuda_lib.crest_cuda_device_count() == 0
+    at = np.array([6, 1, 1], np.int32)
+    xyz = np.zeros((2, 3, 3))
+    with pytest.raises(cb.CrestCudaError):
+        cb.cregen_dup(cb.Env(), 3, 2, at, xyz, np.zeros(2))
+    with pytest.raises(cb.CrestCudaError):
+        cb.rotconst(at, xyz)
+    with pytest.raises(cb.CrestCudaError):
+        cb.CregenContext()
+    assert b"CUDA" in cuda_lib.crest_cuda_last_error() or b"cuda" in cuda_lib.crest_cuda_last_error()
+
+
+def test_host_e_threshold_matches_float32_rule(cuda_lib):
+    """crest_cuda_e_threshold (host-only): e < E  <=>  real(sqrt(max(0,e)/n),sp) < thr, the
+    reference's comparison of the float32-stored RMSD (cregen.f90:1176,1286,1359-1367)."""
+    f = cuda_lib.crest_cuda_e_threshold
+    rng = np.random.default_rng(0)
+    for thr in (0.125, 0.25, 0.1, 0.2, 0.3333, 1e-3):
+        for n in (3, 12, 46, 60, 300):
+            E = f(thr, n)
+            assert E > 0
+            # neighbours of E in double precision sit on either side of the float32 decision
+            lo = np.nextafter(E, 0.0)
+            assert float(np.float32(np.sqrt(lo / n))) < thr
+            assert not (float(np.float32(np.sqrt(E / n))) < thr)
+            for e in np.concatenate([E * (1 + rng.normal(0, 1e-7, 200)), rng.uniform(0, 2 * E, 200)]):
+                assert (e < E) == (float(np.float32(np.sqrt(max(0.0, e) / n))) < thr)
+    assert f(0.0, 10) == -np.inf
+
+
+def test_host_band_tiles(cuda_lib):
+    """crest_cuda_band_tiles (host-only): the in-band tile list covers every pair that passes the
+    reference's energy gate (cregen.f90:1245-1255) exactly once, and shards partition it."""
+    from crest_b200 import cregen as cg
+    rng = np.random.default_rng(1)
+    for n, ethr in ((1, 1.0), (2, 1e9), (33, 0.05), (257, 0.3), (700, 1e9), (700, 0.02)):
+        er = np.sort(rng.uniform(0, 6.0, n)) / 627.50947428 - 50.0
+        ti, tj, rowstart, jfirst = cg.band_tiles(er, ethr)
+        TI, TJ = cg.TILE_I, cg.TILE_J
+        cover = np.zeros((n, n), np.int32)
+        for a, b in zip(ti, tj):
+            cover[a * TI:(a + 1) * TI, b * TJ:(b + 1) * TJ] += 1
+        i, j = np.tril_indices(n, -1)
+        gate = (er[i] - er[j]) * 627.50947428 < ethr
+        assert np.all(cover[i[gate], j[gate]] == 1)
+        assert cover.max() <= 1
+        T = len(ti)
+        for world in (1, 2, 3, 8):
+            parts = [cg.shard_range(T, r, world) for r in range(world)]
+            assert parts[0][0] == 0 and parts[-1][1] == T
+            assert all(parts[k][1] == parts[k + 1][0] for k in range(world - 1))
+            sizes = [e - b for b, e in parts]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_argument_checks(cuda_lib):
+    # NULL thresholds / bad sizes are rejected before any device work
+    rc = cuda_lib.crest_cuda_cregen_dup(3, 2, None, None, None, None, 0, 1, None, None, None, None,
+                                        None)
+    assert rc != 0 and len(cuda_lib.crest_cuda_last_error()) > 0
