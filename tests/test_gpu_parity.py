@@ -58,6 +58,23 @@ def boundary_rows(rmat_rows, rthr):
     return out
 
 
+def check_axis_frame(got, ref, rot_ref):
+    """Principal-axis coordinates agree to 1e-8 A; for (near-)symmetric tops the in-plane axes are
+    mathematically arbitrary (degenerate inertia eigenvalues: any rounding difference rotates
+    them), so there the frames must agree up to a proper rotation instead."""
+    for k in range(len(got)):
+        if np.abs(got[k] - ref[k]).max() < 1e-8:
+            continue
+        r = np.sort(rot_ref[k])
+        degenerate = (r[0] == 0) or min(abs(r[1] / r[0] - 1), abs(r[2] / r[1] - 1)) < 1e-5
+        assert degenerate, (k, np.abs(got[k] - ref[k]).max())
+        H = got[k].T @ ref[k]
+        U, S, Vt = np.linalg.svd(H)
+        assert np.linalg.det(U @ Vt) > 0                       # same handedness
+        e = (got[k] ** 2).sum() + (ref[k] ** 2).sum() - 2 * S.sum()
+        assert e / len(got[k]) < 1e-14, (k, e)
+
+
 def rows_of_allpairs(rmat, n):
     return {i: rmat[i * (i - 1) // 2: i * (i - 1) // 2 + i] for i in range(1, n)}
 
@@ -84,7 +101,7 @@ def test_golden(cb, path):
     assert np.abs(a["rot"][ok] / rot_ref[ok] - 1).max() < ROT_TOL
     xa_ref = np.empty_like(g["xyz_out"])
     xa_ref[inv] = g["xyz_out"]
-    assert np.abs(a["xyz_axis"] - xa_ref).max() < 1e-8
+    check_axis_frame(a["xyz_axis"], xa_ref, rot_ref)
     listed = set()
     all_pairs = kw.get("ethr", 0.05) > 1e8
     if all_pairs and "rmat" in g.files:
@@ -103,7 +120,7 @@ def test_golden(cb, path):
     assert np.array_equal(r.order, g["orderref"])
     assert np.array_equal(r.group, g["group"])
     assert np.array_equal(r.er, g["er_out"])
-    assert np.abs(r.xyz - g["xyz_out"]).max() < 1e-8
+    check_axis_frame(r.xyz, g["xyz_out"], g["rot"])
 
 
 def test_pairs_kat(cb):
