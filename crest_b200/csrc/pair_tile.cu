@@ -190,10 +190,22 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
     if (!active) continue;
 
     // ------------------------------ fused epilogue ------------------------------
+    // Pass 1 (branch-free, 8 independent pairs per lane): quartic invariants of each 3x3 R and
+    // the sign screen at lambda* = (s - E2)/2.  Pass 2 (rare): exact Newton/Jacobi solve only for
+    // pairs the screen could not prove to lie beyond 2*rthr.
     // energy gate can only fail in tiles on the band edge: max de sits at (largest i, smallest j)
     const int ti_last = min(I * kTileI + kTileI - 1, a.nall - 1);
     const bool edge =
         !(__dmul_rn(__dsub_rn(a.er[ti_last], a.er[J * kTileJ]), kAutokcal) < a.g.ethr);
+    double xnj[2][2];
+#pragma unroll
+    for (int nj = 0; nj < 2; ++nj)
+#pragma unroll
+      for (int p = 0; p < 2; ++p) {
+        const int j = j0 + nj * 8 + 2 * tq + p;
+        xnj[nj][p] = (j < a.nall) ? a.xn[j] : 0.0;
+      }
+    unsigned cand = 0;
 #pragma unroll
     for (int mi = 0; mi < 2; ++mi) {
       const int i = i0 + mi * 8 + c;
@@ -201,21 +213,41 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
       const double xni = iok ? a.xn[i] : 0.0;
       const double eri = (edge && iok) ? a.er[i] : 0.0;
 #pragma unroll
+      for (int nj = 0; nj < 2; ++nj)
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+          const int j = j0 + nj * 8 + 2 * tq + p;
+          bool ok = iok && (j < i);
+          if (edge && ok) ok = __dmul_rn(__dsub_rn(eri, a.er[j]), kAutokcal) < a.g.ethr;
+          double r[9];
+#pragma unroll
+          for (int z = 0; z < 9; ++z) r[z] = acc[mi][nj][z][p];
+          const Quartic q = quartic_of(r);
+          const double s = xni + xnj[nj][p];
+          const double c1 = a.g.enantio ? -q.c1abs : -8.0 * q.det;
+          const bool far = screen_far(q, c1, s, fma(1e-8, s, a.g.E2));
+          my_pairs += ok;
+          if (ok && (!far || a.rmat)) cand |= 1u << (mi * 4 + nj * 2 + p);
+        }
+    }
+    if (!a.mask && !__any_sync(0xffffffffu, cand != 0)) continue;
+#pragma unroll
+    for (int mi = 0; mi < 2; ++mi) {
+      const int i = i0 + mi * 8 + c;
+      const double xni = (i < a.nall) ? a.xn[i] : 0.0;
+#pragma unroll
       for (int nj = 0; nj < 2; ++nj) {
         unsigned hit[2] = {0u, 0u};
 #pragma unroll
         for (int p = 0; p < 2; ++p) {
           const int j = j0 + nj * 8 + 2 * tq + p;
-          bool ok = iok && (j < i);
-          if (ok && edge) ok = __dmul_rn(__dsub_rn(eri, a.er[j]), kAutokcal) < a.g.ethr;
           bool dupl = false;
-          if (ok) {
-            ++my_pairs;
-            double r[9];
-#pragma unroll
-            for (int z = 0; z < 9; ++z) r[z] = acc[mi][nj][z][p];
-            const double s = xni + a.xn[j];
-            const double e = pair_e(r, s, a.g.enantio, 0);
+          if (cand & (1u << (mi * 4 + nj * 2 + p))) {
+            const double s = xni + xnj[nj][p];
+            const double e = pair_e_exact(acc[mi][nj][0][p], acc[mi][nj][1][p], acc[mi][nj][2][p],
+                                          acc[mi][nj][3][p], acc[mi][nj][4][p], acc[mi][nj][5][p],
+                                          acc[mi][nj][6][p], acc[mi][nj][7][p], acc[mi][nj][8][p],
+                                          s, a.g.enantio);
             if (a.rmat) {
               const double rr = sqrt(fmax(0.0, e) / (double)L.A);
               a.rmat[(size_t)i * (i - 1) / 2 + j] = (float)rr;

@@ -146,6 +146,38 @@ __device__ __forceinline__ double pair_e(const double* r, double s, int enantio,
   return fma(-2.0, lam, s);
 }
 
+// Out-of-line exact solve for the rare candidate pairs of the tile epilogue (keeps the hot loop's
+// instruction footprint small).
+static __device__ __noinline__ double pair_e_exact(double r0, double r1, double r2, double r3,
+                                                   double r4, double r5, double r6, double r7,
+                                                   double r8, double s, int enantio) {
+  const double r[9] = {r0, r1, r2, r3, r4, r5, r6, r7, r8};
+  return pair_e(r, s, enantio, 0);
+}
+
+// Branch-free screen: true  =>  PROVEN  e = s - 2*lambda_max > Ecut  (the pair cannot pass the
+// 2*rthr gate), false => undecided, run the exact solve.
+// With lam = (s - Ecut)/2 the claim is lambda_max < lam.  For a real-rooted quartic P (the
+// characteristic polynomial of a symmetric matrix) Budan-Fourier gives: P and its first, second
+// and third derivative all > 0 at lam  <=>  no root above lam.  Each sign is required with a
+// floor far above the rounding error of its evaluation (~1e-14 * scale), so a `true` is rigorous;
+// anything closer goes to the exact path, and the caller passes Ecut with a 1e-8*s margin over
+// the decision threshold so the screen never decides a pair whose exact-path result could round
+// to the other side.
+__device__ __forceinline__ bool screen_far(const Quartic& q, double c1, double s, double Ecut) {
+  const double lam = 0.5 * (s - Ecut);
+  const double l2 = lam * lam;
+  const double i1 = -0.5 * q.c2;
+  const double sc = fmax(l2, i1);              // scale^2
+  const double a = l2 + q.c2;                  // l^2 + c2
+  const double t = fma(a, lam, c1);            // l^3 + c2 l + c1
+  const double P = fma(t, lam, q.c0);
+  const double dP = fma(fma(4.0, l2, 2.0 * q.c2), lam, c1);
+  const double ddP = fma(6.0, l2, q.c2);       // second derivative / 2
+  const double fl = 1e-10 * sc;
+  return (lam > 0.0) & (P > fl * sc) & (dP > fl * lam) & (ddP > fl);
+}
+
 // reference src/rotcompare.f90:109-122 (same operation order)
 __device__ __forceinline__ double rotaniso_dev(double a, double b, double c) {
   const double av = __ddiv_rn(__dadd_rn(__dadd_rn(a, b), c), 3.0);
