@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcrest_cuda.so")
+LIB_PATH = os.environ.get("CREST_CUDA_LIB", os.path.join(_HERE, "libcrest_cuda.so"))
 _LIB = None
 
 c_dp = C.POINTER(C.c_double)

@@ -6,6 +6,7 @@
 #include "common.cuh"
 #include <cmath>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <vector>
@@ -55,6 +56,8 @@ static Gates make_gates(const crest_cuda_thresholds& t, int enantio, int A) {
   g.bthrmax = t.bthrmax;
   g.bthrshift = t.bthrshift;
   g.enantio = enantio ? 1 : 0;
+  const char* dbg = std::getenv("CREST_CUDA_DEBUG");
+  g.debug = dbg ? std::atoi(dbg) : 0;
   return g;
 }
 

@@ -53,6 +53,7 @@ struct Gates {
   double bthr_half;  // 0.5*bthr (cregen.f90:1368)
   double bthrmax, bthrshift;
   int enantio;
+  int debug;         // profiling switch (env CREST_CUDA_DEBUG): 1 = skip the epilogue (timing only)
 };
 
 }  // namespace crest

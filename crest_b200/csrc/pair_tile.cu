@@ -58,15 +58,30 @@ __device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b)
 
 constexpr int kMaxStages = 4;
 
-__device__ __forceinline__ void decode_tile(const PairArgs& a, long long t, int& I, int& J) {
-  int lo = 0, hi = a.nI - 1;           // largest I with rowstart[I] <= t
-  while (lo < hi) {
-    const int mid = (lo + hi + 1) >> 1;
-    if (a.rowstart[mid] <= t) lo = mid; else hi = mid - 1;
+// Tile index -> (i-panel I, j-tile J).  A CTA walks t = t0, t0+grid, ... : after one binary search
+// the row is advanced incrementally (a dependent-load search per tile costs ~5k clk of latency).
+struct TileCursor {
+  int I = -1;
+  long long row_beg = 0, row_end = 0;   // rowstart[I], rowstart[I+1]
+  int jf = 0;
+  __device__ __forceinline__ void seek(const PairArgs& a, long long t, int& Iout, int& Jout) {
+    if (I < 0) {
+      int lo = 0, hi = a.nI - 1;        // largest I with rowstart[I] <= t
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (a.rowstart[mid] <= t) lo = mid; else hi = mid - 1;
+      }
+      I = lo;
+      row_beg = a.rowstart[I]; row_end = a.rowstart[I + 1]; jf = a.jfirst[I];
+    }
+    while (t >= row_end) {              // also skips empty rows
+      ++I;
+      row_beg = row_end; row_end = a.rowstart[I + 1]; jf = a.jfirst[I];
+    }
+    Iout = I;
+    Jout = jf + (int)(t - row_beg);
   }
-  I = lo;
-  J = a.jfirst[lo] + (int)(t - a.rowstart[lo]);
-}
+};
 
 __global__ void __launch_bounds__(kPairThreads, 1)
 pair_tile_kernel(const PairArgs a, const int nstage) {
@@ -110,9 +125,10 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
   long long p_tile = a.tile_begin + blockIdx.x;
   int p_slab = 0, p_I = 0, p_J = 0;
   uint32_t p_it = 0;
+  TileCursor p_cur;
   auto produce_one = [&]() {
     if (p_tile >= a.tile_end) return;
-    if (p_slab == 0) decode_tile(a, p_tile, p_I, p_J);
+    if (p_slab == 0) p_cur.seek(a, p_tile, p_I, p_J);
     const int st = p_it % nstage;
     const uint32_t ph = (p_it / nstage) & 1;
     mbar_wait(&empty_bar[st], ph ^ 1);
@@ -132,9 +148,10 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
 
   unsigned long long my_pairs = 0;
   uint32_t it = 0;
+  TileCursor cur;
   for (long long t = a.tile_begin + blockIdx.x; t < a.tile_end; t += gridDim.x) {
     int I, J;
-    decode_tile(a, t, I, J);
+    cur.seek(a, t, I, J);
     const int i0 = I * kTileI + wi * 16;       // first i of this warp
     const int j0 = J * kTileJ + wj * 16;       // first j of this warp
     // warp-level activity: any pair with j < i, i < nall
@@ -187,7 +204,7 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty_bar[st]);
     }
-    if (!active) continue;
+    if (!active || a.g.debug == 1) continue;
 
     // ------------------------------ fused epilogue ------------------------------
     // Pass 1 (branch-free, 8 independent pairs per lane): quartic invariants of each 3x3 R and
@@ -198,12 +215,15 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
     const bool edge =
         !(__dmul_rn(__dsub_rn(a.er[ti_last], a.er[J * kTileJ]), kAutokcal) < a.g.ethr);
     double xnj[2][2];
+    float lam_j[2][2];          // 0.5*(xn_j*(1-2e-6) - E2) rounded down; + 0.5*xn_i*(1-2e-6) gives lam
+    const float e2_up = __double2float_ru(a.g.E2);
 #pragma unroll
     for (int nj = 0; nj < 2; ++nj)
 #pragma unroll
       for (int p = 0; p < 2; ++p) {
         const int j = j0 + nj * 8 + 2 * tq + p;
         xnj[nj][p] = (j < a.nall) ? a.xn[j] : 0.0;
+        lam_j[nj][p] = 0.5f * __fsub_rd(__double2float_rd(xnj[nj][p]) * 0.999998f, e2_up);
       }
     unsigned cand = 0;
 #pragma unroll
@@ -212,6 +232,7 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
       const bool iok = i < a.nall;
       const double xni = iok ? a.xn[i] : 0.0;
       const double eri = (edge && iok) ? a.er[i] : 0.0;
+      const float lam_i = 0.5f * (__double2float_rd(xni) * 0.999998f);
 #pragma unroll
       for (int nj = 0; nj < 2; ++nj)
 #pragma unroll
@@ -219,13 +240,12 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
           const int j = j0 + nj * 8 + 2 * tq + p;
           bool ok = iok && (j < i);
           if (edge && ok) ok = __dmul_rn(__dsub_rn(eri, a.er[j]), kAutokcal) < a.g.ethr;
-          double r[9];
+          float rf[9];
 #pragma unroll
-          for (int z = 0; z < 9; ++z) r[z] = acc[mi][nj][z][p];
-          const Quartic q = quartic_of(r);
-          const double s = xni + xnj[nj][p];
-          const double c1 = a.g.enantio ? -q.c1abs : -8.0 * q.det;
-          const bool far = screen_far(q, c1, s, fma(1e-8, s, a.g.E2));
+          for (int z = 0; z < 9; ++z) rf[z] = __double2float_rn(acc[mi][nj][z][p]);
+          // lam <= (s - E2)/2 - 1e-6*s: below the exact decision point by far more than the
+          // exact path's own rounding (relative 2e-6 covers the three float roundings)
+          const bool far = screen_far_f32(rf, __fadd_rd(lam_i, lam_j[nj][p]), a.g.enantio);
           my_pairs += ok;
           if (ok && (!far || a.rmat)) cand |= 1u << (mi * 4 + nj * 2 + p);
         }
@@ -244,20 +264,33 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
           bool dupl = false;
           if (cand & (1u << (mi * 4 + nj * 2 + p))) {
             const double s = xni + xnj[nj][p];
-            const double e = pair_e_exact(acc[mi][nj][0][p], acc[mi][nj][1][p], acc[mi][nj][2][p],
-                                          acc[mi][nj][3][p], acc[mi][nj][4][p], acc[mi][nj][5][p],
-                                          acc[mi][nj][6][p], acc[mi][nj][7][p], acc[mi][nj][8][p],
-                                          s, a.g.enantio);
-            if (a.rmat) {
-              const double rr = sqrt(fmax(0.0, e) / (double)L.A);
-              a.rmat[(size_t)i * (i - 1) / 2 + j] = (float)rr;
+            bool far = false;
+            if (!a.rmat) {   // second level: the same screen in FP64 (rigorous much closer to E2)
+              double r[9];
+#pragma unroll
+              for (int z = 0; z < 9; ++z) r[z] = acc[mi][nj][z][p];
+              const Quartic q = quartic_of(r);
+              const double c1 = a.g.enantio ? -q.c1abs : -8.0 * q.det;
+              far = screen_far(q, c1, s, fma(1e-8, s, a.g.E2));
             }
-            if (e < a.g.E2) {
-              dupl = e < a.g.E1;
-              if (!dupl)
-                dupl = equalrotaniso_dev(a.rot + 3 * (size_t)i, a.rot + 3 * (size_t)j, a.aniso[i],
-                                         a.aniso[j], a.g.bthr_half, a.g.bthrmax, a.g.bthrshift);
-              if (dupl) atomicMax(a.dup + i, j + 1);
+            if (!far) {
+              const double e = pair_e_exact(acc[mi][nj][0][p], acc[mi][nj][1][p],
+                                            acc[mi][nj][2][p], acc[mi][nj][3][p],
+                                            acc[mi][nj][4][p], acc[mi][nj][5][p],
+                                            acc[mi][nj][6][p], acc[mi][nj][7][p],
+                                            acc[mi][nj][8][p], s, a.g.enantio);
+              if (a.rmat) {
+                const double rr = sqrt(fmax(0.0, e) / (double)L.A);
+                a.rmat[(size_t)i * (i - 1) / 2 + j] = (float)rr;
+              }
+              if (e < a.g.E2) {
+                dupl = e < a.g.E1;
+                if (!dupl)
+                  dupl = equalrotaniso_dev(a.rot + 3 * (size_t)i, a.rot + 3 * (size_t)j,
+                                           a.aniso[i], a.aniso[j], a.g.bthr_half, a.g.bthrmax,
+                                           a.g.bthrshift);
+                if (dupl) atomicMax(a.dup + i, j + 1);
+              }
             }
           }
           if (a.mask) hit[p] = __ballot_sync(0xffffffffu, dupl);

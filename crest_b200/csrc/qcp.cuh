@@ -178,6 +178,41 @@ __device__ __forceinline__ bool screen_far(const Quartic& q, double c1, double s
   return (lam > 0.0) & (P > fl * sc) & (dP > fl * lam) & (ddP > fl);
 }
 
+// FP32 version of the screen, run on the FFMA pipe (which co-issues with the DMMA/FP64 pipe,
+// profiles/r01_fp64_pipes_microbench.txt).  Inputs are the covariance rounded to float and a
+// test point lam <= (s - Ecut)/2 (the caller rounds it DOWN).  Every quantity is a short sum of
+// products bounded by M^2 (P), M^1.5 (P') or M (P''/2) with M = max(lam^2, I1); the accumulated
+// rounding error of the float evaluation, input rounding included, is below ~100 * 2^-24 of those
+// scales, and each sign is required with a floor of 2e-4 of the scale (> 30x that bound), so a
+// `true` still PROVES lambda_max < lam.  Overflow/NaN compare false => undecided.
+__device__ __forceinline__ bool screen_far_f32(const float* r, float lam, int enantio) {
+  const float i1 = fmaf(r[8], r[8], fmaf(r[7], r[7], fmaf(r[6], r[6], fmaf(r[5], r[5],
+                   fmaf(r[4], r[4], fmaf(r[3], r[3], fmaf(r[2], r[2], fmaf(r[1], r[1], r[0] * r[0]))))))));
+  const float k00 = fmaf(r[4], r[8], -r[5] * r[7]);
+  const float k01 = fmaf(r[5], r[6], -r[3] * r[8]);
+  const float k02 = fmaf(r[3], r[7], -r[4] * r[6]);
+  const float k10 = fmaf(r[2], r[7], -r[1] * r[8]);
+  const float k11 = fmaf(r[0], r[8], -r[2] * r[6]);
+  const float k12 = fmaf(r[1], r[6], -r[0] * r[7]);
+  const float k20 = fmaf(r[1], r[5], -r[2] * r[4]);
+  const float k21 = fmaf(r[2], r[3], -r[0] * r[5]);
+  const float k22 = fmaf(r[0], r[4], -r[1] * r[3]);
+  const float det = fmaf(r[0], k00, fmaf(r[1], k01, r[2] * k02));
+  const float i2 = fmaf(k22, k22, fmaf(k21, k21, fmaf(k20, k20, fmaf(k12, k12, fmaf(k11, k11,
+                   fmaf(k10, k10, fmaf(k02, k02, fmaf(k01, k01, k00 * k00))))))));
+  const float c2 = -2.0f * i1;
+  const float c1 = enantio ? -8.0f * fabsf(det) : -8.0f * det;
+  const float c0 = fmaf(i1, i1, -4.0f * i2);
+  const float l2 = lam * lam;
+  const float M = fmaxf(l2, i1);
+  const float t = fmaf(l2 + c2, lam, c1);
+  const float P = fmaf(t, lam, c0);
+  const float dP = fmaf(fmaf(4.0f, l2, 2.0f * c2), lam, c1);
+  const float ddP = fmaf(6.0f, l2, c2);
+  const float fl = 2e-4f * M;
+  return (lam > 0.0f) & (P > fl * M) & (dP > fl * lam) & (ddP > fl);
+}
+
 // reference src/rotcompare.f90:109-122 (same operation order)
 __device__ __forceinline__ double rotaniso_dev(double a, double b, double c) {
   const double av = __ddiv_rn(__dadd_rn(__dadd_rn(a, b), c), 3.0);
