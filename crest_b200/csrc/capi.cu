@@ -47,6 +47,22 @@ static double e_threshold(double thr, int n) {
   return E;
 }
 
+const Tune& tune() {
+  static Tune t;
+  static bool init = false;
+  if (!init) {
+    init = true;
+    if (const char* e = std::getenv("CREST_CUDA_TUNE")) {
+      int v;
+      if (const char* q = std::strstr(e, "slab=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.slab_blocks = v;
+      if (const char* q = std::strstr(e, "stages=")) if (std::sscanf(q + 7, "%d", &v) == 1) t.stages = v;
+      if (const char* q = std::strstr(e, "dist=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.dist = v;
+      if (const char* q = std::strstr(e, "skew=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.skew = v;
+    }
+  }
+  return t;
+}
+
 static Gates make_gates(const crest_cuda_thresholds& t, int enantio, int A) {
   Gates g;
   g.ethr = t.ethr;
@@ -339,7 +355,22 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
   a.L = c->L;
   int ns = 0;
   pair_smem_bytes(c->L, &ns);
+  a.dbg = nullptr;
+  if (a.g.debug == 2) {
+    CREST_CUDA_TRY(cudaMalloc(&a.dbg, sizeof(long long) * 32));
+    CREST_CUDA_TRY(cudaMemsetAsync(a.dbg, 0, sizeof(long long) * 32, st));
+  }
   if (launch_pair_tiles(a, ns, st, &c->last_grid, &c->last_smem)) return 1;
+  if (a.dbg) {
+    long long h[32];
+    CREST_CUDA_TRY(cudaStreamSynchronize(st));
+    CREST_CUDA_TRY(cudaMemcpy(h, a.dbg, sizeof(h), cudaMemcpyDeviceToHost));
+    cudaFree(a.dbg);
+    const double g = c->last_grid > 0 ? c->last_grid : 1;
+    for (int w = 0; w < 8; ++w)
+      std::fprintf(stderr, "[pair_tile dbg] warp %d  avg clk/CTA: produce %.0f  wait_full %.0f  mma %.0f  epi_pass1 %.0f\n",
+                   w, h[4 * w] / g, h[4 * w + 1] / g, h[4 * w + 2] / g, h[4 * w + 3] / g);
+  }
   if (c->last_grid > 0) c->launches += 1;
   return 0;
 }

@@ -28,15 +28,25 @@ struct PackLayout {
   __host__ __device__ size_t total_doubles() const { return chunk_doubles() * nslab * npanel; }
 };
 
+// Developer knobs (env CREST_CUDA_TUNE="slab=<8-atom blocks per slab>,stages=<n>,dist=<n>,skew=<clk>"),
+// read once; 0 = automatic.  Used to A/B the pipeline shape on the GPU box without rebuilding.
+struct Tune { int slab_blocks = 0, stages = 0, dist = 0, skew = -1; };
+const Tune& tune();
+
+// K slabs of at most 40 atoms (5 blocks of 8); KS >= KU is the smem row stride with KS % 16 == 8
+// (bank rule for the 128-bit fragment loads).  Fewer, larger ring items measured faster than a
+// deep ring of small ones: each item costs warp 0 ~1000 clk of bulk-copy issue.
 inline PackLayout make_layout(int A, int nall) {
   PackLayout L;
   L.A = A;
-  const int a8 = ((A + 7) / 8) * 8;
-  L.nslab = (a8 + 39) / 40;
-  if (L.nslab < 1) L.nslab = 1;
-  const int blocks = (a8 / 8 + L.nslab - 1) / L.nslab;
-  L.KU = blocks * 8;
-  if (L.KU < 8) L.KU = 8;
+  const int nb = (A + 7) / 8 > 0 ? (A + 7) / 8 : 1;   // 8-atom blocks
+  int b = tune().slab_blocks;
+  if (b <= 0) {
+    const int nslab = (nb + 4) / 5;
+    b = (nb + nslab - 1) / nslab;
+  }
+  L.nslab = (nb + b - 1) / b;
+  L.KU = b * 8;
   L.KS = (L.KU % 16 == 8) ? L.KU : L.KU + 8;
   int np = (nall + kPanel - 1) / kPanel;
   if (np % kJPanels) np += kJPanels - (np % kJPanels);
@@ -95,6 +105,9 @@ struct PairArgs {
   float* rmat;           // optional all-pairs float32 band (diagnostics)
   Gates g;
   PackLayout L;
+  int dist;              // producer runs `dist` ring items ahead of warp 0
+  int skew_clk;          // start delay of warps 4-7 (half a tile), 0 = none
+  long long* dbg;        // CREST_CUDA_DEBUG=2: per-warp cycle counters [8 warps][4 phases]
 };
 int launch_pair_tiles(const PairArgs& a, int nstage, cudaStream_t stream, int* grid_out,
                       int* smem_out);

@@ -18,6 +18,11 @@
 #include "common.cuh"
 #include "qcp.cuh"
 
+// make PROF=1 builds the phase-instrumented kernel (clock64 counters per warp, CREST_CUDA_DEBUG=2)
+#ifndef CREST_PAIR_PROF
+#define CREST_PAIR_PROF 0
+#endif
+
 namespace crest {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -56,7 +61,7 @@ __device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b)
                : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-constexpr int kMaxStages = 4;
+constexpr int kMaxStages = 8;
 
 // Tile index -> (i-panel I, j-tile J).  A CTA walks t = t0, t0+grid, ... : after one binary search
 // the row is advanced incrementally (a dependent-load search per tile costs ~5k clk of latency).
@@ -119,8 +124,10 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
   const int nblk = L.KU >> 3;
 
   // Producer duty is folded into lane 0 of warp 0 (a 9th warp would be accounted as 12 warps by
-  // the register allocator and cap the kernel at 168 registers): it keeps the ring nstage-1
-  // items ahead of the consumers.  An item = one K slab of one tile (3 bulk copies).
+  // the register allocator and cap the kernel at 168 registers).  An item = one K slab of one
+  // tile (3 bulk copies); the ring is kept `dist` items ahead of warp 0.  Measured with the
+  // CREST_PAIR_PROF build: issuing one item costs warp 0 ~1000 clk, which is why few large items
+  // beat a deep ring of small ones.
   const bool is_producer = (threadIdx.x == 0);
   long long p_tile = a.tile_begin + blockIdx.x;
   int p_slab = 0, p_I = 0, p_J = 0;
@@ -144,10 +151,26 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
     if (++p_slab == L.nslab) { p_slab = 0; p_tile += gridDim.x; }
   };
   if (is_producer)
-    for (int s = 0; s < nstage - 1; ++s) produce_one();
+    for (int s = 0; s < a.dist; ++s) produce_one();
 
+  // Anti-phase start: the two warps of an SM sub-partition (w, w+4) share the DMMA pipe.  Warps
+  // 4-7 begin half a tile late, so one warp's epilogue (FFMA/ALU pipes) runs under the other's
+  // DMMA stream instead of both idling the tensor pipe together; the offset is conserved by the
+  // pipe sharing itself and bounded by the ring depth (nstage - dist - 1 items).
+#if CREST_PAIR_PROF
+  if (warp >= 4 && a.skew_clk > 0) {
+    const long long t0 = clock64();
+    while (clock64() - t0 < a.skew_clk) {}
+  }
+#endif
   unsigned long long my_pairs = 0;
   uint32_t it = 0;
+  long long tw = 0, tm = 0, te = 0, tp = 0, tc = 0;   // debug cycle counters
+#if CREST_PAIR_PROF
+  const bool prof = a.dbg != nullptr;
+#else
+  constexpr bool prof = false;
+#endif
   TileCursor cur;
   for (long long t = a.tile_begin + blockIdx.x; t < a.tile_end; t += gridDim.x) {
     int I, J;
@@ -168,9 +191,12 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
     for (int s = 0; s < L.nslab; ++s, ++it) {
       const int st = it % nstage;
       const uint32_t ph = (it / nstage) & 1;
+      if (prof) tc = clock64();
       if (is_producer) produce_one();
       __syncwarp();
+      if (prof) { const long long t1 = clock64(); tp += t1 - tc; tc = t1; }
       mbar_wait(&full_bar[st], ph);
+      if (prof) { const long long t1 = clock64(); tw += t1 - tc; tc = t1; }
       if (active) {
         const double* sb = sbase + (size_t)st * stage_doubles;
 #pragma unroll 1
@@ -203,8 +229,10 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty_bar[st]);
+      if (prof) { const long long t1 = clock64(); tm += t1 - tc; tc = t1; }
     }
     if (!active || a.g.debug == 1) continue;
+    if (prof) tc = clock64();
 
     // ------------------------------ fused epilogue ------------------------------
     // Pass 1 (branch-free, 8 independent pairs per lane): quartic invariants of each 3x3 R and
@@ -250,6 +278,7 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
           if (ok && (!far || a.rmat)) cand |= 1u << (mi * 4 + nj * 2 + p);
         }
     }
+    if (prof) te += clock64() - tc;
     if (!a.mask && !__any_sync(0xffffffffu, cand != 0)) continue;
 #pragma unroll
     for (int mi = 0; mi < 2; ++mi) {
@@ -314,6 +343,12 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
       }
     }
   }
+  if (prof && lane == 0) {
+    atomicAdd((unsigned long long*)a.dbg + warp * 4 + 0, (unsigned long long)tp);
+    atomicAdd((unsigned long long*)a.dbg + warp * 4 + 1, (unsigned long long)tw);
+    atomicAdd((unsigned long long*)a.dbg + warp * 4 + 2, (unsigned long long)tm);
+    atomicAdd((unsigned long long*)a.dbg + warp * 4 + 3, (unsigned long long)te);
+  }
   // one atomic per warp for the pair counter
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) my_pairs += __shfl_xor_sync(0xffffffffu, my_pairs, o);
@@ -324,13 +359,15 @@ int pair_smem_bytes(const PackLayout& L, int* nstage_out) {
   const size_t stage = L.chunk_doubles() * (1 + kJPanels) * sizeof(double);
   int ns = (int)((size_t)(227 * 1024 - 1024) / stage);
   if (ns > kMaxStages) ns = kMaxStages;
+  if (tune().stages > 0 && tune().stages < ns) ns = tune().stages;
   if (ns < 1) ns = 1;
   if (nstage_out) *nstage_out = ns;
   return (int)(stage * ns);
 }
 
-int launch_pair_tiles(const PairArgs& a, int nstage, cudaStream_t stream, int* grid_out,
+int launch_pair_tiles(const PairArgs& a_in, int nstage, cudaStream_t stream, int* grid_out,
                       int* smem_out) {
+  PairArgs a = a_in;
   const long long ntiles = a.tile_end - a.tile_begin;
   if (grid_out) *grid_out = 0;
   if (ntiles <= 0) return 0;
@@ -338,10 +375,17 @@ int launch_pair_tiles(const PairArgs& a, int nstage, cudaStream_t stream, int* g
   CREST_CUDA_TRY(cudaGetDevice(&dev));
   CREST_CUDA_TRY(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
   int ns = nstage;
-  const int smem = pair_smem_bytes(a.L, nstage > 0 ? nullptr : &ns);
+  if (ns <= 0) pair_smem_bytes(a.L, &ns);
   const size_t stage = a.L.chunk_doubles() * (1 + kJPanels) * sizeof(double);
   const int smem_used = (int)(stage * ns);
-  (void)smem;
+  // ring shape: the producer keeps up to `dist` items in flight beyond the one being consumed.
+  // Skew = half of a tile's DMMA time on one sub-partition (2 warps x 72 DMMA per 8-atom block,
+  // 16 clk of pipe each); it needs ring slots to live in, so only with >= 3 stages.
+  a.dist = tune().dist > 0 ? tune().dist : ns - 1;
+  if (a.dist > ns - 1) a.dist = ns - 1;
+  if (a.dist < 0) a.dist = 0;
+  a.skew_clk = 0;          // measured: no gain while all 8 warps share one ring
+  if (tune().skew >= 0) a.skew_clk = tune().skew;
   CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tile_kernel,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem_used));
   const int grid = (int)(ntiles < nsm ? ntiles : nsm);   // persistent: one CTA per SM
