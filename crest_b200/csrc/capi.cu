@@ -57,6 +57,7 @@ const Tune& tune() {
       if (const char* q = std::strstr(e, "slab=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.slab_blocks = v;
       if (const char* q = std::strstr(e, "stages=")) if (std::sscanf(q + 7, "%d", &v) == 1) t.stages = v;
       if (const char* q = std::strstr(e, "dist=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.dist = v;
+      if (std::strstr(e, "tile")) t.force_tile = 1;
       if (const char* q = std::strstr(e, "skew=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.skew = v;
     }
   }
@@ -68,6 +69,7 @@ static Gates make_gates(const crest_cuda_thresholds& t, int enantio, int A) {
   g.ethr = t.ethr;
   g.E1 = e_threshold(t.rthr, A);
   g.E2 = e_threshold(2.0 * t.rthr, A);
+  g.E2_up = std::nextafterf((float)g.E2, std::numeric_limits<float>::infinity());
   g.bthr_half = 0.5 * t.bthr;
   g.bthrmax = t.bthrmax;
   g.bthrshift = t.bthrshift;
@@ -107,6 +109,12 @@ struct crest_cuda_ctx {
   std::vector<long long> rowstart;
   std::vector<int> jfirst;
   double tiles_ethr = std::numeric_limits<double>::quiet_NaN();
+  // column-sweep kernel work list (pair_col.cu): {J, u_begin, u_end, edge} quadruples
+  bool use_col = false;
+  std::vector<int> items;
+  int* d_items = nullptr;
+  size_t cap_items = 0;
+  double items_ethr = std::numeric_limits<double>::quiet_NaN();
   long long launches = 0;
   int last_grid = 0, last_smem = 0;
 };
@@ -148,6 +156,66 @@ void band_tiles_host(int n, const double* er, double ethr, std::vector<long long
 void build_tiles(crest_cuda_ctx* c, double ethr) {
   band_tiles_host(c->nall, c->h_er.data(), ethr, c->rowstart, c->jfirst);
   c->tiles_ethr = ethr;
+}
+
+// Work list of the column-sweep kernel.  Column J = j-tile of 64 conformers; its in-band rows run
+// from the diagonal to the last i with (er[i]-er[j_hi])*autokcal < ethr (the tile's largest j
+// admits the largest i; the per-pair gate inside edge units does the rest, cregen.f90:1275).
+// Rows are cut on a fixed grid of `seg` 16-row units and the list is ordered segment-major, so
+// the CTAs that run at the same time stream the SAME i-units (L2-resident) past different j-tiles.
+void col_items_host(int n, const double* er, double ethr, std::vector<int>& items) {
+  items.clear();
+  if (n < 2) return;
+  const int nJ = (n + kColJ - 1) / kColJ;
+  std::vector<int> uend(nJ, 0);
+  long long total = 0;
+  for (int J = 0; J < nJ; ++J) {
+    const int jlo = J * kColJ, jhi = std::min(jlo + kColJ - 1, n - 1);
+    // last i in [jlo, n-1] with de(i, jhi) < ethr; de grows with i.  i <= jhi always passes
+    // (de <= 0 < ethr unless ethr <= 0, where nothing passes).
+    int lo = jlo, hi = n - 1;
+    if (!((er[lo] - er[jhi]) * kAutokcal < ethr)) { uend[J] = 0; continue; }
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) / 2;
+      if ((er[mid] - er[jhi]) * kAutokcal < ethr) lo = mid; else hi = mid - 1;
+    }
+    const int imax = lo;
+    if (imax <= jlo) { uend[J] = 0; continue; }
+    uend[J] = imax / kUnit + 1;
+    total += uend[J] - 4 * J;
+  }
+  long long seg = total / (148LL * 8 * 24);
+  if (seg < 8) seg = 8;
+  if (seg > 256) seg = 256;
+  const int nu = (n + kUnit - 1) / kUnit;
+  const int nseg = (int)((nu + seg - 1) / seg);
+  for (int sg = nseg - 1; sg >= 0; --sg) {          // bottom rows first: most columns, full items
+    const int s0 = (int)(sg * seg), s1 = (int)std::min<long long>((sg + 1) * seg, nu);
+    for (int J = 0; J < nJ; ++J) {
+      if (uend[J] == 0) continue;
+      const int b = std::max(4 * J, s0), e = std::min(uend[J], s1);
+      if (b < e) {
+        // edge: the item's largest i against the tile's smallest j may fail the gate
+        const int ilast = std::min(e * kUnit - 1, n - 1);
+        const int edge = ((er[ilast] - er[J * kColJ]) * kAutokcal < ethr) ? 0 : 1;
+        items.push_back(J); items.push_back(b); items.push_back(e); items.push_back(edge);
+      }
+    }
+  }
+}
+
+int upload_items(crest_cuda_ctx* c, double ethr, cudaStream_t st) {
+  col_items_host(c->nall, c->h_er.data(), ethr, c->items);
+  c->items_ethr = ethr;
+  const size_t n = c->items.size();
+  if (n > c->cap_items) {
+    cudaFree(c->d_items); c->d_items = nullptr; c->cap_items = 0;
+    CREST_CUDA_TRY(cudaMalloc(&c->d_items, sizeof(int) * n));
+    c->cap_items = n;
+  }
+  if (n) CREST_CUDA_TRY(cudaMemcpyAsync(c->d_items, c->items.data(), sizeof(int) * n,
+                                        cudaMemcpyHostToDevice, st));
+  return 0;
 }
 
 int upload_tiles(crest_cuda_ctx* c, cudaStream_t st) {
@@ -239,7 +307,7 @@ void crest_cuda_ctx_destroy(crest_cuda_ctx* c) {
   cudaSetDevice(c->device);
   cudaFree(c->d_at); cudaFree(c->d_sel); cudaFree(c->d_xyz); cudaFree(c->d_xyz_axis);
   cudaFree(c->d_er); cudaFree(c->d_rot); cudaFree(c->d_aniso); cudaFree(c->d_X); cudaFree(c->d_xn);
-  cudaFree(c->d_dup); cudaFree(c->d_npairs); cudaFree(c->d_rowstart); cudaFree(c->d_jfirst);
+  cudaFree(c->d_dup); cudaFree(c->d_npairs); cudaFree(c->d_rowstart); cudaFree(c->d_jfirst); cudaFree(c->d_items);
   cudaFree(c->d_mask); cudaFree(c->d_rmat);
   delete c;
 }
@@ -261,7 +329,9 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
     if (!rmsd_mask || rmsd_mask[k] > 0) sel.push_back(k);
   if (sel.empty()) { set_error("RMSD atom mask selects no atom"); return 1; }
   c->nat = nat; c->nall = nall; c->nsel = (int)sel.size(); c->rot_from_mask = rot_from_mask ? 1 : 0;
-  c->L = make_layout(c->nsel, nall);
+  c->use_col = col_layout_fits(c->nsel) && !tune().force_tile;
+  c->L = c->use_col ? make_col_layout(c->nsel, nall) : make_layout(c->nsel, nall);
+  c->items_ethr = std::numeric_limits<double>::quiet_NaN();
   c->h_er.assign(er, er + nall);
   c->tiles_ethr = std::numeric_limits<double>::quiet_NaN();
 
@@ -328,11 +398,13 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
   if (nranks < 1 || rank < 0 || rank >= nranks) { set_error("bad shard %d/%d", rank, nranks); return 1; }
   CREST_CUDA_TRY(cudaSetDevice(c->device));
   if (c->nall < 2) return 0;
-  if (!(c->tiles_ethr == thr->ethr)) {
+  if (c->use_col) {
+    if (!(c->items_ethr == thr->ethr) && upload_items(c, thr->ethr, st)) return 1;
+  } else if (!(c->tiles_ethr == thr->ethr)) {
     build_tiles(c, thr->ethr);
     if (upload_tiles(c, st)) return 1;
   }
-  const long long T = c->rowstart.back();
+  const long long T = c->use_col ? (long long)(c->items.size() / 4) : c->rowstart.back();
   PairArgs a{};
   a.X = c->d_X; a.xn = c->d_xn; a.er = c->d_er; a.rot = c->d_rot; a.aniso = c->d_aniso;
   a.rowstart = c->d_rowstart; a.jfirst = c->d_jfirst;
@@ -353,14 +425,20 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
   a.rmat = d_rmat;
   a.g = make_gates(*thr, enantio, c->nsel);
   a.L = c->L;
-  int ns = 0;
-  pair_smem_bytes(c->L, &ns);
   a.dbg = nullptr;
   if (a.g.debug == 2) {
     CREST_CUDA_TRY(cudaMalloc(&a.dbg, sizeof(long long) * 32));
     CREST_CUDA_TRY(cudaMemsetAsync(a.dbg, 0, sizeof(long long) * 32, st));
   }
-  if (launch_pair_tiles(a, ns, st, &c->last_grid, &c->last_smem)) return 1;
+  int ns = 0;
+  if (c->use_col) {
+    if (launch_pair_cols(a, c->d_items, (int)a.tile_begin, (int)a.tile_end, st, &c->last_grid,
+                         &c->last_smem))
+      return 1;
+  } else {
+    pair_smem_bytes(c->L, &ns);
+    if (launch_pair_tiles(a, ns, st, &c->last_grid, &c->last_smem)) return 1;
+  }
   if (a.dbg) {
     long long h[32];
     CREST_CUDA_TRY(cudaStreamSynchronize(st));
@@ -368,7 +446,7 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
     cudaFree(a.dbg);
     const double g = c->last_grid > 0 ? c->last_grid : 1;
     for (int w = 0; w < 8; ++w)
-      std::fprintf(stderr, "[pair_tile dbg] warp %d  avg clk/CTA: produce %.0f  wait_full %.0f  mma %.0f  epi_pass1 %.0f\n",
+      std::fprintf(stderr, "[pair dbg] warp %d  avg clk/CTA: produce+meta %.0f  wait_full %.0f  mma(+screen) %.0f  epilogue/exact %.0f\n",
                    w, h[4 * w] / g, h[4 * w + 1] / g, h[4 * w + 2] / g, h[4 * w + 3] / g);
   }
   if (c->last_grid > 0) c->launches += 1;
@@ -416,13 +494,20 @@ int crest_cuda_ctx_info(crest_cuda_ctx* c, const crest_cuda_thresholds* thr, int
   if (!c || !info) { set_error("NULL argument"); return 1; }
   if (check_thr(thr)) return 1;
   if (nranks < 1 || rank < 0 || rank >= nranks) { set_error("bad shard %d/%d", rank, nranks); return 1; }
-  if (c->nall >= 2 && !(c->tiles_ethr == thr->ethr)) {
+  if (c->nall >= 2 && c->use_col) {
+    if (!(c->items_ethr == thr->ethr)) {
+      CREST_CUDA_TRY(cudaSetDevice(c->device));
+      if (upload_items(c, thr->ethr, 0)) return 1;
+      CREST_CUDA_TRY(cudaStreamSynchronize(0));
+    }
+  } else if (c->nall >= 2 && !(c->tiles_ethr == thr->ethr)) {
     build_tiles(c, thr->ethr);
     CREST_CUDA_TRY(cudaSetDevice(c->device));
     if (upload_tiles(c, 0)) return 1;
     CREST_CUDA_TRY(cudaStreamSynchronize(0));
   }
-  const long long T = c->rowstart.empty() ? 0 : c->rowstart.back();
+  const long long T = c->use_col ? (long long)(c->items.size() / 4)
+                                 : (c->rowstart.empty() ? 0 : c->rowstart.back());
   long long tb = 0, te = 0;
   crest_cuda_shard_range(T, rank, nranks, &tb, &te);
   info[0] = te - tb;

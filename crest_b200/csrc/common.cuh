@@ -23,14 +23,15 @@ struct PackLayout {
   int nslab;    // K slabs
   int KU;       // atoms used per slab
   int KS;       // row stride (doubles)
-  int npanel;   // panels (even, >= ceil(nall/32))
-  __host__ __device__ size_t chunk_doubles() const { return (size_t)3 * kPanel * KS; }
+  int npanel;   // panels (even, >= ceil(nall/32)) / 16-row units (multiple of 4) in the column layout
+  int rows;     // conformers per chunk: kPanel (row-tile kernel) or kUnit (column kernel)
+  __host__ __device__ size_t chunk_doubles() const { return (size_t)3 * rows * KS; }
   __host__ __device__ size_t total_doubles() const { return chunk_doubles() * nslab * npanel; }
 };
 
 // Developer knobs (env CREST_CUDA_TUNE="slab=<8-atom blocks per slab>,stages=<n>,dist=<n>,skew=<clk>"),
 // read once; 0 = automatic.  Used to A/B the pipeline shape on the GPU box without rebuilding.
-struct Tune { int slab_blocks = 0, stages = 0, dist = 0, skew = -1; };
+struct Tune { int slab_blocks = 0, stages = 0, dist = 0, skew = -1, force_tile = 0; };
 const Tune& tune();
 
 // K slabs of at most 40 atoms (5 blocks of 8); KS >= KU is the smem row stride with KS % 16 == 8
@@ -39,6 +40,7 @@ const Tune& tune();
 inline PackLayout make_layout(int A, int nall) {
   PackLayout L;
   L.A = A;
+  L.rows = kPanel;
   const int nb = (A + 7) / 8 > 0 ? (A + 7) / 8 : 1;   // 8-atom blocks
   int b = tune().slab_blocks;
   if (b <= 0) {
@@ -55,6 +57,28 @@ inline PackLayout make_layout(int A, int nall) {
   return L;
 }
 
+// Column-sweep kernel (pair_col.cu): the whole K extent of a conformer is one row, chunks are
+// 16-row units, a j-tile is 4 consecutive units.  Usable while a j-tile plus >= 2 ring stages fit
+// in shared memory (A <= 88).
+constexpr int kUnit = 16;
+constexpr int kColJ = 64;          // j-tile width = 4 units
+constexpr int kColMaxNkb = 11;
+inline bool col_layout_fits(int A) { return (A + 7) / 8 <= kColMaxNkb; }
+inline PackLayout make_col_layout(int A, int nall) {
+  PackLayout L;
+  L.A = A;
+  L.rows = kUnit;
+  const int nb = (A + 7) / 8 > 0 ? (A + 7) / 8 : 1;
+  L.nslab = 1;
+  L.KU = nb * 8;
+  L.KS = (L.KU % 16 == 8) ? L.KU : L.KU + 8;
+  int nu = (nall + kUnit - 1) / kUnit;
+  nu = (nu + 3) / 4 * 4;
+  if (nu < 4) nu = 4;
+  L.npanel = nu;
+  return L;
+}
+
 // per-launch gate constants, precomputed on the host (capi.cu: make_gates)
 struct Gates {
   double ethr;       // kcal/mol
@@ -62,6 +86,7 @@ struct Gates {
   double E2;         // e < E2  <=>  real(rmsd,sp) < 2*rthr
   double bthr_half;  // 0.5*bthr (cregen.f90:1368)
   double bthrmax, bthrshift;
+  float E2_up;       // E2 rounded up to float (FP32 screen)
   int enantio;
   int debug;         // profiling switch (env CREST_CUDA_DEBUG): 1 = skip the epilogue (timing only)
 };
@@ -112,6 +137,10 @@ struct PairArgs {
 int launch_pair_tiles(const PairArgs& a, int nstage, cudaStream_t stream, int* grid_out,
                       int* smem_out);
 int pair_smem_bytes(const PackLayout& L, int* nstage_out);
+// column-sweep kernel (pair_col.cu); items = device array of {J, u_begin, u_end, edge} int quadruples
+int launch_pair_cols(const PairArgs& a, const void* d_items, int item_begin, int item_end,
+                     cudaStream_t stream, int* grid_out, int* smem_out);
+int col_smem_bytes(int KS, int* nstage_out);
 int launch_backtrack(int nall, int* d_dup, cudaStream_t stream);
 int launch_rmsd_pairs(int A, int n, const double* d_packed, long long npairs, const int* d_i,
                       const int* d_j, double* d_rmsd, double* d_rmsd_m, cudaStream_t stream);

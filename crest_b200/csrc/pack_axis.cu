@@ -258,7 +258,7 @@ pack_axis_kernel(int nat, int nall, const int* __restrict__ at, const double* __
   }
   const double inv_n = 1.0 / (double)nsel;
   cx = warp_sum(cx) * inv_n; cy = warp_sum(cy) * inv_n; cz = warp_sum(cz) * inv_n;
-  const int panel = conf / kPanel, row = conf % kPanel;
+  const int panel = conf / L.rows, row = conf % L.rows;
   double nrm = 0.0;
   const int kpad = L.nslab * L.KU;
   for (int k = lane; k < kpad; k += 32) {
@@ -270,9 +270,9 @@ pack_axis_kernel(int nat, int nall, const int* __restrict__ at, const double* __
     }
     const int slab = k / L.KU, kk = k % L.KU;
     double* chunk = X + ((size_t)panel * L.nslab + slab) * L.chunk_doubles();
-    chunk[((size_t)0 * kPanel + row) * L.KS + kk] = x;
-    chunk[((size_t)1 * kPanel + row) * L.KS + kk] = y;
-    chunk[((size_t)2 * kPanel + row) * L.KS + kk] = z;
+    chunk[((size_t)0 * L.rows + row) * L.KS + kk] = x;
+    chunk[((size_t)1 * L.rows + row) * L.KS + kk] = y;
+    chunk[((size_t)2 * L.rows + row) * L.KS + kk] = z;
   }
   nrm = warp_sum(nrm);
   if (lane == 0) xn_out[conf] = nrm;

@@ -17,6 +17,7 @@
 // B200, which is why the epilogue is written to minimise FP64 instruction count.
 #include "common.cuh"
 #include "qcp.cuh"
+#include "pipe.cuh"
 
 // make PROF=1 builds the phase-instrumented kernel (clock64 counters per warp, CREST_CUDA_DEBUG=2)
 #ifndef CREST_PAIR_PROF
@@ -24,42 +25,6 @@
 #endif
 
 namespace crest {
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
-               "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-      "selp.u32 %0, 1, 0, p;\n"
-      "}\n" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-  return ok != 0;
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {}
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-      ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1},{%2},{%3},{%0,%1};"
-               : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
-}
 
 constexpr int kMaxStages = 8;
 
@@ -244,14 +209,14 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
         !(__dmul_rn(__dsub_rn(a.er[ti_last], a.er[J * kTileJ]), kAutokcal) < a.g.ethr);
     double xnj[2][2];
     float lam_j[2][2];          // 0.5*(xn_j*(1-2e-6) - E2) rounded down; + 0.5*xn_i*(1-2e-6) gives lam
-    const float e2_up = __double2float_ru(a.g.E2);
+    const float e2_up = a.g.E2_up;
 #pragma unroll
     for (int nj = 0; nj < 2; ++nj)
 #pragma unroll
       for (int p = 0; p < 2; ++p) {
         const int j = j0 + nj * 8 + 2 * tq + p;
         xnj[nj][p] = (j < a.nall) ? a.xn[j] : 0.0;
-        lam_j[nj][p] = 0.5f * __fsub_rd(__double2float_rd(xnj[nj][p]) * 0.999998f, e2_up);
+        lam_j[nj][p] = 0.5f * __fsub_rd(f64_to_f32_trunc(xnj[nj][p]) * 0.999998f, e2_up);
       }
     unsigned cand = 0;
 #pragma unroll
@@ -260,7 +225,7 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
       const bool iok = i < a.nall;
       const double xni = iok ? a.xn[i] : 0.0;
       const double eri = (edge && iok) ? a.er[i] : 0.0;
-      const float lam_i = 0.5f * (__double2float_rd(xni) * 0.999998f);
+      const float lam_i = 0.5f * (f64_to_f32_trunc(xni) * 0.999998f);
 #pragma unroll
       for (int nj = 0; nj < 2; ++nj)
 #pragma unroll
@@ -270,10 +235,12 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
           if (edge && ok) ok = __dmul_rn(__dsub_rn(eri, a.er[j]), kAutokcal) < a.g.ethr;
           float rf[9];
 #pragma unroll
-          for (int z = 0; z < 9; ++z) rf[z] = __double2float_rn(acc[mi][nj][z][p]);
+          for (int z = 0; z < 9; ++z) rf[z] = f64_to_f32_trunc(acc[mi][nj][z][p]);
           // lam <= (s - E2)/2 - 1e-6*s: below the exact decision point by far more than the
           // exact path's own rounding (relative 2e-6 covers the three float roundings)
-          const bool far = screen_far_f32(rf, __fadd_rd(lam_i, lam_j[nj][p]), a.g.enantio);
+          const float lam_f = __fadd_rd(lam_i, lam_j[nj][p]);
+          // lam_f < 2^99 bounds every |R_ab| (<= s/2) inside the float range of the narrowing
+          const bool far = (lam_f < 6.0e29f) & screen_far_f32(rf, lam_f, a.g.enantio);
           my_pairs += ok;
           if (ok && (!far || a.rmat)) cand |= 1u << (mi * 4 + nj * 2 + p);
         }

@@ -178,11 +178,24 @@ __device__ __forceinline__ bool screen_far(const Quartic& q, double c1, double s
   return (lam > 0.0) & (P > fl * sc) & (dP > fl * lam) & (ddP > fl);
 }
 
+// FP64 -> FP32 narrowing by four integer ops (truncation toward zero, relative error < 2^-23).
+// F2F.F32.F64 is a slow-path instruction on B200 that also stalls the DMMA pipe
+// (tools/microbench/cvt_bench.cu, profiles/r01_cvt_microbench.txt); ALU instructions run beside
+// the tensor pipe.  |x| below the float normal range (incl. 0) gives a float denormal < 2^-126,
+// i.e. an absolute error far below every floor of the screen.  The caller guarantees
+// |x| < 2^127 (pair_tile checks s = |x|^2+|y|^2 against 2^100; |R_ab| <= s/2 by Cauchy-Schwarz).
+__device__ __forceinline__ float f64_to_f32_trunc(double x) {
+  const int hi = __double2hiint(x), lo = __double2loint(x);
+  const int t = max((hi & 0x7fffffff) - 0x38000000, 0);
+  const unsigned f = __funnelshift_l((unsigned)lo, (unsigned)t, 3);
+  return __uint_as_float(f | ((unsigned)hi & 0x80000000u));
+}
+
 // FP32 version of the screen, run on the FFMA pipe (which co-issues with the DMMA/FP64 pipe,
 // profiles/r01_fp64_pipes_microbench.txt).  Inputs are the covariance rounded to float and a
 // test point lam <= (s - Ecut)/2 (the caller rounds it DOWN).  Every quantity is a short sum of
 // products bounded by M^2 (P), M^1.5 (P') or M (P''/2) with M = max(lam^2, I1); the accumulated
-// rounding error of the float evaluation, input rounding included, is below ~100 * 2^-24 of those
+// rounding error of the float evaluation, input truncation (2^-23) included, is below ~100 * 2^-24 of those
 // scales, and each sign is required with a floor of 2e-4 of the scale (> 30x that bound), so a
 // `true` still PROVES lambda_max < lam.  Overflow/NaN compare false => undecided.
 __device__ __forceinline__ bool screen_far_f32(const float* r, float lam, int enantio) {
