@@ -104,6 +104,14 @@ __device__ __forceinline__ unsigned unit_block(double (&cur)[2][9][2], const dou
       if (((pm.ok >> q) & 1u) && (!far || all_cand)) cand |= 1u << q;
     }
   }
+  if (!SCREEN) {   // timing-only variant: keep the accumulators live without screening
+    double t = 0.0;
+#pragma unroll
+    for (int y = 0; y < 2; ++y)
+#pragma unroll
+      for (int z = 0; z < 9; ++z) t += prev[y][z][0] + prev[y][z][1];
+    if (t == 1.2345e-300) cand = 1;
+  }
   return cand;
 }
 
@@ -410,10 +418,7 @@ pair_col_kernel(const ColArgs a) {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  if ((threadIdx.x >> 5) < 4)
-    pair_col_body<NKB, 0, SCREEN>(a, smem_raw, full_bar, empty_bar, jfull_bar, jempty_bar);
-  else
-    pair_col_body<NKB, 1, SCREEN>(a, smem_raw, full_bar, empty_bar, jfull_bar, jempty_bar);
+  pair_col_body<NKB, 0, SCREEN>(a, smem_raw, full_bar, empty_bar, jfull_bar, jempty_bar);
 }
 
 int col_smem_bytes(int KS, int* nstage_out) {
