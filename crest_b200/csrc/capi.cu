@@ -58,6 +58,7 @@ const Tune& tune() {
       if (const char* q = std::strstr(e, "stages=")) if (std::sscanf(q + 7, "%d", &v) == 1) t.stages = v;
       if (const char* q = std::strstr(e, "dist=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.dist = v;
       if (std::strstr(e, "tile")) t.force_tile = 1;
+      if (std::strstr(e, "nohalf")) t.no_half = 1;
       if (const char* q = std::strstr(e, "skew=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.skew = v;
     }
   }

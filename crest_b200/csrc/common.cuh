@@ -25,13 +25,15 @@ struct PackLayout {
   int KS;       // row stride (doubles)
   int npanel;   // panels (even, >= ceil(nall/32)) / 16-row units (multiple of 4) in the column layout
   int rows;     // conformers per chunk: kPanel (row-tile kernel) or kUnit (column kernel)
+  int half_tail; // column layout: the last 8-atom block holds <= 4 atoms, stored at its EVEN slots
+                 // (the k-step that reads the odd slots is skipped: no MMA work on K padding)
   __host__ __device__ size_t chunk_doubles() const { return (size_t)3 * rows * KS; }
   __host__ __device__ size_t total_doubles() const { return chunk_doubles() * nslab * npanel; }
 };
 
 // Developer knobs (env CREST_CUDA_TUNE="slab=<8-atom blocks per slab>,stages=<n>,dist=<n>,skew=<clk>"),
 // read once; 0 = automatic.  Used to A/B the pipeline shape on the GPU box without rebuilding.
-struct Tune { int slab_blocks = 0, stages = 0, dist = 0, skew = -1, force_tile = 0; };
+struct Tune { int slab_blocks = 0, stages = 0, dist = 0, skew = -1, force_tile = 0, no_half = 0; };
 const Tune& tune();
 
 // K slabs of at most 40 atoms (5 blocks of 8); KS >= KU is the smem row stride with KS % 16 == 8
@@ -41,6 +43,7 @@ inline PackLayout make_layout(int A, int nall) {
   PackLayout L;
   L.A = A;
   L.rows = kPanel;
+  L.half_tail = 0;
   const int nb = (A + 7) / 8 > 0 ? (A + 7) / 8 : 1;   // 8-atom blocks
   int b = tune().slab_blocks;
   if (b <= 0) {
@@ -69,6 +72,7 @@ inline PackLayout make_col_layout(int A, int nall) {
   L.A = A;
   L.rows = kUnit;
   const int nb = (A + 7) / 8 > 0 ? (A + 7) / 8 : 1;
+  L.half_tail = (A - 8 * (nb - 1) <= 4 && !tune().no_half) ? 1 : 0;
   L.nslab = 1;
   L.KU = nb * 8;
   L.KS = (L.KU % 16 == 8) ? L.KU : L.KU + 8;

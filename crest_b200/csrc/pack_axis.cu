@@ -261,10 +261,15 @@ pack_axis_kernel(int nat, int nall, const int* __restrict__ at, const double* __
   const int panel = conf / L.rows, row = conf % L.rows;
   double nrm = 0.0;
   const int kpad = L.nslab * L.KU;
+  const int last0 = kpad - 8;          // first slot of the last 8-atom block
   for (int k = lane; k < kpad; k += 32) {
+    // slot k holds selected atom ks (or nothing): identity, except in a half tail where the
+    // <= 4 atoms of the last block sit at its even slots
+    int ks = k;
+    if (L.half_tail && k >= last0) ks = ((k - last0) & 1) ? -1 : last0 + ((k - last0) >> 1);
     double x = 0.0, y = 0.0, z = 0.0;
-    if (k < nsel) {
-      const int a = sel[k];
+    if (ks >= 0 && ks < nsel) {
+      const int a = sel[ks];
       x = dst[3 * a] - cx; y = dst[3 * a + 1] - cy; z = dst[3 * a + 2] - cz;
       nrm += x * x + y * y + z * z;
     }

@@ -56,7 +56,7 @@ struct UnitMeta {
 
 // One straight-line block: DMMA stream of the current unit into `cur` + FP32 screen of the
 // previous unit from `prev`.  Returns the candidate bits of the previous unit.
-template <int NKB, int PHASE, bool SCREEN>
+template <int NKB, bool HALF, bool SCREEN>
 __device__ __forceinline__ unsigned unit_block(double (&cur)[2][9][2], const double (&prev)[2][9][2],
                                                const double* __restrict__ su,   // unit stage + lane offset
                                                const double* __restrict__ sj0,  // j-tile + lane offset, nj=0
@@ -86,13 +86,14 @@ __device__ __forceinline__ unsigned unit_block(double (&cur)[2][9][2], const dou
 #pragma unroll
         for (int y = 0; y < 3; ++y) {
           dmma_nv(cur[nj][3 * x + y][0], cur[nj][3 * x + y][1], fa[x].x, fb[nj][y].x);
-          dmma_nv(cur[nj][3 * x + y][0], cur[nj][3 * x + y][1], fa[x].y, fb[nj][y].y);
+          if (!(HALF && kb == NKB - 1))     // half tail: the odd slots of the last block are padding
+            dmma_nv(cur[nj][3 * x + y][0], cur[nj][3 * x + y][1], fa[x].y, fb[nj][y].y);
         }
     // screen slice: the 4 pairs of the previous unit are spread over the K blocks
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       if (!SCREEN) continue;
-      if (screen_slot<NKB, PHASE>(q) != kb) continue;       // compile-time after unrolling
+      if (screen_slot<NKB, 0>(q) != kb) continue;       // compile-time after unrolling
       const int nj = q >> 1, p = q & 1;
       float rf[9];
 #pragma unroll
@@ -244,7 +245,7 @@ __device__ __forceinline__ void unit_meta(const ColArgs& a, const ColWarp& w, in
   m.ok = ok;
 }
 
-template <int NKB, int PHASE, bool SCREEN>
+template <int NKB, bool HALF, bool SCREEN>
 __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* smem_raw,
                                               uint64_t* full_bar, uint64_t* empty_bar,
                                               uint64_t& jfull_bar, uint64_t& jempty_bar) {
@@ -356,7 +357,7 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
     mbar_wait(&full_bar[st], ph);
     if (prof) { const long long t1 = clock64(); tw += t1 - tc; tc = t1; }
     const double* su = sU + (size_t)st * unit_doubles + w.a_off;
-    const unsigned cand = unit_block<NKB, PHASE, SCREEN>(cur, prev, su, sJ + w.b_off0, sJ + w.b_off1, w.comp,
+    const unsigned cand = unit_block<NKB, HALF, SCREEN>(cur, prev, su, sJ + w.b_off0, sJ + w.b_off1, w.comp,
                                           w.comp, mp, e2_up, a.g.enantio, all_cand);
     __syncwarp();
     if (w.lane == 0) mbar_arrive(&empty_bar[st]);
@@ -373,7 +374,7 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
     mB.ok = 0;
     if (!next_unit()) {
       // flush A: screen it without new data (the DMMAs re-read a resident stage; result unused)
-      const unsigned cand = unit_block<NKB, PHASE, SCREEN>(accB, accA, sU + w.a_off, sJ + w.b_off0, sJ + w.b_off1,
+      const unsigned cand = unit_block<NKB, HALF, SCREEN>(accB, accA, sU + w.a_off, sJ + w.b_off0, sJ + w.b_off1,
                                             w.comp, w.comp, mA, e2_up, a.g.enantio, all_cand);
       w.my_pairs += __popc(mA.ok);
       if (__any_sync(0xffffffffu, cand != 0)) unit_exact(a, w, accA, mA, cand);
@@ -384,7 +385,7 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
     mA.ok = 0;
   }
   if (__any_sync(0xffffffffu, mB.ok != 0)) {
-    const unsigned cand = unit_block<NKB, PHASE, SCREEN>(accA, accB, sU + w.a_off, sJ + w.b_off0, sJ + w.b_off1,
+    const unsigned cand = unit_block<NKB, HALF, SCREEN>(accA, accB, sU + w.a_off, sJ + w.b_off0, sJ + w.b_off1,
                                           w.comp, w.comp, mB, e2_up, a.g.enantio, all_cand);
     w.my_pairs += __popc(mB.ok);
     if (__any_sync(0xffffffffu, cand != 0)) unit_exact(a, w, accB, mB, cand);
@@ -401,7 +402,7 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
   if (w.lane == 0 && my_pairs) atomicAdd(a.npairs, my_pairs);
 }
 
-template <int NKB, bool SCREEN>
+template <int NKB, bool HALF, bool SCREEN>
 __global__ void __launch_bounds__(kPairThreads, 1)
 pair_col_kernel(const ColArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -418,7 +419,7 @@ pair_col_kernel(const ColArgs a) {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  pair_col_body<NKB, 0, SCREEN>(a, smem_raw, full_bar, empty_bar, jfull_bar, jempty_bar);
+  pair_col_body<NKB, HALF, SCREEN>(a, smem_raw, full_bar, empty_bar, jfull_bar, jempty_bar);
 }
 
 int col_smem_bytes(int KS, int* nstage_out) {
@@ -431,20 +432,22 @@ int col_smem_bytes(int KS, int* nstage_out) {
   return (int)(unit * (4 + ns));
 }
 
-template <int NKB>
-static int launch_col_nkb(const ColArgs& a, int grid, int smem, cudaStream_t stream) {
-  if (a.g.debug == 1) {     // timing-only variant without the screen (CREST_CUDA_DEBUG=1)
-    CREST_CUDA_TRY(cudaFuncSetAttribute(pair_col_kernel<NKB, false>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    pair_col_kernel<NKB, false><<<grid, kPairThreads, smem, stream>>>(a);
-    CREST_CUDA_TRY(cudaGetLastError());
-    return 0;
-  }
-  CREST_CUDA_TRY(cudaFuncSetAttribute(pair_col_kernel<NKB, true>,
+template <int NKB, bool HALF, bool SCREEN>
+static int launch_col_inst(const ColArgs& a, int grid, int smem, cudaStream_t stream) {
+  CREST_CUDA_TRY(cudaFuncSetAttribute(pair_col_kernel<NKB, HALF, SCREEN>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  pair_col_kernel<NKB, true><<<grid, kPairThreads, smem, stream>>>(a);
+  pair_col_kernel<NKB, HALF, SCREEN><<<grid, kPairThreads, smem, stream>>>(a);
   CREST_CUDA_TRY(cudaGetLastError());
   return 0;
+}
+
+template <int NKB>
+static int launch_col_nkb(const ColArgs& a, int half, int grid, int smem, cudaStream_t stream) {
+  if (a.g.debug == 1)      // timing-only variant without the screen (CREST_CUDA_DEBUG=1)
+    return half ? launch_col_inst<NKB, true, false>(a, grid, smem, stream)
+                : launch_col_inst<NKB, false, false>(a, grid, smem, stream);
+  return half ? launch_col_inst<NKB, true, true>(a, grid, smem, stream)
+              : launch_col_inst<NKB, false, true>(a, grid, smem, stream);
 }
 
 int launch_pair_cols(const PairArgs& pa, const void* d_items, int item_begin, int item_end,
@@ -467,17 +470,17 @@ int launch_pair_cols(const PairArgs& pa, const void* d_items, int item_begin, in
   const int grid = nitems < nsm ? nitems : nsm;     // persistent: one CTA per SM
   int rc = 1;
   switch (pa.L.KU / 8) {
-    case 1: rc = launch_col_nkb<1>(a, grid, smem, stream); break;
-    case 2: rc = launch_col_nkb<2>(a, grid, smem, stream); break;
-    case 3: rc = launch_col_nkb<3>(a, grid, smem, stream); break;
-    case 4: rc = launch_col_nkb<4>(a, grid, smem, stream); break;
-    case 5: rc = launch_col_nkb<5>(a, grid, smem, stream); break;
-    case 6: rc = launch_col_nkb<6>(a, grid, smem, stream); break;
-    case 7: rc = launch_col_nkb<7>(a, grid, smem, stream); break;
-    case 8: rc = launch_col_nkb<8>(a, grid, smem, stream); break;
-    case 9: rc = launch_col_nkb<9>(a, grid, smem, stream); break;
-    case 10: rc = launch_col_nkb<10>(a, grid, smem, stream); break;
-    case 11: rc = launch_col_nkb<11>(a, grid, smem, stream); break;
+    case 1: rc = launch_col_nkb<1>(a, pa.L.half_tail, grid, smem, stream); break;
+    case 2: rc = launch_col_nkb<2>(a, pa.L.half_tail, grid, smem, stream); break;
+    case 3: rc = launch_col_nkb<3>(a, pa.L.half_tail, grid, smem, stream); break;
+    case 4: rc = launch_col_nkb<4>(a, pa.L.half_tail, grid, smem, stream); break;
+    case 5: rc = launch_col_nkb<5>(a, pa.L.half_tail, grid, smem, stream); break;
+    case 6: rc = launch_col_nkb<6>(a, pa.L.half_tail, grid, smem, stream); break;
+    case 7: rc = launch_col_nkb<7>(a, pa.L.half_tail, grid, smem, stream); break;
+    case 8: rc = launch_col_nkb<8>(a, pa.L.half_tail, grid, smem, stream); break;
+    case 9: rc = launch_col_nkb<9>(a, pa.L.half_tail, grid, smem, stream); break;
+    case 10: rc = launch_col_nkb<10>(a, pa.L.half_tail, grid, smem, stream); break;
+    case 11: rc = launch_col_nkb<11>(a, pa.L.half_tail, grid, smem, stream); break;
     default: set_error("column kernel: unsupported K extent %d", pa.L.KU); return 1;
   }
   if (rc) return rc;
