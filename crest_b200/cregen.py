@@ -71,6 +71,11 @@ def __getattr__(name):            # module-level lazy constants
     raise AttributeError(name)
 
 
+def set_tune(spec=None):
+    """Developer knobs of the pair kernels (crest_cuda_set_tune); None restores the defaults."""
+    _lib.lib().crest_cuda_set_tune(spec.encode() if spec else None)
+
+
 def band_tiles(er, ethr):
     """Host-only: the in-band tile list (i-tile, j-tile arrays, rowstart, jfirst) for ascending
     energies er (Eh) and gate ethr (kcal/mol) — reference band cregen.f90:1240-1256 in tiles."""
@@ -252,10 +257,11 @@ class CregenContext:
 
     def info(self, env: Env, rank=0, nranks=1):
         thr = env.thresholds()
-        buf = (C.c_longlong * 8)()
+        buf = (C.c_longlong * 16)()
         _lib.check(self._L.crest_cuda_ctx_info(self._h, C.byref(thr), rank, nranks, buf))
-        keys = ["tiles_shard", "tiles_total", "A", "A_padded", "grid", "smem", "launches"]
-        return dict(zip(keys, list(buf)[:7]))
+        keys = ["tiles_shard", "tiles_total", "A", "A_padded", "grid", "smem", "launches",
+                "variant", "candidates", "overflow", "violations"]
+        return dict(zip(keys, list(buf)[:11]))
 
     def download(self, want_xyz=False, stream=0):
         rot = np.zeros((max(self.nall, 1), 3))

@@ -47,22 +47,32 @@ static double e_threshold(double thr, int n) {
   return E;
 }
 
+static void parse_tune(const char* e, Tune& t) {
+  t = Tune();
+  if (!e) return;
+  int v;
+  if (const char* q = std::strstr(e, "slab=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.slab_blocks = v;
+  if (const char* q = std::strstr(e, "stages=")) if (std::sscanf(q + 7, "%d", &v) == 1) t.stages = v;
+  if (const char* q = std::strstr(e, "dist=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.dist = v;
+  if (std::strstr(e, "tile")) t.force_tile = 1;
+  if (std::strstr(e, "nohalf")) t.no_half = 1;
+  if (std::strstr(e, "notf32")) t.no_tf32 = 1;
+  if (const char* q = std::strstr(e, "cap=")) if (std::sscanf(q + 4, "%d", &v) == 1) t.cand_cap = v;
+  if (const char* q = std::strstr(e, "chunk=")) if (std::sscanf(q + 6, "%d", &v) == 1) t.chunk = v;
+  if (const char* q = std::strstr(e, "skew=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.skew = v;
+}
+static Tune g_tune;
+static bool g_tune_init = false;
 const Tune& tune() {
-  static Tune t;
-  static bool init = false;
-  if (!init) {
-    init = true;
-    if (const char* e = std::getenv("CREST_CUDA_TUNE")) {
-      int v;
-      if (const char* q = std::strstr(e, "slab=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.slab_blocks = v;
-      if (const char* q = std::strstr(e, "stages=")) if (std::sscanf(q + 7, "%d", &v) == 1) t.stages = v;
-      if (const char* q = std::strstr(e, "dist=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.dist = v;
-      if (std::strstr(e, "tile")) t.force_tile = 1;
-      if (std::strstr(e, "nohalf")) t.no_half = 1;
-      if (const char* q = std::strstr(e, "skew=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.skew = v;
-    }
+  if (!g_tune_init) {
+    g_tune_init = true;
+    parse_tune(std::getenv("CREST_CUDA_TUNE"), g_tune);
   }
-  return t;
+  return g_tune;
+}
+void set_tune(const char* spec) {
+  g_tune_init = true;
+  parse_tune(spec, g_tune);
 }
 
 static Gates make_gates(const crest_cuda_thresholds& t, int enantio, int A) {
@@ -118,6 +128,17 @@ struct crest_cuda_ctx {
   double items_ethr = std::numeric_limits<double>::quiet_NaN();
   long long launches = 0;
   int last_grid = 0, last_smem = 0;
+  // tensor-core screen (pair_tf32.cu): TF32 operand copies, candidate list, its own work list
+  bool use_tf32 = false;
+  int ntile = 0;                       // i-tiles of 128 conformers
+  Tf32Buffers tf{};
+  size_t cap_tf_x = 0, cap_tf_hn = 0;
+  unsigned long long* d_npairs_scratch = nullptr;   // pair counter of a fallback re-run (discarded)
+  std::vector<int> tf_items;
+  int* d_tf_items = nullptr;
+  size_t cap_tf_items = 0;
+  double tf_items_ethr = std::numeric_limits<double>::quiet_NaN();
+  int last_variant = 0;                // 0 row-tile DMMA, 1 column DMMA, 2 TF32 screen + exact list
 };
 
 namespace {
@@ -205,6 +226,65 @@ void col_items_host(int n, const double* er, double ethr, std::vector<int>& item
   }
 }
 
+// Work list of the tensor-core screen kernel.  i-tile I = 128 conformers; its in-band j-groups (16
+// conformers) run from the first j admitted by the tile's FIRST row (smallest de) to the diagonal.
+// Groups below g_gate_end contain pairs that fail the energy gate for the tile's LAST row and are
+// gated pair by pair (cregen.f90:1275); the rest of the band needs no energies at all.  The list is
+// cut on a fixed grid of `chunk` groups and ordered segment-major so that concurrently running CTAs
+// stream the same j-groups (L2-resident) past different i-tiles.
+void tf_items_host(int n, const double* er, double ethr, std::vector<int>& items) {
+  items.clear();
+  if (n < 2) return;
+  const int ntile = (n + 127) / 128;
+  std::vector<int> gb(ntile, 0), ge(ntile, 0), gg(ntile, 0);
+  // first j in [0, i] with (er[i]-er[j])*autokcal < ethr; i+1 if none (monotone: er ascends)
+  auto first_in_band = [&](int i) {
+    int lo = 0, hi = i + 1;
+    while (lo < hi) {
+      const int mid = (lo + hi) / 2;
+      if ((er[i] - er[mid]) * kAutokcal < ethr) hi = mid; else lo = mid + 1;
+    }
+    return lo;
+  };
+  long long total = 0;
+  for (int I = 0; I < ntile; ++I) {
+    const int i0 = I * 128, ilast = std::min(i0 + 127, n - 1), jhi = ilast - 1;
+    if (jhi < 0) continue;
+    const int jlo = first_in_band(i0);
+    if (jlo > jhi) continue;
+    gb[I] = jlo / 16; ge[I] = jhi / 16 + 1;
+    const int jint = first_in_band(ilast);
+    gg[I] = (jint + 15) / 16;
+    total += ge[I] - gb[I];
+  }
+  long long chunk = tune().chunk > 0 ? tune().chunk : total / (148LL * 16);
+  if (chunk < 8) chunk = 8;
+  if (chunk > 256 && tune().chunk <= 0) chunk = 256;
+  const int ngroup = ntile * 8;
+  const int nseg = (int)((ngroup + chunk - 1) / chunk);
+  for (int sg = 0; sg < nseg; ++sg) {
+    const int s0 = (int)(sg * chunk), s1 = (int)std::min<long long>((sg + 1) * chunk, ngroup);
+    for (int I = ntile - 1; I >= 0; --I) {
+      const int b = std::max(gb[I], s0), e = std::min(ge[I], s1);
+      if (b < e) { items.push_back(I); items.push_back(b); items.push_back(e); items.push_back(gg[I]); }
+    }
+  }
+}
+
+int upload_tf_items(crest_cuda_ctx* c, double ethr, cudaStream_t st) {
+  tf_items_host(c->nall, c->h_er.data(), ethr, c->tf_items);
+  c->tf_items_ethr = ethr;
+  const size_t n = c->tf_items.size();
+  if (n > c->cap_tf_items) {
+    cudaFree(c->d_tf_items); c->d_tf_items = nullptr; c->cap_tf_items = 0;
+    CREST_CUDA_TRY(cudaMalloc(&c->d_tf_items, sizeof(int) * n));
+    c->cap_tf_items = n;
+  }
+  if (n) CREST_CUDA_TRY(cudaMemcpyAsync(c->d_tf_items, c->tf_items.data(), sizeof(int) * n,
+                                        cudaMemcpyHostToDevice, st));
+  return 0;
+}
+
 int upload_items(crest_cuda_ctx* c, double ethr, cudaStream_t st) {
   col_items_host(c->nall, c->h_er.data(), ethr, c->items);
   c->items_ethr = ethr;
@@ -247,6 +327,8 @@ int check_thr(const crest_cuda_thresholds* t) {
 extern "C" {
 
 const char* crest_cuda_last_error(void) { return g_err; }
+
+void crest_cuda_set_tune(const char* spec) { crest::set_tune(spec); }
 
 int crest_cuda_device_count(void) {
   int n = 0;
@@ -310,6 +392,8 @@ void crest_cuda_ctx_destroy(crest_cuda_ctx* c) {
   cudaFree(c->d_er); cudaFree(c->d_rot); cudaFree(c->d_aniso); cudaFree(c->d_X); cudaFree(c->d_xn);
   cudaFree(c->d_dup); cudaFree(c->d_npairs); cudaFree(c->d_rowstart); cudaFree(c->d_jfirst); cudaFree(c->d_items);
   cudaFree(c->d_mask); cudaFree(c->d_rmat);
+  cudaFree(c->tf.Xa); cudaFree(c->tf.Xb); cudaFree(c->tf.hn); cudaFree(c->tf.cand);
+  cudaFree(c->tf.cand_count); cudaFree(c->d_npairs_scratch); cudaFree(c->d_tf_items);
   delete c;
 }
 
@@ -333,6 +417,9 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
   c->use_col = col_layout_fits(c->nsel) && !tune().force_tile;
   c->L = c->use_col ? make_col_layout(c->nsel, nall) : make_layout(c->nsel, nall);
   c->items_ethr = std::numeric_limits<double>::quiet_NaN();
+  c->tf_items_ethr = std::numeric_limits<double>::quiet_NaN();
+  c->use_tf32 = c->use_col && !tune().no_tf32 && nall >= 2 && tf32_smem_bytes(c->L.KU, nullptr) > 0;
+  c->ntile = (nall + 127) / 128;
   c->h_er.assign(er, er + nall);
   c->tiles_ethr = std::numeric_limits<double>::quiet_NaN();
 
@@ -368,6 +455,34 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
     CREST_CUDA_TRY(cudaMalloc(&c->d_X, sizeof(double) * nX));
     c->cap_X = nX;
   }
+  if (c->use_tf32) {
+    const size_t nx = (size_t)c->ntile * 128 * 3 * c->L.KU;    // floats, same for Xa and Xb
+    if (nx > c->cap_tf_x) {
+      cudaFree(c->tf.Xa); cudaFree(c->tf.Xb); c->tf.Xa = c->tf.Xb = nullptr; c->cap_tf_x = 0;
+      CREST_CUDA_TRY(cudaMalloc(&c->tf.Xa, sizeof(float) * nx));
+      CREST_CUDA_TRY(cudaMalloc(&c->tf.Xb, sizeof(float) * nx));
+      c->cap_tf_x = nx;
+    }
+    const size_t nh = (size_t)c->ntile * 128;
+    if (nh > c->cap_tf_hn) {
+      cudaFree(c->tf.hn); c->tf.hn = nullptr; c->cap_tf_hn = 0;
+      CREST_CUDA_TRY(cudaMalloc(&c->tf.hn, sizeof(float) * nh));
+      c->cap_tf_hn = nh;
+    }
+    if (!c->tf.cand_count) {
+      CREST_CUDA_TRY(cudaMalloc(&c->tf.cand_count, sizeof(unsigned) * 4));
+      CREST_CUDA_TRY(cudaMalloc(&c->d_npairs_scratch, sizeof(unsigned long long)));
+    }
+    // candidate list: duplicates + near-threshold pairs; sized for 64 per conformer (min 1M,
+    // max 32M entries); an overflow re-runs the launch on the FP64 column kernel
+    size_t want = tune().cand_cap > 0 ? (size_t)tune().cand_cap
+                                      : std::min<size_t>(std::max<size_t>((size_t)nall * 64, 1u << 20), 32u << 20);
+    if (want > c->tf.cand_cap || (tune().cand_cap > 0 && want != c->tf.cand_cap)) {
+      cudaFree(c->tf.cand); c->tf.cand = nullptr; c->tf.cand_cap = 0;
+      CREST_CUDA_TRY(cudaMalloc(&c->tf.cand, sizeof(int) * 2 * want));
+      c->tf.cand_cap = (unsigned)want;
+    }
+  }
   CREST_CUDA_TRY(cudaMemcpy(c->d_at, at, sizeof(int) * nat, cudaMemcpyHostToDevice));
   CREST_CUDA_TRY(cudaMemcpy(c->d_sel, sel.data(), sizeof(int) * sel.size(), cudaMemcpyHostToDevice));
   if (nall > 0) {
@@ -390,6 +505,11 @@ int crest_cuda_ctx_pack(crest_cuda_ctx* c, void* stream) {
                        c->L, c->d_xyz_axis, c->d_rot, c->d_aniso, c->d_X, c->d_xn, st))
     return 1;
   if (c->nall > 0) c->launches += 1;
+  if (c->use_tf32) {
+    if (launch_tf32_convert(c->d_X, c->d_xn, c->nall, c->L, c->ntile, c->tf.Xa, c->tf.Xb, c->tf.hn, st))
+      return 1;
+    c->launches += 1;
+  }
   return 0;
 }
 
@@ -432,6 +552,31 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
     CREST_CUDA_TRY(cudaMemsetAsync(a.dbg, 0, sizeof(long long) * 32, st));
   }
   int ns = 0;
+  a.run_if = nullptr;
+  if (c->use_tf32 && !want_mask && !d_rmat && a.g.debug != 1 && a.g.debug != 2) {
+    // tensor-core screen + exact candidate pass; the FP64 column kernel follows as a conditional
+    // launch that only runs if the candidate list overflowed (results are idempotent: atomicMax)
+    if (!(c->tf_items_ethr == thr->ethr) && upload_tf_items(c, thr->ethr, st)) return 1;
+    const long long Ttf = (long long)(c->tf_items.size() / 4);
+    long long tb = 0, te = 0;
+    crest_cuda_shard_range(Ttf, rank, nranks, &tb, &te);
+    CREST_CUDA_TRY(cudaMemsetAsync(c->tf.cand_count, 0, sizeof(unsigned) * 4, st));
+    if (launch_pair_tf32(a, c->tf, c->d_tf_items, (int)tb, (int)te, a.g.debug == 3, st,
+                         &c->last_grid, &c->last_smem))
+      return 1;
+    if (c->last_grid > 0) c->launches += 2;
+    PairArgs fb = a;
+    fb.run_if = c->tf.cand_count + 1;
+    fb.npairs = c->d_npairs_scratch;
+    // the fallback covers the WHOLE triangle on this rank: the tf32 and column work lists shard
+    // the pair space differently, so a per-shard re-run would leave holes in a multi-rank job
+    int g2 = 0, s2 = 0;
+    if (launch_pair_cols(fb, c->d_items, 0, (int)(c->items.size() / 4), st, &g2, &s2)) return 1;
+    if (g2 > 0) c->launches += 1;
+    c->last_variant = 2;
+    return 0;
+  }
+  c->last_variant = c->use_col ? 1 : 0;
   if (c->use_col) {
     if (launch_pair_cols(a, c->d_items, (int)a.tile_begin, (int)a.tile_end, st, &c->last_grid,
                          &c->last_smem))
@@ -507,10 +652,20 @@ int crest_cuda_ctx_info(crest_cuda_ctx* c, const crest_cuda_thresholds* thr, int
     if (upload_tiles(c, 0)) return 1;
     CREST_CUDA_TRY(cudaStreamSynchronize(0));
   }
-  const long long T = c->use_col ? (long long)(c->items.size() / 4)
-                                 : (c->rowstart.empty() ? 0 : c->rowstart.back());
+  long long T = c->use_col ? (long long)(c->items.size() / 4)
+                           : (c->rowstart.empty() ? 0 : c->rowstart.back());
+  if (c->last_variant == 2) T = (long long)(c->tf_items.size() / 4);
   long long tb = 0, te = 0;
   crest_cuda_shard_range(T, rank, nranks, &tb, &te);
+  info[7] = c->last_variant;
+  info[8] = info[9] = info[10] = 0;
+  if (c->last_variant == 2 && c->tf.cand_count) {
+    unsigned h[4] = {0, 0, 0, 0};
+    CREST_CUDA_TRY(cudaSetDevice(c->device));
+    CREST_CUDA_TRY(cudaDeviceSynchronize());
+    CREST_CUDA_TRY(cudaMemcpy(h, c->tf.cand_count, sizeof(h), cudaMemcpyDeviceToHost));
+    info[8] = h[0]; info[9] = h[1]; info[10] = h[2];
+  }
   info[0] = te - tb;
   info[1] = T;
   info[2] = c->nsel;

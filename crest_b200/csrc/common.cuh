@@ -33,8 +33,9 @@ struct PackLayout {
 
 // Developer knobs (env CREST_CUDA_TUNE="slab=<8-atom blocks per slab>,stages=<n>,dist=<n>,skew=<clk>"),
 // read once; 0 = automatic.  Used to A/B the pipeline shape on the GPU box without rebuilding.
-struct Tune { int slab_blocks = 0, stages = 0, dist = 0, skew = -1, force_tile = 0, no_half = 0; };
+struct Tune { int slab_blocks = 0, stages = 0, dist = 0, skew = -1, force_tile = 0, no_half = 0, no_tf32 = 0, cand_cap = 0, chunk = 0; };
 const Tune& tune();
+void set_tune(const char* spec);   // re-parse the knobs (tests A/B kernel variants in one process)
 
 // K slabs of at most 40 atoms (5 blocks of 8); KS >= KU is the smem row stride with KS % 16 == 8
 // (bank rule for the 128-bit fragment loads).  Fewer, larger ring items measured faster than a
@@ -137,6 +138,8 @@ struct PairArgs {
   int dist;              // producer runs `dist` ring items ahead of warp 0
   int skew_clk;          // start delay of warps 4-7 (half a tile), 0 = none
   long long* dbg;        // CREST_CUDA_DEBUG=2: per-warp cycle counters [8 warps][4 phases]
+  const unsigned* run_if; // column kernel only: if non-NULL the kernel runs only when *run_if != 0
+                          // (FP64 fallback behind the tensor-core screen's candidate-list overflow)
 };
 int launch_pair_tiles(const PairArgs& a, int nstage, cudaStream_t stream, int* grid_out,
                       int* smem_out);
@@ -145,6 +148,22 @@ int pair_smem_bytes(const PackLayout& L, int* nstage_out);
 int launch_pair_cols(const PairArgs& a, const void* d_items, int item_begin, int item_end,
                      cudaStream_t stream, int* grid_out, int* smem_out);
 int col_smem_bytes(int KS, int* nstage_out);
+// tensor-core screen (pair_tf32.cu): TF32 operand copies, screen norms and the candidate list
+constexpr double kTfKappa = 1.8e-3;   // lam_test = (1-kappa) s/2 - E2/2 (error budget: pair_tf32.cu header)
+struct Tf32Buffers {
+  float* Xa = nullptr;        // [tile][comp][chunk][128][4]  A operands (i-tiles of 128 conformers)
+  float* Xb = nullptr;        // [group][chunk][48][4]        B operands (j-groups of 16 conformers)
+  float* hn = nullptr;        // [ntile*128] rd(0.5*|x|^2*(1-kappa))
+  void* cand = nullptr;       // int2[cand_cap] candidate pairs (i, j)
+  unsigned cand_cap = 0;
+  unsigned* cand_count = nullptr;   // [0] appended, [1] overflow, [2] debug violations, [3] spare
+};
+int tf32_smem_bytes(int KU, int* nbstage_out);
+int launch_tf32_convert(const double* d_X, const double* d_xn, int nall, const PackLayout& L,
+                        int ntile, float* d_Xa, float* d_Xb, float* d_hn, cudaStream_t stream);
+// items = device array of {I, g_begin, g_end, g_gate_end} int quadruples
+int launch_pair_tf32(const PairArgs& a, const Tf32Buffers& tb, const void* d_items, int item_begin,
+                     int item_end, int all_cand, cudaStream_t stream, int* grid_out, int* smem_out);
 int launch_backtrack(int nall, int* d_dup, cudaStream_t stream);
 int launch_rmsd_pairs(int A, int n, const double* d_packed, long long npairs, const int* d_i,
                       const int* d_j, double* d_rmsd, double* d_rmsd_m, cudaStream_t stream);

@@ -136,6 +136,7 @@ struct ColArgs {
   Gates g;
   int A, KS, nstage;
   long long* dbg;        // make PROF=1 + CREST_CUDA_DEBUG=2: per-warp cycle counters
+  const unsigned* run_if; // non-NULL: run only if *run_if != 0 (fallback behind the TF32 screen)
 };
 
 // Per-warp constants of the kernel, bundled so the two ping-pong call sites stay short.
@@ -409,6 +410,7 @@ pair_col_kernel(const ColArgs a) {
   __shared__ __align__(8) uint64_t full_bar[kColStagesMax];
   __shared__ __align__(8) uint64_t empty_bar[kColStagesMax];
   __shared__ __align__(8) uint64_t jfull_bar, jempty_bar;
+  if (a.run_if && *a.run_if == 0u) return;
   if (threadIdx.x == 0) {
     for (int s = 0; s < a.nstage; ++s) {
       mbar_init(&full_bar[s], 1);
@@ -460,7 +462,7 @@ int launch_pair_cols(const PairArgs& pa, const void* d_items, int item_begin, in
   a.items = static_cast<const ColItem*>(d_items);
   a.item_begin = item_begin; a.item_end = item_end;
   a.nall = pa.nall; a.dup = pa.dup; a.npairs = pa.npairs; a.mask = pa.mask; a.n8 = pa.n8;
-  a.rmat = pa.rmat; a.g = pa.g; a.A = pa.L.A; a.KS = pa.L.KS; a.dbg = pa.dbg;
+  a.rmat = pa.rmat; a.g = pa.g; a.A = pa.L.A; a.KS = pa.L.KS; a.dbg = pa.dbg; a.run_if = pa.run_if;
   int ns = 0;
   const int smem = col_smem_bytes(a.KS, &ns);
   a.nstage = ns;

@@ -1,0 +1,432 @@
+// Kernels (2)+(3), tensor-core SCREEN variant for A <= 88 atoms: the all-pairs 3x3 covariance
+// blocks are contracted on the 5th-generation tensor cores (tcgen05.mma kind::tf32, accumulators
+// in TMEM), every pair is screened in FP32 with a RIGOROUS error bound, and only the pairs the
+// screen cannot prove "far" (duplicates and near-threshold pairs: ~1e-4 of an ensemble) are
+// re-contracted in FP64 and decided exactly.
+//
+// Replaces the reference's pair loops K1/K2/K3 (src/cregen.f90:1266-1349, two rmsd() calls per
+// pair = src/ls_rmsd.f90:72-174) and the duplicate test of K4 (src/cregen.f90:1353-1373); the
+// decisions are the ones of the FP64 kernels (pair_col.cu / pair_tile.cu), because a pair leaves
+// the FP32 path only with a proof.
+//
+// Why this is allowed: CREGEN never needs the RMSD of a far pair, only the fact
+// rmsd >= 2*rthr, i.e. lambda_max(S(R)) < lam* = (s - E2)/2 with s = |x|^2+|y|^2.  With the operands
+// rounded to TF32 (relative error u <= 2^-11 each) and FP32 accumulation,
+//     |dR_ab| <= rho * |x_a||y_b|,  rho = 2u + u^2 + gamma  (gamma: accumulation, budget 6e-5)
+//     ||dR||_F <= rho * |x||y| <= rho * s/2
+//     |lambda_max(R) - lambda_max(R~)| <= ||dR||_* <= sqrt(3) ||dR||_F <= 1.78e-3 * s/2
+// (S is linear in R and every eigenvalue of S(dR) is a signed sum of the singular values of dR), so
+// the Budan-Fourier sign test of qcp.cuh evaluated on R~ at lam = (1 - 1.8e-3) s/2 - E2/2 proves
+// lambda_max(R) < lam*.  B200's FP64 tensor path tops out at ~36 TFLOP/s; the TF32 path is >20x
+// wider, which moves the bound of this stage from the DMMA pipe to the FP32 screen arithmetic.
+//
+// Shape: a CTA keeps one i-tile (128 conformers, all K, 3 components = 3 A operands [128 x K]) in
+// shared memory and streams j-groups of 16 conformers past it; a j-group is ONE B operand
+// [48 x K] (row n = 16*b + jj), so three MMAs per K step (N = 48) leave, in TMEM lane i, the full
+// 3x3 covariance of the 16 pairs (i, j0..j0+15): D_a[i][16 b + jj].  Operands are written by
+// tf32_convert_kernel in the canonical no-swizzle K-major core-matrix layout, so one 1-D bulk copy
+// (TMA engine) brings a tile/group in exactly the byte order the UMMA descriptor describes.
+// Warp roles: warps 0-7 epilogue (TMEM -> registers -> screen), warp 8 producer, warp 9 MMA issuer.
+#include "common.cuh"
+#include "qcp.cuh"
+#include "pipe.cuh"
+
+namespace crest {
+
+constexpr int kTfThreads = 320;
+constexpr int kTfEpiWarps = 8;
+constexpr int kTfBStagesMax = 8;
+constexpr int kTfDStages = 2;          // TMEM accumulator stages
+constexpr int kTfAccStride = 64;       // TMEM columns between the three accumulators of a stage
+constexpr int kTfStageStride = 256;    // TMEM columns between stages
+constexpr int kTfCols = 512;
+
+// ---- tcgen05 primitives (sm_100a PTX) ------------------------------------------------------
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+               ::"r"(smem_u32(bar)) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, kind::tf32, one CTA
+__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc,
+                                            uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_ld8(uint32_t taddr, uint32_t (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+                 "=r"(v[7]) : "r"(taddr));
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major, no-swizzle shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
+// core matrix = 8 rows x 16 B, contiguous (128 B); SBO = byte distance between 8-row groups,
+// LBO = byte distance between the two 16-byte K chunks of one MMA; version 1 (Blackwell).
+__device__ __forceinline__ uint64_t umma_desc_kmajor(uint32_t smem_addr, uint32_t lbo_bytes,
+                                                     uint32_t sbo_bytes) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) |
+         ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) | (1ull << 46);
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor): D=F32, A=B=TF32, both K-major, M=128, N=48
+constexpr uint32_t kTfIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((48u >> 3) << 17) | ((128u >> 4) << 24);
+
+struct TfItem { int I; int g_begin; int g_end; int g_gate_end; };
+
+struct TfArgs {
+  const float* Xa;        // [tile][comp][chunk][128][4]
+  const float* Xb;        // [group][chunk][48][4]
+  const float* hn;        // rd(0.5*|x|^2*(1-kappa)) per conformer, zero padded to the tile grid
+  const double* er;
+  const TfItem* items;
+  int item_begin, item_end;
+  int nall;
+  int KU;                 // K extent (multiple of 8)
+  int nbstage;
+  float cE;               // -0.5 * E2_up
+  double ethr;
+  int enantio;
+  int all_cand;           // debug: every pair goes to the exact kernel, bit 31 of j = screen said far
+  int2* cand;             // candidate list
+  unsigned cand_cap;
+  unsigned* cand_count;   // [0] = appended, [1] = overflow flag, [2] = screen violations (debug)
+  unsigned long long* npairs;
+};
+
+__global__ void __launch_bounds__(kTfThreads, 1)
+pair_tf32_kernel(const TfArgs a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t a_full, a_empty;
+  __shared__ __align__(8) uint64_t b_full[kTfBStagesMax], b_empty[kTfBStagesMax];
+  __shared__ __align__(8) uint64_t d_full[kTfDStages], d_empty[kTfDStages];
+  __shared__ uint32_t tmem_base_smem;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nchunk = a.KU >> 2;
+  const uint32_t a_comp_bytes = (uint32_t)nchunk * 2048u;       // one component of the i-tile
+  const uint32_t a_bytes = 3u * a_comp_bytes;
+  const uint32_t b_bytes = (uint32_t)nchunk * 768u;             // one j-group
+  unsigned char* const sA = smem_raw;
+  unsigned char* const sB = smem_raw + a_bytes;
+  const int nbs = a.nbstage;
+
+  if (threadIdx.x == 0) {
+    mbar_init(&a_full, 1);
+    mbar_init(&a_empty, 1);
+    for (int s = 0; s < nbs; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+    for (int t = 0; t < kTfDStages; ++t) { mbar_init(&d_full[t], 1); mbar_init(&d_empty[t], kTfEpiWarps); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 8) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 ::"r"(smem_u32(&tmem_base_smem)), "r"((uint32_t)kTfCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp == 8) {
+    // ===================== producer: bulk copies of the i-tile and the j-group ring ==========
+    if (lane == 0) {
+      uint32_t nb = 0, na = 0;
+      for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
+        const TfItem item = a.items[k];
+        mbar_wait(&a_empty, (na & 1) ^ 1);              // every MMA on the previous tile is done
+        mbar_expect_tx(&a_full, a_bytes);
+        bulk_g2s(sA, a.Xa + (size_t)item.I * (a_bytes >> 2), a_bytes, &a_full);
+        ++na;
+        for (int g = item.g_begin; g < item.g_end; ++g) {
+          const int s = nb % nbs;
+          mbar_wait(&b_empty[s], ((nb / nbs) & 1) ^ 1);
+          mbar_expect_tx(&b_full[s], b_bytes);
+          bulk_g2s(sB + (size_t)s * b_bytes, a.Xb + (size_t)g * (b_bytes >> 2), b_bytes, &b_full[s]);
+          ++nb;
+        }
+      }
+    }
+  } else if (warp == 9) {
+    // ===================== MMA issuer: one thread, 3 x KU/8 tcgen05.mma per j-group ==========
+    if (lane == 0) {
+      uint32_t nb = 0, na = 0, nd = 0;
+      const uint32_t sA_addr = smem_u32(sA), sB_addr = smem_u32(sB);
+      const int ksteps = a.KU >> 3;
+      for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
+        const TfItem item = a.items[k];
+        mbar_wait(&a_full, na & 1);
+        ++na;
+        for (int g = item.g_begin; g < item.g_end; ++g) {
+          const int s = nb % nbs, t = nd % kTfDStages;
+          mbar_wait(&d_empty[t], ((nd / kTfDStages) & 1) ^ 1);   // epilogue drained this TMEM stage
+          mbar_wait(&b_full[s], (nb / nbs) & 1);
+          tc_fence_after();
+          const uint32_t bs = sB_addr + (uint32_t)s * b_bytes;
+#pragma unroll 1
+          for (int ks = 0; ks < ksteps; ++ks) {
+            const uint64_t bdesc = umma_desc_kmajor(bs + (uint32_t)ks * 2u * 768u, 768u, 128u);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+              const uint64_t adesc = umma_desc_kmajor(
+                  sA_addr + (uint32_t)c * a_comp_bytes + (uint32_t)ks * 2u * 2048u, 2048u, 128u);
+              tc_mma_tf32(tmem_base + (uint32_t)(t * kTfStageStride + c * kTfAccStride), adesc, bdesc,
+                          kTfIdesc, ks > 0 ? 1u : 0u);
+            }
+          }
+          tc_commit(&b_empty[s]);      // smem slot reusable once these MMAs have read it
+          tc_commit(&d_full[t]);       // accumulators of this group complete
+          ++nb; ++nd;
+        }
+        tc_commit(&a_empty);           // i-tile reusable once every MMA of the item is done
+      }
+    }
+  } else {
+    // ===================== epilogue: TMEM -> registers -> FP32 screen -> candidate list ======
+    const int q = warp & 3, h = warp >> 2;       // TMEM lane quarter, j half of the group
+    uint32_t nd = 0;
+    unsigned long long my_pairs = 0;
+    for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
+      const TfItem item = a.items[k];
+      const int i = item.I * 128 + q * 32 + lane;
+      const bool iok = i < a.nall;
+      const float hi = a.hn[i];
+      for (int g = item.g_begin; g < item.g_end; ++g) {
+        const int t = nd % kTfDStages;
+        const int j0 = g * 16 + h * 8;
+        const float4 h0 = __ldg(reinterpret_cast<const float4*>(a.hn + j0));
+        const float4 h1 = __ldg(reinterpret_cast<const float4*>(a.hn + j0 + 4));
+        const float hj[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+        mbar_wait(&d_full[t], (nd / kTfDStages) & 1);
+        ++nd;
+        tc_fence_after();
+        uint32_t v[9][8];
+        const uint32_t tad = tmem_base + ((uint32_t)(q * 32) << 16) +
+                             (uint32_t)(t * kTfStageStride + h * 8);
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+#pragma unroll
+          for (int b = 0; b < 3; ++b) tc_ld8(tad + (uint32_t)(c * kTfAccStride + b * 16), v[3 * c + b]);
+        tc_wait_ld();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&d_empty[t]);
+        // which pairs count: j < i, inside the ensemble, inside the energy band (cregen.f90:1275)
+        unsigned ok = iok ? 0xFFu : 0u;
+        const bool slow = (g < item.g_gate_end) || (g * 16 + 15 >= item.I * 128);
+        if (slow) {
+          ok = 0;
+          const bool gate = g < item.g_gate_end;
+          const double eri = gate && iok ? a.er[i] : 0.0;
+#pragma unroll
+          for (int p = 0; p < 8; ++p) {
+            const int j = j0 + p;
+            bool o = iok && (j < i);
+            if (o && gate) o = __dmul_rn(__dsub_rn(eri, a.er[j]), kAutokcal) < a.ethr;
+            ok |= (o ? 1u : 0u) << p;
+          }
+        }
+        my_pairs += __popc(ok);
+        unsigned cand = 0, farbits = 0;
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+          float rf[9];
+#pragma unroll
+          for (int z = 0; z < 9; ++z) rf[z] = __uint_as_float(v[z][p]);
+          const float lam_f = __fadd_rd(__fadd_rd(hi, hj[p]), a.cE);
+          const bool far = (lam_f < 6.0e29f) & screen_far_f32(rf, lam_f, a.enantio);
+          farbits |= (far ? 1u : 0u) << p;
+          if (!far) cand |= 1u << p;
+        }
+        if (a.all_cand) cand = 0xFFu;
+        cand &= ok;
+        if (cand) {
+#pragma unroll 1
+          for (int p = 0; p < 8; ++p) {
+            if (!((cand >> p) & 1u)) continue;
+            const unsigned idx = atomicAdd(a.cand_count, 1u);
+            if (idx < a.cand_cap) {
+              int jj = j0 + p;
+              if (a.all_cand && ((farbits >> p) & 1u)) jj |= (int)0x80000000u;
+              a.cand[idx] = make_int2(i, jj);
+            } else {
+              a.cand_count[1] = 1u;
+            }
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) my_pairs += __shfl_xor_sync(0xffffffffu, my_pairs, o);
+    if (lane == 0 && my_pairs) atomicAdd(a.npairs, my_pairs);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;"
+                 ::"r"(tmem_base), "r"((uint32_t)kTfCols) : "memory");
+  }
+}
+
+// ---- operand conversion: FP64 column layout X -> TF32 operands + screen norms ------------------
+// X: [unit][comp][16][KS] doubles (pack_axis.cu).  One thread per (conformer, comp, 4-atom chunk).
+__device__ __forceinline__ float to_tf32_rn(double x) {
+  unsigned u = __float_as_uint(__double2float_rn(x));
+  u = (u + 0x1000u) & 0xFFFFE000u;       // round to 10 mantissa bits (half-ulp added to the magnitude)
+  return __uint_as_float(u);
+}
+
+__global__ void __launch_bounds__(256)
+tf32_convert_kernel(const double* __restrict__ X, const double* __restrict__ xn, int nall, int nunit,
+                    int KS, int KU, int ntile, float* __restrict__ Xa, float* __restrict__ Xb,
+                    float* __restrict__ hn, double kappa) {
+  const int nchunk = KU >> 2;
+  const long long total = (long long)ntile * 128 * 3 * nchunk;
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid < (long long)ntile * 128) {
+    const int i = (int)tid;
+    hn[i] = i < nall ? __double2float_rd(0.5 * xn[i] * (1.0 - kappa)) : 0.0f;
+  }
+  if (tid >= total) return;
+  const int r = (int)(tid % 128);
+  long long rest = tid / 128;
+  const int c = (int)(rest % nchunk); rest /= nchunk;
+  const int comp = (int)(rest % 3);
+  const int I = (int)(rest / 3);
+  const int i = I * 128 + r;
+  float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int unit = i >> 4;
+  if (i < nall && unit < nunit) {
+    const double* src = X + ((size_t)(unit * 3 + comp) * 16 + (i & 15)) * KS + 4 * c;
+    const double2 p0 = *reinterpret_cast<const double2*>(src);
+    const double2 p1 = *reinterpret_cast<const double2*>(src + 2);
+    o = make_float4(to_tf32_rn(p0.x), to_tf32_rn(p0.y), to_tf32_rn(p1.x), to_tf32_rn(p1.y));
+  }
+  reinterpret_cast<float4*>(Xa)[(((size_t)I * 3 + comp) * nchunk + c) * 128 + r] = o;
+  const int g = i >> 4, jj = i & 15;
+  reinterpret_cast<float4*>(Xb)[((size_t)g * nchunk + c) * 48 + comp * 16 + jj] = o;
+}
+
+// ---- exact pass over the candidate list: FP64 covariance, Newton/Jacobi, gates, atomicMax --------
+// 8 lanes per pair.  Decisions are those of pair_col.cu's unit_exact (same second-level screen,
+// same pair_e_exact, same float32-threshold emulation and rot gate).
+struct ExactArgs {
+  const double* X; const double* xn; const double* rot; const double* aniso;
+  const int2* cand; const unsigned* cand_count; unsigned cand_cap;
+  int KS, KU;
+  Gates g;
+  int* dup;
+  unsigned* violations;   // debug (all_cand): pairs the screen called far whose exact e < E2
+};
+
+__global__ void __launch_bounds__(256)
+exact_cand_kernel(const ExactArgs a) {
+  const unsigned n = min(a.cand_count[0], a.cand_cap);
+  const int sub = threadIdx.x & 7;
+  const unsigned gmask = 0xFFu << (threadIdx.x & 24);
+  for (unsigned p = blockIdx.x * 32u + (threadIdx.x >> 3); p < ((n + 31u) & ~31u); p += gridDim.x * 32u) {
+    const bool live = p < n;
+    const int2 ij = live ? a.cand[p] : make_int2(0, 0);
+    const int i = ij.x, j = ij.y & 0x7fffffff;
+    const bool screen_far_flag = ij.y < 0;
+    const double* xi = a.X + ((size_t)(i >> 4) * 3 * 16 + (i & 15)) * a.KS;
+    const double* xj = a.X + ((size_t)(j >> 4) * 3 * 16 + (j & 15)) * a.KS;
+    const size_t cs = (size_t)16 * a.KS;
+    double r[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    if (live)
+      for (int k = sub; k < a.KU; k += 8) {
+        const double x0 = xi[k], x1 = xi[cs + k], x2 = xi[2 * cs + k];
+        const double y0 = xj[k], y1 = xj[cs + k], y2 = xj[2 * cs + k];
+        r[0] = fma(x0, y0, r[0]); r[1] = fma(x0, y1, r[1]); r[2] = fma(x0, y2, r[2]);
+        r[3] = fma(x1, y0, r[3]); r[4] = fma(x1, y1, r[4]); r[5] = fma(x1, y2, r[5]);
+        r[6] = fma(x2, y0, r[6]); r[7] = fma(x2, y1, r[7]); r[8] = fma(x2, y2, r[8]);
+      }
+#pragma unroll
+    for (int z = 0; z < 9; ++z) {
+      r[z] += __shfl_xor_sync(gmask, r[z], 1);
+      r[z] += __shfl_xor_sync(gmask, r[z], 2);
+      r[z] += __shfl_xor_sync(gmask, r[z], 4);
+    }
+    if (live && sub == 0) {
+      const double s = a.xn[i] + a.xn[j];
+      const Quartic q = quartic_of(r);
+      const double c1 = a.g.enantio ? -q.c1abs : -8.0 * q.det;
+      if (!screen_far(q, c1, s, fma(1e-8, s, a.g.E2))) {
+        const double e = pair_e_exact(r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], r[8], s,
+                                      a.g.enantio);
+        if (e < a.g.E2) {
+          if (screen_far_flag && a.violations) atomicAdd(a.violations, 1u);
+          bool dupl = e < a.g.E1;
+          if (!dupl)
+            dupl = equalrotaniso_dev(a.rot + 3 * (size_t)i, a.rot + 3 * (size_t)j, a.aniso[i],
+                                     a.aniso[j], a.g.bthr_half, a.g.bthrmax, a.g.bthrshift);
+          if (dupl) atomicMax(a.dup + i, j + 1);
+        }
+      }
+    }
+  }
+}
+
+// ---- host side -------------------------------------------------------------------------------
+int tf32_smem_bytes(int KU, int* nbstage_out) {
+  const size_t a_bytes = (size_t)3 * (KU / 4) * 2048, b_bytes = (size_t)(KU / 4) * 768;
+  int ns = (int)(((size_t)(227 * 1024 - 2048) - a_bytes) / b_bytes);
+  if (ns > kTfBStagesMax) ns = kTfBStagesMax;
+  if (tune().stages > 0 && tune().stages < ns) ns = tune().stages;
+  if (nbstage_out) *nbstage_out = ns;
+  return (int)(a_bytes + (size_t)ns * b_bytes);
+}
+
+int launch_tf32_convert(const double* d_X, const double* d_xn, int nall, const PackLayout& L,
+                        int ntile, float* d_Xa, float* d_Xb, float* d_hn, cudaStream_t stream) {
+  const long long total = (long long)ntile * 128 * 3 * (L.KU / 4);
+  if (total <= 0) return 0;
+  const int blocks = (int)((total + 255) / 256);
+  tf32_convert_kernel<<<blocks, 256, 0, stream>>>(d_X, d_xn, nall, L.npanel, L.KS, L.KU, ntile, d_Xa,
+                                                  d_Xb, d_hn, kTfKappa);
+  CREST_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int launch_pair_tf32(const PairArgs& pa, const Tf32Buffers& tb, const void* d_items, int item_begin,
+                     int item_end, int all_cand, cudaStream_t stream, int* grid_out, int* smem_out) {
+  if (grid_out) *grid_out = 0;
+  const int nitems = item_end - item_begin;
+  if (nitems <= 0) return 0;
+  TfArgs a{};
+  a.Xa = tb.Xa; a.Xb = tb.Xb; a.hn = tb.hn; a.er = pa.er;
+  a.items = static_cast<const TfItem*>(d_items);
+  a.item_begin = item_begin; a.item_end = item_end;
+  a.nall = pa.nall; a.KU = pa.L.KU;
+  int ns = 0;
+  const int smem = tf32_smem_bytes(a.KU, &ns);
+  if (ns < 2) { set_error("tf32 kernel: K extent %d does not fit shared memory", a.KU); return 1; }
+  a.nbstage = ns;
+  a.cE = -0.5f * pa.g.E2_up;
+  a.ethr = pa.g.ethr; a.enantio = pa.g.enantio; a.all_cand = all_cand;
+  a.cand = static_cast<int2*>(tb.cand); a.cand_cap = tb.cand_cap; a.cand_count = tb.cand_count;
+  a.npairs = pa.npairs;
+  int dev = 0, nsm = 148;
+  CREST_CUDA_TRY(cudaGetDevice(&dev));
+  CREST_CUDA_TRY(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
+  const int grid = nitems < nsm ? nitems : nsm;
+  CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  pair_tf32_kernel<<<grid, kTfThreads, smem, stream>>>(a);
+  CREST_CUDA_TRY(cudaGetLastError());
+  ExactArgs e{};
+  e.X = pa.X; e.xn = pa.xn; e.rot = pa.rot; e.aniso = pa.aniso;
+  e.cand = a.cand; e.cand_count = tb.cand_count; e.cand_cap = tb.cand_cap;
+  e.KS = pa.L.KS; e.KU = pa.L.KU; e.g = pa.g; e.dup = pa.dup;
+  e.violations = all_cand ? tb.cand_count + 2 : nullptr;
+  exact_cand_kernel<<<nsm * 4, 256, 0, stream>>>(e);
+  CREST_CUDA_TRY(cudaGetLastError());
+  if (grid_out) *grid_out = grid;
+  if (smem_out) *smem_out = smem;
+  return 0;
+}
+
+}  // namespace crest

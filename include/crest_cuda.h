@@ -124,7 +124,12 @@ int crest_cuda_ctx_download(crest_cuda_ctx* ctx, double* rot, double* xyz_axis, 
 
 /* Geometry of the launch that ctx_pairs would do (for bench/roofline bookkeeping):
  * info[0]=tiles in shard, [1]=tiles total, [2]=atoms in RMSD (A), [3]=padded atoms used by MMA,
- * [4]=grid, [5]=dynamic smem bytes, [6]=kernels launched by the last ctx_* call sequence. */
+ * [4]=grid, [5]=dynamic smem bytes, [6]=kernels launched by the last ctx_* call sequence,
+ * [7]=pair-kernel variant of the last ctx_pairs (0 row-tile DMMA, 1 column DMMA, 2 tensor-core
+ * TF32 screen + exact FP64 candidate pass), [8]=candidate pairs the screen passed to the exact
+ * kernel, [9]=1 if the candidate list overflowed (launch re-run on the FP64 column kernel),
+ * [10]=screen violations counted in the CREST_CUDA_DEBUG=3 self-check (must be 0).
+ * info must hold 16 entries; reading [8..10] synchronises the device. */
 int crest_cuda_ctx_info(crest_cuda_ctx* ctx, const crest_cuda_thresholds* thr, int rank,
                         int nranks, long long* info);
 
@@ -147,6 +152,11 @@ int crest_cuda_band_tiles(int nall, const double* er, double ethr, long long* ro
                           int* jfirst, long long* ntiles);
 int crest_cuda_shard_range(long long ntiles, int rank, int nranks, long long* begin,
                            long long* end);
+
+/* Developer knobs (same syntax as the CREST_CUDA_TUNE environment variable; NULL = defaults):
+ * "notf32" forces the FP64 (DMMA) pair kernels, "tile" the row-tile kernel, "cap=<n>" the candidate
+ * list capacity, "chunk=<n>" j-groups per work item.  Takes effect at the next ctx_upload. */
+void crest_cuda_set_tune(const char* spec);
 
 const char* crest_cuda_last_error(void);
 int crest_cuda_device_count(void);
