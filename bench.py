@@ -194,6 +194,31 @@ def fp64_peak_tflops(torch, dev):
     return 2.0 * n ** 3 / (best * 1e-3) / 1e12
 
 
+def tf32_peak_tflops(torch, dev):
+    """TF32 tensor roofline denominator for the tcgen05 screen kernel: cuBLAS TF32 GEMM 8192^3, best
+    of 5 (MEASURED_PEAKS.json holds the bf16 figure only; TF32 dense = half of it nominally)."""
+    n = 8192
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    a = torch.randn(n, n, dtype=torch.float32, device=dev)
+    b = torch.randn(n, n, dtype=torch.float32, device=dev)
+    for _ in range(2):
+        a @ b
+    torch.cuda.synchronize()
+    best = 1e30
+    for _ in range(5):
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        a @ b
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    torch.backends.cuda.matmul.allow_tf32 = old
+    del a, b
+    return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -304,22 +329,39 @@ def run_ours(args):
 
     if rank == 0:
         A = info["A"]
-        peak = fp64_peak_tflops(torch, dev)
+        fp64_peak = fp64_peak_tflops(torch, dev)
         achieved = 18.0 * A * my_pairs / (pair_ms * 1e-3) / 1e12
+        variant = {0: "pair_tile (DMMA row tiles)", 1: "pair_col (DMMA column sweep)",
+                   2: "pair_tf32 (tcgen05 TF32 screen) + exact_cand (FP64 list)"}[info["variant"]]
+        if info["variant"] == 2:
+            peak = tf32_peak_tflops(torch, dev)
+            note = ("tensor roofline of the dominant kernel pair_tf32_kernel (tcgen05.mma kind::tf32): "
+                    "18*A FLOP per pair x pairs of rank 0 / pair-stage time (CUDA events around "
+                    "pair_tf32 + exact_cand + the conditional fallback launch); peak = cuBLAS TF32 GEMM "
+                    "8192^3 measured in this run (MEASURED_PEAKS.json has bf16 only). The kernel is "
+                    "bound by the FP32 screen arithmetic of its epilogue warps, not by the tensor "
+                    "pipe (DESIGN.md 4); fp64_tensor_equiv = the same FLOP against the measured DGEMM "
+                    "peak, i.e. what an FP64-only formulation could reach at most")
+        else:
+            peak = fp64_peak
+            note = ("FP64 tensor (DMMA) roofline: 18*A FLOP per pair x pairs of rank 0 / pair kernel "
+                    "time (CUDA events); peak = cuBLAS DGEMM 6144^3 measured in this run "
+                    "(MEASURED_PEAKS.json has no FP64 figure)")
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args, ens),
             "pairs_per_step": pairs_step, "duplicates_found": int((res["dup"] != 0).sum()),
-            "gpu_launches": int(3 * args.steps),
-            "kernels": {"pair_tile_ms": pair_ms, "grid": info["grid"], "smem": info["smem"],
-                        "tiles_this_rank": info["tiles_shard"], "atoms_padded": info["A_padded"]},
+            "gpu_launches": int(info["launches"] * args.steps),
+            "kernels": {"variant": variant, "pair_stage_ms": pair_ms, "grid": info["grid"],
+                        "smem": info["smem"], "items_this_rank": info["tiles_shard"],
+                        "atoms_padded": info["A_padded"], "launches_per_step": info["launches"],
+                        "exact_candidates": info["candidates"], "overflow": info["overflow"]},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                          "frac": achieved / peak, "traffic": None,
-                         "note": "FP64 tensor (DMMA) roofline: 18*A FLOP per pair x pairs of rank 0 "
-                                 "/ pair_tile kernel time (CUDA events); peak = cuBLAS DGEMM 6144^3 "
-                                 "measured in this run (MEASURED_PEAKS.json has no FP64 figure)"},
+                         "fp64_tensor_peak": fp64_peak, "fp64_tensor_equiv": achieved / fp64_peak,
+                         "note": note},
             "clocks": clocks, "e2e": e2e,
         }
         if world == 1 and not args.no_cpu_baseline:

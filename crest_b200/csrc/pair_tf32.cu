@@ -63,6 +63,11 @@ __device__ __forceinline__ void tc_ld8(uint32_t taddr, uint32_t (&v)[8]) {
                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
                  "=r"(v[7]) : "r"(taddr));
 }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major, no-swizzle shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
@@ -98,6 +103,7 @@ struct TfArgs {
   unsigned long long* npairs;
 };
 
+template <int KSTEPS>
 __global__ void __launch_bounds__(kTfThreads, 1)
 pair_tf32_kernel(const TfArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -107,10 +113,10 @@ pair_tf32_kernel(const TfArgs a) {
   __shared__ uint32_t tmem_base_smem;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nchunk = a.KU >> 2;
-  const uint32_t a_comp_bytes = (uint32_t)nchunk * 2048u;       // one component of the i-tile
-  const uint32_t a_bytes = 3u * a_comp_bytes;
-  const uint32_t b_bytes = (uint32_t)nchunk * 768u;             // one j-group
+  constexpr int nchunk = 2 * KSTEPS;
+  constexpr uint32_t a_comp_bytes = (uint32_t)nchunk * 2048u;       // one component of the i-tile
+  constexpr uint32_t a_bytes = 3u * a_comp_bytes;
+  constexpr uint32_t b_bytes = (uint32_t)nchunk * 768u;         // one j-group
   unsigned char* const sA = smem_raw;
   unsigned char* const sB = smem_raw + a_bytes;
   const int nbs = a.nbstage;
@@ -135,55 +141,59 @@ pair_tf32_kernel(const TfArgs a) {
   if (warp == 8) {
     // ===================== producer: bulk copies of the i-tile and the j-group ring ==========
     if (lane == 0) {
-      uint32_t nb = 0, na = 0;
+      uint32_t sb = 0, phb = 0, pha = 0;
       for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
         const TfItem item = a.items[k];
-        mbar_wait(&a_empty, (na & 1) ^ 1);              // every MMA on the previous tile is done
+        mbar_wait(&a_empty, pha ^ 1);                   // every MMA on the previous tile is done
+        pha ^= 1;
         mbar_expect_tx(&a_full, a_bytes);
         bulk_g2s(sA, a.Xa + (size_t)item.I * (a_bytes >> 2), a_bytes, &a_full);
-        ++na;
         for (int g = item.g_begin; g < item.g_end; ++g) {
-          const int s = nb % nbs;
-          mbar_wait(&b_empty[s], ((nb / nbs) & 1) ^ 1);
-          mbar_expect_tx(&b_full[s], b_bytes);
-          bulk_g2s(sB + (size_t)s * b_bytes, a.Xb + (size_t)g * (b_bytes >> 2), b_bytes, &b_full[s]);
-          ++nb;
+          mbar_wait(&b_empty[sb], phb ^ 1);
+          mbar_expect_tx(&b_full[sb], b_bytes);
+          bulk_g2s(sB + (size_t)sb * b_bytes, a.Xb + (size_t)g * (b_bytes >> 2), b_bytes, &b_full[sb]);
+          if (++sb == (uint32_t)nbs) { sb = 0; phb ^= 1; }
         }
       }
     }
   } else if (warp == 9) {
-    // ===================== MMA issuer: one thread, 3 x KU/8 tcgen05.mma per j-group ==========
-    if (lane == 0) {
-      uint32_t nb = 0, na = 0, nd = 0;
-      const uint32_t sA_addr = smem_u32(sA), sB_addr = smem_u32(sB);
-      const int ksteps = a.KU >> 3;
-      for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
-        const TfItem item = a.items[k];
-        mbar_wait(&a_full, na & 1);
-        ++na;
-        for (int g = item.g_begin; g < item.g_end; ++g) {
-          const int s = nb % nbs, t = nd % kTfDStages;
-          mbar_wait(&d_empty[t], ((nd / kTfDStages) & 1) ^ 1);   // epilogue drained this TMEM stage
-          mbar_wait(&b_full[s], (nb / nbs) & 1);
-          tc_fence_after();
-          const uint32_t bs = sB_addr + (uint32_t)s * b_bytes;
-#pragma unroll 1
-          for (int ks = 0; ks < ksteps; ++ks) {
-            const uint64_t bdesc = umma_desc_kmajor(bs + (uint32_t)ks * 2u * 768u, 768u, 128u);
+    // ===================== MMA issuer: the warp runs the control flow, ONE elected lane issues
+    // 3 x KSTEPS tcgen05.mma per j-group.  Descriptors differ only in the 14-bit start-address
+    // field, so every MMA of the unrolled block is base + compile-time constant.
+    uint32_t sb = 0, phb = 0, td = 0, phd = 0, pha = 0;
+    const uint32_t a_lo0 = ((smem_u32(sA) >> 4) & 0x3FFFu) | ((2048u >> 4) << 16);
+    const uint32_t b_lo00 = ((smem_u32(sB) >> 4) & 0x3FFFu) | ((768u >> 4) << 16);
+    constexpr uint32_t desc_hi = (128u >> 4) | (1u << 14);      // SBO = 128 B, version 1
+    for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
+      const int g_begin = a.items[k].g_begin, g_end = a.items[k].g_end;
+      mbar_wait(&a_full, pha);
+      pha ^= 1;
+      for (int g = g_begin; g < g_end; ++g) {
+        mbar_wait(&d_empty[td], phd ^ 1);              // epilogue drained this TMEM stage
+        mbar_wait(&b_full[sb], phb);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t b_lo0 = b_lo00 + sb * (b_bytes >> 4);
+          const uint32_t d0 = tmem_base + td * kTfStageStride;
+#pragma unroll
+          for (int ks = 0; ks < KSTEPS; ++ks) {
+            const uint64_t bdesc = ((uint64_t)desc_hi << 32) | (b_lo0 + (uint32_t)ks * (2u * 768u >> 4));
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
-              const uint64_t adesc = umma_desc_kmajor(
-                  sA_addr + (uint32_t)c * a_comp_bytes + (uint32_t)ks * 2u * 2048u, 2048u, 128u);
-              tc_mma_tf32(tmem_base + (uint32_t)(t * kTfStageStride + c * kTfAccStride), adesc, bdesc,
-                          kTfIdesc, ks > 0 ? 1u : 0u);
+              const uint64_t adesc = ((uint64_t)desc_hi << 32) |
+                                     (a_lo0 + (((uint32_t)c * a_comp_bytes + (uint32_t)ks * 4096u) >> 4));
+              tc_mma_tf32(d0 + (uint32_t)(c * kTfAccStride), adesc, bdesc, kTfIdesc, ks > 0 ? 1u : 0u);
             }
           }
-          tc_commit(&b_empty[s]);      // smem slot reusable once these MMAs have read it
-          tc_commit(&d_full[t]);       // accumulators of this group complete
-          ++nb; ++nd;
+          tc_commit(&b_empty[sb]);     // smem slot reusable once these MMAs have read it
+          tc_commit(&d_full[td]);      // accumulators of this group complete
         }
-        tc_commit(&a_empty);           // i-tile reusable once every MMA of the item is done
+        __syncwarp();
+        if (++sb == (uint32_t)nbs) { sb = 0; phb ^= 1; }
+        td ^= 1; if (td == 0) phd ^= 1;
       }
+      if (elect_one()) tc_commit(&a_empty);            // i-tile reusable once every MMA of the item is done
+      __syncwarp();
     }
   } else {
     // ===================== epilogue: TMEM -> registers -> FP32 screen -> candidate list ======
@@ -392,6 +402,15 @@ int launch_tf32_convert(const double* d_X, const double* d_xn, int nall, const P
   return 0;
 }
 
+template <int KSTEPS>
+static int launch_tf32_inst(const TfArgs& a, int grid, int smem, cudaStream_t stream) {
+  CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_kernel<KSTEPS>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  pair_tf32_kernel<KSTEPS><<<grid, kTfThreads, smem, stream>>>(a);
+  CREST_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 int launch_pair_tf32(const PairArgs& pa, const Tf32Buffers& tb, const void* d_items, int item_begin,
                      int item_end, int all_cand, cudaStream_t stream, int* grid_out, int* smem_out) {
   if (grid_out) *grid_out = 0;
@@ -414,9 +433,22 @@ int launch_pair_tf32(const PairArgs& pa, const Tf32Buffers& tb, const void* d_it
   CREST_CUDA_TRY(cudaGetDevice(&dev));
   CREST_CUDA_TRY(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
   const int grid = nitems < nsm ? nitems : nsm;
-  CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  pair_tf32_kernel<<<grid, kTfThreads, smem, stream>>>(a);
-  CREST_CUDA_TRY(cudaGetLastError());
+  int rc = 1;
+  switch (a.KU / 8) {
+    case 1: rc = launch_tf32_inst<1>(a, grid, smem, stream); break;
+    case 2: rc = launch_tf32_inst<2>(a, grid, smem, stream); break;
+    case 3: rc = launch_tf32_inst<3>(a, grid, smem, stream); break;
+    case 4: rc = launch_tf32_inst<4>(a, grid, smem, stream); break;
+    case 5: rc = launch_tf32_inst<5>(a, grid, smem, stream); break;
+    case 6: rc = launch_tf32_inst<6>(a, grid, smem, stream); break;
+    case 7: rc = launch_tf32_inst<7>(a, grid, smem, stream); break;
+    case 8: rc = launch_tf32_inst<8>(a, grid, smem, stream); break;
+    case 9: rc = launch_tf32_inst<9>(a, grid, smem, stream); break;
+    case 10: rc = launch_tf32_inst<10>(a, grid, smem, stream); break;
+    case 11: rc = launch_tf32_inst<11>(a, grid, smem, stream); break;
+    default: set_error("tf32 kernel: unsupported K extent %d", a.KU); return 1;
+  }
+  if (rc) return rc;
   ExactArgs e{};
   e.X = pa.X; e.xn = pa.xn; e.rot = pa.rot; e.aniso = pa.aniso;
   e.cand = a.cand; e.cand_count = tb.cand_count; e.cand_cap = tb.cand_cap;
