@@ -36,9 +36,16 @@ namespace crest {
 constexpr int kTfThreads = 320;
 constexpr int kTfEpiWarps = 8;
 constexpr int kTfBStagesMax = 8;
-constexpr int kTfDStages = 2;          // TMEM accumulator stages
-constexpr int kTfAccStride = 64;       // TMEM columns between the three accumulators of a stage
-constexpr int kTfStageStride = 256;    // TMEM columns between stages
+constexpr int kTfAccStride = 48;       // TMEM columns between the three accumulators of a stage
+constexpr int kTfStageStride = 160;    // TMEM columns between accumulator stages (3 x 48 + pad)
+constexpr int kTfDStagesMax = 3;
+// A operand placement.  K <= 64 ("TS"): the i-tile lives in TMEM (lane = conformer, column = atom
+// slot, 3 x K columns) next to TWO accumulator stages, and an MMA reads only its 1.5 KB B slice from
+// shared memory.  K > 64 ("SS"): A stays in shared memory (4 KB re-read per MMA, smem-bound) with
+// THREE accumulator stages.  512 columns either way.
+__host__ __device__ constexpr bool tf_ts_mode(int ksteps) { return ksteps <= 8; }
+__host__ __device__ constexpr int tf_d_stages(int ksteps) { return tf_ts_mode(ksteps) ? 2 : 3; }
+__host__ __device__ constexpr int tf_d_base(int ksteps) { return tf_ts_mode(ksteps) ? 192 : 0; }
 constexpr int kTfCols = 512;
 
 // ---- tcgen05 primitives (sm_100a PTX) ------------------------------------------------------
@@ -58,6 +65,22 @@ __device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uin
       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
       "}\n" ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// same, A operand in TMEM (lane = row, 8 columns = the K extent of one TF32 MMA)
+__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc,
+                                               uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n"
+      "}\n" ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_st8(uint32_t taddr, const uint32_t (&v)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]),
+                 "r"(v[6]), "r"(v[7]) : "memory");
+}
+__device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_ld8(uint32_t taddr, uint32_t (&v)[8]) {
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
@@ -96,6 +119,7 @@ struct TfArgs {
   float cE;               // -0.5 * E2_up
   double ethr;
   int enantio;
+  int dbg;                // timing experiments (CREST_CUDA_DEBUG=4: no screen arithmetic, 5: no MMAs)
   int all_cand;           // debug: every pair goes to the exact kernel, bit 31 of j = screen said far
   int2* cand;             // candidate list
   unsigned cand_cap;
@@ -107,9 +131,12 @@ template <int KSTEPS>
 __global__ void __launch_bounds__(kTfThreads, 1)
 pair_tf32_kernel(const TfArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  __shared__ __align__(8) uint64_t a_full, a_empty;
+  __shared__ __align__(8) uint64_t a_full, a_empty, at_full, at_empty;
+  constexpr bool TS = tf_ts_mode(KSTEPS);
+  constexpr int kTfDStages = tf_d_stages(KSTEPS);
+  constexpr uint32_t kDBase = (uint32_t)tf_d_base(KSTEPS);
   __shared__ __align__(8) uint64_t b_full[kTfBStagesMax], b_empty[kTfBStagesMax];
-  __shared__ __align__(8) uint64_t d_full[kTfDStages], d_empty[kTfDStages];
+  __shared__ __align__(8) uint64_t d_full[kTfDStagesMax], d_empty[kTfDStagesMax];
   __shared__ uint32_t tmem_base_smem;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -123,9 +150,11 @@ pair_tf32_kernel(const TfArgs a) {
 
   if (threadIdx.x == 0) {
     mbar_init(&a_full, 1);
-    mbar_init(&a_empty, 1);
+    mbar_init(&a_empty, TS ? 4 : 1);
+    mbar_init(&at_full, 4);
+    mbar_init(&at_empty, 1);
     for (int s = 0; s < nbs; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
-    for (int t = 0; t < kTfDStages; ++t) { mbar_init(&d_full[t], 1); mbar_init(&d_empty[t], kTfEpiWarps); }
+    for (int t = 0; t < kTfDStages; ++t) { mbar_init(&d_full[t], 1); mbar_init(&d_empty[t], kTfEpiWarps / 2); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 8) {
@@ -166,105 +195,153 @@ pair_tf32_kernel(const TfArgs a) {
     constexpr uint32_t desc_hi = (128u >> 4) | (1u << 14);      // SBO = 128 B, version 1
     for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
       const int g_begin = a.items[k].g_begin, g_end = a.items[k].g_end;
-      mbar_wait(&a_full, pha);
+      mbar_wait(TS ? &at_full : &a_full, pha);         // i-tile in TMEM (TS) / in shared memory (SS)
       pha ^= 1;
       for (int g = g_begin; g < g_end; ++g) {
         mbar_wait(&d_empty[td], phd ^ 1);              // epilogue drained this TMEM stage
         mbar_wait(&b_full[sb], phb);
         tc_fence_after();
-        if (elect_one()) {
+        if (a.dbg != 5 && elect_one()) {
           const uint32_t b_lo0 = b_lo00 + sb * (b_bytes >> 4);
-          const uint32_t d0 = tmem_base + td * kTfStageStride;
+          const uint32_t d0 = tmem_base + kDBase + td * kTfStageStride;
 #pragma unroll
           for (int ks = 0; ks < KSTEPS; ++ks) {
             const uint64_t bdesc = ((uint64_t)desc_hi << 32) | (b_lo0 + (uint32_t)ks * (2u * 768u >> 4));
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
-              const uint64_t adesc = ((uint64_t)desc_hi << 32) |
-                                     (a_lo0 + (((uint32_t)c * a_comp_bytes + (uint32_t)ks * 4096u) >> 4));
-              tc_mma_tf32(d0 + (uint32_t)(c * kTfAccStride), adesc, bdesc, kTfIdesc, ks > 0 ? 1u : 0u);
+              if (TS) {
+                tc_mma_tf32_ts(d0 + (uint32_t)(c * kTfAccStride),
+                               tmem_base + (uint32_t)(c * 8 * KSTEPS + ks * 8), bdesc, kTfIdesc,
+                               ks > 0 ? 1u : 0u);
+              } else {
+                const uint64_t adesc = ((uint64_t)desc_hi << 32) |
+                                       (a_lo0 + (((uint32_t)c * a_comp_bytes + (uint32_t)ks * 4096u) >> 4));
+                tc_mma_tf32(d0 + (uint32_t)(c * kTfAccStride), adesc, bdesc, kTfIdesc, ks > 0 ? 1u : 0u);
+              }
             }
           }
           tc_commit(&b_empty[sb]);     // smem slot reusable once these MMAs have read it
           tc_commit(&d_full[td]);      // accumulators of this group complete
+        } else if (a.dbg == 5 && elect_one()) {
+          tc_commit(&b_empty[sb]);
+          tc_commit(&d_full[td]);
         }
         __syncwarp();
         if (++sb == (uint32_t)nbs) { sb = 0; phb ^= 1; }
-        td ^= 1; if (td == 0) phd ^= 1;
+        if (++td == (uint32_t)kTfDStages) { td = 0; phd ^= 1; }
       }
-      if (elect_one()) tc_commit(&a_empty);            // i-tile reusable once every MMA of the item is done
+      if (elect_one()) tc_commit(TS ? &at_empty : &a_empty);   // i-tile reusable once every MMA of the item is done
       __syncwarp();
     }
   } else {
     // ===================== epilogue: TMEM -> registers -> FP32 screen -> candidate list ======
-    const int q = warp & 3, h = warp >> 2;       // TMEM lane quarter, j half of the group
-    uint32_t nd = 0;
+    // Warps 0-3 take the even groups of this CTA's group stream, warps 4-7 the odd ones (each warp a
+    // whole group = 16 pairs per lane, in two halves), so the two epilogue warps of an SM
+    // sub-partition are out of phase: one waits for TMEM while the other runs its screen.
+    const int q = warp & 3, wg = warp >> 2;      // TMEM lane quarter, group parity
+    uint32_t n = 0, pht = 0;
     unsigned long long my_pairs = 0;
     for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
       const TfItem item = a.items[k];
       const int i = item.I * 128 + q * 32 + lane;
       const bool iok = i < a.nall;
       const float hi = a.hn[i];
-      for (int g = item.g_begin; g < item.g_end; ++g) {
-        const int t = nd % kTfDStages;
-        const int j0 = g * 16 + h * 8;
-        const float4 h0 = __ldg(reinterpret_cast<const float4*>(a.hn + j0));
-        const float4 h1 = __ldg(reinterpret_cast<const float4*>(a.hn + j0 + 4));
-        const float hj[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
-        mbar_wait(&d_full[t], (nd / kTfDStages) & 1);
-        ++nd;
+      if (TS && wg == 0) {
+        // move the i-tile shared memory -> TMEM: this lane's row, 3 x K columns.  The previous
+        // tile's MMAs must have completed (at_empty), the new tile must have landed (a_full).
+        mbar_wait(&at_empty, pht ^ 1);
+        mbar_wait(&a_full, pht);
+        pht ^= 1;
         tc_fence_after();
-        uint32_t v[9][8];
-        const uint32_t tad = tmem_base + ((uint32_t)(q * 32) << 16) +
-                             (uint32_t)(t * kTfStageStride + h * 8);
+        const int row = q * 32 + lane;
 #pragma unroll
         for (int c = 0; c < 3; ++c)
 #pragma unroll
-          for (int b = 0; b < 3; ++b) tc_ld8(tad + (uint32_t)(c * kTfAccStride + b * 16), v[3 * c + b]);
-        tc_wait_ld();
+          for (int ks = 0; ks < KSTEPS; ++ks) {
+            const uint4 lo = *reinterpret_cast<const uint4*>(sA + ((size_t)(c * nchunk + 2 * ks) * 128 + row) * 16);
+            const uint4 up = *reinterpret_cast<const uint4*>(sA + ((size_t)(c * nchunk + 2 * ks + 1) * 128 + row) * 16);
+            const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, up.x, up.y, up.z, up.w};
+            tc_st8(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 8 * KSTEPS + ks * 8), w);
+          }
+        tc_wait_st();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&d_empty[t]);
-        // which pairs count: j < i, inside the ensemble, inside the energy band (cregen.f90:1275)
-        unsigned ok = iok ? 0xFFu : 0u;
-        const bool slow = (g < item.g_gate_end) || (g * 16 + 15 >= item.I * 128);
-        if (slow) {
-          ok = 0;
-          const bool gate = g < item.g_gate_end;
-          const double eri = gate && iok ? a.er[i] : 0.0;
-#pragma unroll
-          for (int p = 0; p < 8; ++p) {
-            const int j = j0 + p;
-            bool o = iok && (j < i);
-            if (o && gate) o = __dmul_rn(__dsub_rn(eri, a.er[j]), kAutokcal) < a.ethr;
-            ok |= (o ? 1u : 0u) << p;
-          }
-        }
-        my_pairs += __popc(ok);
-        unsigned cand = 0, farbits = 0;
-#pragma unroll
-        for (int p = 0; p < 8; ++p) {
-          float rf[9];
-#pragma unroll
-          for (int z = 0; z < 9; ++z) rf[z] = __uint_as_float(v[z][p]);
-          const float lam_f = __fadd_rd(__fadd_rd(hi, hj[p]), a.cE);
-          const bool far = (lam_f < 6.0e29f) & screen_far_f32(rf, lam_f, a.enantio);
-          farbits |= (far ? 1u : 0u) << p;
-          if (!far) cand |= 1u << p;
-        }
-        if (a.all_cand) cand = 0xFFu;
-        cand &= ok;
-        if (cand) {
+        if (lane == 0) { mbar_arrive(&at_full); mbar_arrive(&a_empty); }
+      }
+      for (int g = item.g_begin; g < item.g_end; ++g) {
+        const uint32_t my = n++;
+        if ((int)(my & 1u) != wg) continue;
+        const uint32_t t = my % kTfDStages, ph = (my / kTfDStages) & 1u;
+        const bool gate = g < item.g_gate_end;
+        const bool slow = gate || (g * 16 + 15 >= item.I * 128);
+        const double eri = gate && iok ? a.er[i] : 0.0;
+        mbar_wait(&d_full[t], ph);
+        tc_fence_after();
 #pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+          const int j0 = g * 16 + h * 8;
+          const float4 h0 = __ldg(reinterpret_cast<const float4*>(a.hn + j0));
+          const float4 h1 = __ldg(reinterpret_cast<const float4*>(a.hn + j0 + 4));
+          const float hj[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+          uint32_t v[9][8];
+          const uint32_t tad = tmem_base + ((uint32_t)(q * 32) << 16) +
+                               kDBase + (uint32_t)(t * kTfStageStride + h * 8);
+#pragma unroll
+          for (int c = 0; c < 3; ++c)
+#pragma unroll
+            for (int b = 0; b < 3; ++b) tc_ld8(tad + (uint32_t)(c * kTfAccStride + b * 16), v[3 * c + b]);
+          tc_wait_ld();
+          if (h == 1) {                          // both halves are in registers: hand the stage back
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&d_empty[t]);
+          }
+          // which pairs count: j < i, inside the ensemble, inside the energy band (cregen.f90:1275)
+          unsigned ok = iok ? 0xFFu : 0u;
+          if (slow) {
+            ok = 0;
+#pragma unroll
+            for (int p = 0; p < 8; ++p) {
+              const int j = j0 + p;
+              bool o = iok && (j < i);
+              if (o && gate) o = __dmul_rn(__dsub_rn(eri, a.er[j]), kAutokcal) < a.ethr;
+              ok |= (o ? 1u : 0u) << p;
+            }
+          }
+          my_pairs += __popc(ok);
+          unsigned cand = 0, farbits = 0;
+          if (a.dbg == 4) {              // timing experiment: keep the loads live, skip the screen
+            unsigned x = 0;
+#pragma unroll
+            for (int z = 0; z < 9; ++z)
+#pragma unroll
+              for (int p = 0; p < 8; ++p) x ^= v[z][p];
+            if (x == 0x12345678u) cand = 1;
+          } else
+#pragma unroll
           for (int p = 0; p < 8; ++p) {
-            if (!((cand >> p) & 1u)) continue;
-            const unsigned idx = atomicAdd(a.cand_count, 1u);
-            if (idx < a.cand_cap) {
-              int jj = j0 + p;
-              if (a.all_cand && ((farbits >> p) & 1u)) jj |= (int)0x80000000u;
-              a.cand[idx] = make_int2(i, jj);
-            } else {
-              a.cand_count[1] = 1u;
+            float rf[9];
+#pragma unroll
+            for (int z = 0; z < 9; ++z) rf[z] = __uint_as_float(v[z][p]);
+            const float lam_f = __fadd_rd(__fadd_rd(hi, hj[p]), a.cE);
+            const bool far = (lam_f < 6.0e29f) & screen_far_f32(rf, lam_f, a.enantio);
+            farbits |= (far ? 1u : 0u) << p;
+            if (!far) cand |= 1u << p;
+          }
+          if (a.all_cand) cand = 0xFFu;
+          cand &= ok;
+          if (cand) {
+#pragma unroll 1
+            for (int p = 0; p < 8; ++p) {
+              if (!((cand >> p) & 1u)) continue;
+              const unsigned idx = atomicAdd(a.cand_count, 1u);
+              if (idx < a.cand_cap) {
+                int jj = j0 + p;
+                if (a.all_cand && ((farbits >> p) & 1u)) jj |= (int)0x80000000u;
+                a.cand[idx] = make_int2(i, jj);
+              } else {
+                a.cand_count[1] = 1u;
+              }
             }
           }
         }
@@ -426,7 +503,7 @@ int launch_pair_tf32(const PairArgs& pa, const Tf32Buffers& tb, const void* d_it
   if (ns < 2) { set_error("tf32 kernel: K extent %d does not fit shared memory", a.KU); return 1; }
   a.nbstage = ns;
   a.cE = -0.5f * pa.g.E2_up;
-  a.ethr = pa.g.ethr; a.enantio = pa.g.enantio; a.all_cand = all_cand;
+  a.ethr = pa.g.ethr; a.enantio = pa.g.enantio; a.all_cand = all_cand; a.dbg = pa.g.debug;
   a.cand = static_cast<int2*>(tb.cand); a.cand_cap = tb.cand_cap; a.cand_count = tb.cand_count;
   a.npairs = pa.npairs;
   int dev = 0, nsm = 148;

@@ -1,0 +1,6 @@
+#!/bin/bash
+mkdir -p gpurun_out
+for d in 0 4 5; do
+CREST_CUDA_DEBUG=$d timeout 300 python bench.py --no-cpu-baseline --no-e2e --steps 3 2>/dev/null | python -c "
+import json,sys; d=json.loads(sys.stdin.read()); print('debug=$d', 'pair_stage_ms', d['kernels']['pair_stage_ms'])"
+done
