@@ -20,21 +20,29 @@
 // lambda_max(R) < lam*.  B200's FP64 tensor path tops out at ~36 TFLOP/s; the TF32 path is >20x
 // wider, which moves the bound of this stage from the DMMA pipe to the FP32 screen arithmetic.
 //
-// Shape: a CTA keeps one i-tile (128 conformers, all K, 3 components = 3 A operands [128 x K]) in
-// shared memory and streams j-groups of 16 conformers past it; a j-group is ONE B operand
-// [48 x K] (row n = 16*b + jj), so three MMAs per K step (N = 48) leave, in TMEM lane i, the full
-// 3x3 covariance of the 16 pairs (i, j0..j0+15): D_a[i][16 b + jj].  Operands are written by
-// tf32_convert_kernel in the canonical no-swizzle K-major core-matrix layout, so one 1-D bulk copy
-// (TMA engine) brings a tile/group in exactly the byte order the UMMA descriptor describes.
-// Warp roles: warps 0-7 epilogue (TMEM -> registers -> screen), warp 8 producer, warp 9 MMA issuer.
+// Shape: a CTA owns one i-tile (128 conformers, all K, 3 components = 3 A operands [128 x K]) and
+// streams j-groups of 16 conformers past it; a j-group is ONE B operand [48 x K] (row n = 16*b + jj),
+// so three MMAs per K step (M = 128, N = 48, K = 8) leave, in TMEM lane i, the full 3x3 covariance of
+// the 16 pairs (i, j0..j0+15): D_a[i][16 b + jj].  Operands are written by tf32_convert_kernel in the
+// canonical no-swizzle K-major core-matrix layout, so one 1-D bulk copy (TMA engine) brings a
+// tile/group in exactly the byte order the UMMA descriptor describes.  For K <= 64 the i-tile is moved
+// once per work item from shared memory into TMEM (tcgen05.st) and the MMAs take A from TMEM: an MMA
+// then reads only its 1.5 KB B slice from shared memory instead of 5.5 KB (measured: MMA path alone
+// 12.8 ms -> 8.2 ms on C3).
+// Warp roles: warps 0-15 epilogue (TMEM -> registers -> screen), warp 16 producer (bulk copies),
+// warp 17 MMA issuer (one elected lane).  Pipelines: B ring (producer <-> MMA, mbarrier + tcgen05.commit),
+// TMEM accumulator stages (MMA <-> epilogue), i-tile (producer -> epilogue warps 0-3 -> MMA).
+// Measured bound: per j-group an SM moves 72 KB TMEM -> registers (~128 B/clk) and
+// issues ~880 clk of packed FP32 arithmetic per sub-partition; the two do not overlap on B200, so the
+// kernel runs at ~1500 clk per 2048 pairs.
 #include "common.cuh"
 #include "qcp.cuh"
 #include "pipe.cuh"
 
 namespace crest {
 
-constexpr int kTfThreads = 320;
-constexpr int kTfEpiWarps = 8;
+constexpr int kTfEpiWarps = 16;        // (TMEM lane quarter q) x (quarter s of the 16 j's of a group)
+constexpr int kTfThreads = (kTfEpiWarps + 2) * 32;
 constexpr int kTfBStagesMax = 8;
 constexpr int kTfAccStride = 48;       // TMEM columns between the three accumulators of a stage
 constexpr int kTfStageStride = 160;    // TMEM columns between accumulator stages (3 x 48 + pad)
@@ -104,6 +112,18 @@ __device__ __forceinline__ uint64_t umma_desc_kmajor(uint32_t smem_addr, uint32_
 // instruction descriptor (cute::UMMA::InstrDescriptor): D=F32, A=B=TF32, both K-major, M=128, N=48
 constexpr uint32_t kTfIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((48u >> 3) << 17) | ((128u >> 4) << 24);
 
+__device__ __forceinline__ void tc_ld4(uint32_t taddr, uint32_t (&v)[4]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(taddr));
+}
+// 9 x (32 lanes x 4 columns) TMEM loads: v[3c+b][p] = R_cb of pair (lane, p), a batch of 4 pairs
+__device__ __forceinline__ void ld_batch(uint32_t taddr, uint32_t (&v)[9][4]) {
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int b = 0; b < 3; ++b) tc_ld4(taddr + (uint32_t)(c * kTfAccStride + b * 16), v[3 * c + b]);
+}
+
 struct TfItem { int I; int g_begin; int g_end; int g_gate_end; };
 
 struct TfArgs {
@@ -119,13 +139,70 @@ struct TfArgs {
   float cE;               // -0.5 * E2_up
   double ethr;
   int enantio;
-  int dbg;                // timing experiments (CREST_CUDA_DEBUG=4: no screen arithmetic, 5: no MMAs)
+  int dbg;                // timing experiments (CREST_CUDA_DEBUG=4: no screen arithmetic, 5: no MMAs, 6: neither)
   int all_cand;           // debug: every pair goes to the exact kernel, bit 31 of j = screen said far
   int2* cand;             // candidate list
   unsigned cand_cap;
   unsigned* cand_count;   // [0] = appended, [1] = overflow flag, [2] = screen violations (debug)
   unsigned long long* npairs;
 };
+
+// FP32 screen of the 4 pairs (i, j0..j0+3) of this lane + candidate emission
+__device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v)[9][4], int j0, int i,
+                                             bool iok, float hi, bool gate, bool slow,
+                                             unsigned long long& my_pairs) {
+  const float4 h0 = __ldg(reinterpret_cast<const float4*>(a.hn + j0));
+  const float hj[4] = {h0.x, h0.y, h0.z, h0.w};
+  // which pairs count: j < i, inside the ensemble, inside the energy band (cregen.f90:1275)
+  unsigned ok = iok ? 0xFu : 0u;
+  if (slow) {
+    ok = 0;
+    const double eri = gate && iok ? a.er[i] : 0.0;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const int j = j0 + p;
+      bool o = iok && (j < i);
+      if (o && gate) o = __dmul_rn(__dsub_rn(eri, a.er[j]), kAutokcal) < a.ethr;
+      ok |= (o ? 1u : 0u) << p;
+    }
+  }
+  my_pairs += __popc(ok);
+  unsigned farbits = 0;
+  if (a.dbg == 4 || a.dbg >= 6) {   // timing experiment: keep the loads live, skip the screen
+    unsigned x = 0;
+#pragma unroll
+    for (int z = 0; z < 9; ++z)
+#pragma unroll
+      for (int p = 0; p < 4; ++p) x ^= v[z][p];
+    farbits = (x == 0x12345678u) ? 0xEu : 0xFu;
+  } else {
+#pragma unroll
+    for (int p = 0; p < 4; p += 2) {     // two pairs per packed instruction (qcp.cuh)
+      f2_t rp[9];
+#pragma unroll
+      for (int z = 0; z < 9; ++z) rp[z] = f2_pack_u(v[z][p], v[z][p + 1]);
+      const f2_t lam2 = f2_pack(__fadd_rd(__fadd_rd(hi, hj[p]), a.cE),
+                                __fadd_rd(__fadd_rd(hi, hj[p + 1]), a.cE));
+      farbits |= screen_far_f32x2(rp, lam2, a.enantio) << p;
+    }
+  }
+  unsigned cand = a.all_cand ? 0xFu : (~farbits & 0xFu);
+  cand &= ok;
+  if (cand) {
+#pragma unroll 1
+    for (int p = 0; p < 4; ++p) {
+      if (!((cand >> p) & 1u)) continue;
+      const unsigned idx = atomicAdd(a.cand_count, 1u);
+      if (idx < a.cand_cap) {
+        int jj = j0 + p;
+        if (a.all_cand && ((farbits >> p) & 1u)) jj |= (int)0x80000000u;
+        a.cand[idx] = make_int2(i, jj);
+      } else {
+        a.cand_count[1] = 1u;
+      }
+    }
+  }
+}
 
 template <int KSTEPS>
 __global__ void __launch_bounds__(kTfThreads, 1)
@@ -154,10 +231,10 @@ pair_tf32_kernel(const TfArgs a) {
     mbar_init(&at_full, 4);
     mbar_init(&at_empty, 1);
     for (int s = 0; s < nbs; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
-    for (int t = 0; t < kTfDStages; ++t) { mbar_init(&d_full[t], 1); mbar_init(&d_empty[t], kTfEpiWarps / 2); }
+    for (int t = 0; t < kTfDStages; ++t) { mbar_init(&d_full[t], 1); mbar_init(&d_empty[t], kTfEpiWarps); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 8) {
+  if (warp == kTfEpiWarps) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
                  ::"r"(smem_u32(&tmem_base_smem)), "r"((uint32_t)kTfCols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -167,7 +244,7 @@ pair_tf32_kernel(const TfArgs a) {
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
 
-  if (warp == 8) {
+  if (warp == kTfEpiWarps) {
     // ===================== producer: bulk copies of the i-tile and the j-group ring ==========
     if (lane == 0) {
       uint32_t sb = 0, phb = 0, pha = 0;
@@ -185,7 +262,7 @@ pair_tf32_kernel(const TfArgs a) {
         }
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == kTfEpiWarps + 1) {
     // ===================== MMA issuer: the warp runs the control flow, ONE elected lane issues
     // 3 x KSTEPS tcgen05.mma per j-group.  Descriptors differ only in the 14-bit start-address
     // field, so every MMA of the unrolled block is base + compile-time constant.
@@ -201,7 +278,7 @@ pair_tf32_kernel(const TfArgs a) {
         mbar_wait(&d_empty[td], phd ^ 1);              // epilogue drained this TMEM stage
         mbar_wait(&b_full[sb], phb);
         tc_fence_after();
-        if (a.dbg != 5 && elect_one()) {
+        if (a.dbg < 5 && elect_one()) {
           const uint32_t b_lo0 = b_lo00 + sb * (b_bytes >> 4);
           const uint32_t d0 = tmem_base + kDBase + td * kTfStageStride;
 #pragma unroll
@@ -222,7 +299,7 @@ pair_tf32_kernel(const TfArgs a) {
           }
           tc_commit(&b_empty[sb]);     // smem slot reusable once these MMAs have read it
           tc_commit(&d_full[td]);      // accumulators of this group complete
-        } else if (a.dbg == 5 && elect_one()) {
+        } else if (a.dbg >= 5 && elect_one()) {
           tc_commit(&b_empty[sb]);
           tc_commit(&d_full[td]);
         }
@@ -235,10 +312,11 @@ pair_tf32_kernel(const TfArgs a) {
     }
   } else {
     // ===================== epilogue: TMEM -> registers -> FP32 screen -> candidate list ======
-    // Warps 0-3 take the even groups of this CTA's group stream, warps 4-7 the odd ones (each warp a
-    // whole group = 16 pairs per lane, in two halves), so the two epilogue warps of an SM
-    // sub-partition are out of phase: one waits for TMEM while the other runs its screen.
-    const int q = warp & 3, wg = warp >> 2;      // TMEM lane quarter, group parity
+    // Four epilogue warps per TMEM lane quarter q, one per quarter s of a group's 16 j's: a warp
+    // pulls its 4 pairs per lane (36 registers of covariance) out of TMEM, hands the accumulator
+    // stage back at once and screens them.  Four warps per SM sub-partition at different points of
+    // wait / load / screen keep the FMA pipe fed.
+    const int q = warp & 3, sq = warp >> 2;
     uint32_t n = 0, pht = 0;
     unsigned long long my_pairs = 0;
     for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
@@ -246,7 +324,7 @@ pair_tf32_kernel(const TfArgs a) {
       const int i = item.I * 128 + q * 32 + lane;
       const bool iok = i < a.nall;
       const float hi = a.hn[i];
-      if (TS && wg == 0) {
+      if (TS && warp < 4) {
         // move the i-tile shared memory -> TMEM: this lane's row, 3 x K columns.  The previous
         // tile's MMAs must have completed (at_empty), the new tile must have landed (a_full).
         mbar_wait(&at_empty, pht ^ 1);
@@ -268,83 +346,21 @@ pair_tf32_kernel(const TfArgs a) {
         __syncwarp();
         if (lane == 0) { mbar_arrive(&at_full); mbar_arrive(&a_empty); }
       }
+      const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + kDBase + (uint32_t)(sq * 4);
       for (int g = item.g_begin; g < item.g_end; ++g) {
         const uint32_t my = n++;
-        if ((int)(my & 1u) != wg) continue;
         const uint32_t t = my % kTfDStages, ph = (my / kTfDStages) & 1u;
         const bool gate = g < item.g_gate_end;
         const bool slow = gate || (g * 16 + 15 >= item.I * 128);
-        const double eri = gate && iok ? a.er[i] : 0.0;
+        uint32_t v[9][4];
         mbar_wait(&d_full[t], ph);
         tc_fence_after();
-#pragma unroll 1
-        for (int h = 0; h < 2; ++h) {
-          const int j0 = g * 16 + h * 8;
-          const float4 h0 = __ldg(reinterpret_cast<const float4*>(a.hn + j0));
-          const float4 h1 = __ldg(reinterpret_cast<const float4*>(a.hn + j0 + 4));
-          const float hj[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
-          uint32_t v[9][8];
-          const uint32_t tad = tmem_base + ((uint32_t)(q * 32) << 16) +
-                               kDBase + (uint32_t)(t * kTfStageStride + h * 8);
-#pragma unroll
-          for (int c = 0; c < 3; ++c)
-#pragma unroll
-            for (int b = 0; b < 3; ++b) tc_ld8(tad + (uint32_t)(c * kTfAccStride + b * 16), v[3 * c + b]);
-          tc_wait_ld();
-          if (h == 1) {                          // both halves are in registers: hand the stage back
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&d_empty[t]);
-          }
-          // which pairs count: j < i, inside the ensemble, inside the energy band (cregen.f90:1275)
-          unsigned ok = iok ? 0xFFu : 0u;
-          if (slow) {
-            ok = 0;
-#pragma unroll
-            for (int p = 0; p < 8; ++p) {
-              const int j = j0 + p;
-              bool o = iok && (j < i);
-              if (o && gate) o = __dmul_rn(__dsub_rn(eri, a.er[j]), kAutokcal) < a.ethr;
-              ok |= (o ? 1u : 0u) << p;
-            }
-          }
-          my_pairs += __popc(ok);
-          unsigned cand = 0, farbits = 0;
-          if (a.dbg == 4) {              // timing experiment: keep the loads live, skip the screen
-            unsigned x = 0;
-#pragma unroll
-            for (int z = 0; z < 9; ++z)
-#pragma unroll
-              for (int p = 0; p < 8; ++p) x ^= v[z][p];
-            if (x == 0x12345678u) cand = 1;
-          } else
-#pragma unroll
-          for (int p = 0; p < 8; ++p) {
-            float rf[9];
-#pragma unroll
-            for (int z = 0; z < 9; ++z) rf[z] = __uint_as_float(v[z][p]);
-            const float lam_f = __fadd_rd(__fadd_rd(hi, hj[p]), a.cE);
-            const bool far = (lam_f < 6.0e29f) & screen_far_f32(rf, lam_f, a.enantio);
-            farbits |= (far ? 1u : 0u) << p;
-            if (!far) cand |= 1u << p;
-          }
-          if (a.all_cand) cand = 0xFFu;
-          cand &= ok;
-          if (cand) {
-#pragma unroll 1
-            for (int p = 0; p < 8; ++p) {
-              if (!((cand >> p) & 1u)) continue;
-              const unsigned idx = atomicAdd(a.cand_count, 1u);
-              if (idx < a.cand_cap) {
-                int jj = j0 + p;
-                if (a.all_cand && ((farbits >> p) & 1u)) jj |= (int)0x80000000u;
-                a.cand[idx] = make_int2(i, jj);
-              } else {
-                a.cand_count[1] = 1u;
-              }
-            }
-          }
-        }
+        ld_batch(lane_base + t * kTfStageStride, v);
+        tc_wait_ld();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&d_empty[t]);       // this warp's 4 pairs are in registers
+        screen_batch(a, v, g * 16 + sq * 4, i, iok, hi, gate, slow, my_pairs);
       }
     }
 #pragma unroll
@@ -353,7 +369,7 @@ pair_tf32_kernel(const TfArgs a) {
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) {
+  if (warp == kTfEpiWarps) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;"
                  ::"r"(tmem_base), "r"((uint32_t)kTfCols) : "memory");
   }
