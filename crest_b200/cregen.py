@@ -98,6 +98,18 @@ def band_tiles(er, ethr):
     return np.array(ti, np.int64), np.array(tj, np.int64), rowstart, jfirst[:nI]
 
 
+def tf32_items(er, ethr):
+    """Host-only: work list of the tensor-core screen kernel, (n,4) int32 rows
+    {I, g_begin, g_end, g_gate_end} (see include/crest_cuda.h)."""
+    L = _lib.lib()
+    er = np.ascontiguousarray(er, np.float64)
+    n = C.c_longlong(0)
+    _lib.check(L.crest_cuda_tf32_items(len(er), _dp(er), float(ethr), None, 0, C.byref(n)))
+    items = np.zeros((max(n.value, 1), 4), np.int32)
+    _lib.check(L.crest_cuda_tf32_items(len(er), _dp(er), float(ethr), _ip(items), n.value, C.byref(n)))
+    return items[: n.value]
+
+
 def shard_range(ntiles, rank, nranks):
     """Host-only: [begin, end) of the tile list owned by `rank` of `nranks`."""
     b, e = C.c_longlong(0), C.c_longlong(0)

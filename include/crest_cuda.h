@@ -152,6 +152,13 @@ int crest_cuda_band_tiles(int nall, const double* er, double ethr, long long* ro
                           int* jfirst, long long* ntiles);
 int crest_cuda_shard_range(long long ntiles, int rank, int nranks, long long* begin,
                            long long* end);
+/* Work list of the tensor-core screen kernel (host-only): quadruples {I, g_begin, g_end,
+ * g_gate_end}: i-tile I = conformers 128*I .. 128*I+127 against the j-groups g (16 conformers
+ * each) in [g_begin, g_end); groups below g_gate_end hold pairs that can fail the energy gate
+ * (cregen.f90:1275) and are gated pair by pair.  items may be NULL to query the count; cap is the
+ * capacity of items in quadruples. */
+int crest_cuda_tf32_items(int nall, const double* er, double ethr, int* items, long long cap,
+                          long long* nitems);
 
 /* Developer knobs (same syntax as the CREST_CUDA_TUNE environment variable; NULL = defaults):
  * "notf32" forces the FP64 (DMMA) pair kernels, "tile" the row-tile kernel, "cap=<n>" the candidate

@@ -95,6 +95,35 @@ def test_host_band_tiles(cuda_lib):
             assert max(sizes) - min(sizes) <= 1
 
 
+def test_host_tf32_items(cuda_lib):
+    """crest_cuda_tf32_items (host-only): the (i-tile, j-group range) work list of the tensor-core
+    screen covers every pair that passes the reference's energy gate (cregen.f90:1245-1255,1275)
+    exactly once, and pairs in groups at or above g_gate_end need no per-pair gate."""
+    from crest_b200 import cregen as cg
+    rng = np.random.default_rng(3)
+    for n, ethr in ((1, 1.0), (2, 1e9), (17, 1e9), (129, 0.05), (300, 0.3), (700, 1e9), (700, 0.02),
+                    (1500, 0.5), (600, 0.0)):
+        er = np.sort(rng.uniform(0, 6.0, n)) / 627.50947428 - 50.0
+        items = cg.tf32_items(er, ethr)
+        cover = np.zeros((n, n), np.int32)
+        nogate = np.zeros((n, n), bool)
+        for I, gb, ge, gg in items:
+            assert 0 <= gb < ge
+            i0, i1 = I * 128, min(I * 128 + 128, n)
+            j0, j1 = gb * 16, min(ge * 16, n)
+            cover[i0:i1, j0:j1] += 1
+            jn = max(j0, gg * 16)
+            if jn < j1:
+                nogate[i0:i1, jn:j1] = True
+        i, j = np.tril_indices(n, -1)
+        gate = (er[i] - er[j]) * 627.50947428 < ethr
+        assert np.all(cover[i[gate], j[gate]] == 1), (n, ethr)
+        assert cover.max() <= 1
+        assert np.all(gate[nogate[i, j]]), (n, ethr)          # un-gated groups hold in-band pairs only
+        if n >= 2 and ethr > 1e8:
+            assert len(items) >= 1
+
+
 def test_argument_checks(cuda_lib):
     # NULL thresholds / bad sizes are rejected before any device work
     rc = cuda_lib.crest_cuda_cregen_dup(3, 2, None, None, None, None, 0, 1, None, None, None, None,

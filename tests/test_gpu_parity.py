@@ -336,3 +336,129 @@ def test_full_size_properties_c3(cb, oracle):
     ref_rot = oracle.rotconst(at, xyz[rows])
     assert np.abs(rot[rows] / ref_rot - 1).max() < ROT_TOL
     ctx.close()
+
+
+# ------------------------------------------------------------------------------------------------
+# Tensor-core screen (pair_tf32.cu): TF32 covariance on tcgen05 + FP32 screen + exact FP64 list.
+# Its decisions must be THE SAME as those of the FP64 (DMMA) kernels: a pair leaves the FP32 path
+# only with a proof that it is far.
+# ------------------------------------------------------------------------------------------------
+def _stage_a(cb, ens, env, tune=None, debug=None):
+    from crest_b200 import cregen
+    cregen.set_tune(tune)
+    if debug is not None:
+        os.environ["CREST_CUDA_DEBUG"] = str(debug)
+    try:
+        ctx = cb.CregenContext()
+        ctx.upload(env, ens["at"], ens["xyz"], ens["er"])
+        ctx.pack()
+        ctx.pairs(env)
+        links = ctx.download()
+        info = ctx.info(env)
+        ctx.sweep()
+        root = ctx.download()["dup"]
+        ctx.close()
+    finally:
+        os.environ.pop("CREST_CUDA_DEBUG", None)
+        cregen.set_tune(None)
+    return links, root, info
+
+
+@pytest.mark.parametrize("cfg,nall,ethr", [("C1", 1000, 1e9), ("C1", 1000, 0.05), ("C1", 1000, 0.0),
+                                           ("C2", 3000, 1e9), ("C2", 3000, 0.1), ("C5", 5000, 1e9),
+                                           ("C5", 4097, 0.3), ("C3", 20000, 1e9)])
+def test_tf32_equals_fp64_kernels(cb, cfg, nall, ethr):
+    ens = synth.make_config(cfg, nall=nall, seed=99)
+    env = cb.Env(ethr=ethr, heavyrmsd=ens["heavy"])
+    l_tf, r_tf, i_tf = _stage_a(cb, ens, env)
+    l_col, r_col, i_col = _stage_a(cb, ens, env, "notf32")
+    l_til, r_til, i_til = _stage_a(cb, ens, env, "notf32,tile")
+    assert (i_tf["variant"], i_col["variant"], i_til["variant"]) == (2, 1, 0)
+    assert i_tf["overflow"] == 0
+    assert l_tf["npairs"] == l_col["npairs"] == l_til["npairs"]
+    assert np.array_equal(l_tf["dup"], l_col["dup"]) and np.array_equal(l_tf["dup"], l_til["dup"])
+    assert np.array_equal(r_tf, r_col)
+    # the screen decides the overwhelming majority of pairs in FP32
+    if ethr > 1e8 and l_tf["npairs"] > 100000:
+        assert i_tf["candidates"] < 0.01 * l_tf["npairs"]
+
+
+def test_tf32_screen_selfcheck(cb):
+    """CREST_CUDA_DEBUG=3 sends EVERY in-band pair through the exact FP64 pass, tagged with the
+    screen's verdict; `violations` counts pairs the screen called far whose exact e is below the
+    2*rthr threshold.  Rigour of the error bound means 0 - also for straddler-heavy ensembles,
+    the adversarial golden geometries and mirror images."""
+    from crest_b200 import cregen
+    cases = []
+    cases.append((synth.make_config("C1", nall=1000, seed=3), cb.Env(ethr=1e9)))
+    ens = synth.make_ensemble(1400, 40, 40, copies=20, seed=8, frac_straddle=0.6, frac_mirror=0.2)
+    ens["heavy"] = False
+    cases.append((ens, cb.Env(ethr=1e9)))
+    for name in ("adv_chiral", "adv_linear", "adv_planar"):
+        g = np.load(os.path.join(GOLDEN, name + ".npz"))
+        cases.append((dict(at=g["at"], xyz=g["xyz"], er=g["er"], heavy=False),
+                      env_from_kwargs(cb, gold_kwargs(g), g["xyz"].shape[1])))
+    for ens, env in cases:
+        n = len(ens["er"])
+        cregen.set_tune(f"cap={n * n}")
+        try:
+            os.environ["CREST_CUDA_DEBUG"] = "3"
+            ctx = cb.CregenContext()
+            ctx.upload(env, ens["at"], ens["xyz"], ens["er"])
+            ctx.pack()
+            ctx.pairs(env)
+            links = ctx.download()
+            info = ctx.info(env)
+            ctx.close()
+        finally:
+            os.environ.pop("CREST_CUDA_DEBUG", None)
+            cregen.set_tune(None)
+        assert info["variant"] == 2 and info["overflow"] == 0
+        assert info["candidates"] == links["npairs"]          # every pair was re-checked
+        assert info["violations"] == 0
+        ref, _, _ = _stage_a(cb, ens, env, "notf32")
+        assert np.array_equal(links["dup"], ref["dup"])
+
+
+def test_tf32_overflow_falls_back_to_fp64(cb):
+    """A candidate list that is too small must not lose pairs: the launch is re-run on the FP64
+    column kernel (conditional launch, no host round trip)."""
+    ens = synth.make_config("C1", nall=1000, seed=5)
+    env = cb.Env(ethr=1e9)
+    ref, rref, _ = _stage_a(cb, ens, env, "notf32")
+    got, rgot, info = _stage_a(cb, ens, env, "cap=32")
+    assert info["variant"] == 2 and info["overflow"] == 1
+    assert np.array_equal(got["dup"], ref["dup"]) and np.array_equal(rgot, rref)
+    assert got["npairs"] == ref["npairs"]
+
+
+@pytest.mark.parametrize("nall", [2, 15, 16, 17, 127, 128, 129, 255, 257, 1025])
+def test_tf32_ragged_tiles(cb, oracle, nall):
+    """Ensemble sizes around the i-tile (128) and j-group (16) edges, against the oracle."""
+    ens = synth.make_config("C5", nall=nall, seed=31)
+    at, xyz, er = ens["at"], ens["xyz"], ens["er"]
+    env = cb.Env(ethr=1e9)
+    links, root, info = _stage_a(cb, ens, env)
+    assert info["variant"] == 2
+    ref = oracle.cregen_cre(at, xyz, er, ethr=1e9, want_rmat=True)
+    assert links["npairs"] == nall * (nall - 1) // 2
+    listed = boundary_rows(rows_of_allpairs(ref["rmat"], nall), env.rthr)
+    bad = set(np.where(root != ref["dup"])[0].tolist())
+    assert bad <= listed, sorted(bad - listed)
+
+
+def test_tf32_sharded_equals_single(cb):
+    """Contiguous shards of the tensor-core work list (what N ranks run) accumulate to the
+    single-launch result (atomicMax on dup, atomicAdd on the pair counter)."""
+    ens = synth.make_config("C2", nall=2500, seed=12)
+    env = cb.Env(ethr=0.5, heavyrmsd=True)
+    one, _, info = _stage_a(cb, ens, env)
+    assert info["variant"] == 2
+    ctx = cb.CregenContext()
+    ctx.upload(env, ens["at"], ens["xyz"], ens["er"])
+    ctx.pack()
+    for r in range(3):
+        ctx.pairs(env, r, 3)
+    many = ctx.download()
+    ctx.close()
+    assert np.array_equal(many["dup"], one["dup"]) and many["npairs"] == one["npairs"]
