@@ -2,8 +2,9 @@
 """bench.py — RMSD pairs/s of the CREGEN duplicate-sorting hot path on N B200s.
 
 A step = one pass of the hot path over the whole synthetic ensemble, inputs resident in HBM:
-  kernel (1) pack/axis  ->  kernels (2)+(3) pair tiles of this rank's shard of the in-band tile
-  list  ->  all-reduce(MAX) of dup[] over ranks (NCCL, N>1 only)  ->  kernel (4) backtrack.
+  kernel (1) pack/axis + TF32 operand conversion  ->  kernels (2)+(3): tensor-core screen + exact
+  FP64 pass over this rank's shard of the in-band work list  ->  all-reduce(MAX) of dup[] over
+  ranks (NCCL, N>1 only)  ->  kernel (4) backtrack.
 `value` = pairs whose (proper+mirror) RMSD was evaluated by ALL ranks / device time (max over
 ranks).  `e2e` runs the same step from HOST buffers (H2D of xyz/er, D2H of rot/dup) every step.
 `--impl reference` times the CPU restatement of the reference loops (oracle/, OpenMP, all host
@@ -312,11 +313,15 @@ def run_ours(args):
             def e2e_step():
                 return cb.cregen_dup(env, nat, nall, at, xyz_p, er_p, want_xyz=False)
         else:
-            api = ("CregenContext.upload+pack+pairs+all_reduce(MAX)+sweep+download (crest_cuda_ctx_*), "
-                   "host buffers; every rank uploads the whole ensemble")
+            api = ("CregenContext.upload_rows (1/N of xyz per rank over PCIe) + NCCL all_gather + pack + "
+                   "pairs + all_reduce(MAX) + sweep + download (crest_cuda_ctx_*), host buffers")
+
+            rec = 3 * nat
 
             def e2e_step():
-                ctx.upload(env, at, xyz_p, er_p)
+                chunk, first, count = ctx.upload_rows(env, at, xyz_p, er_p, rank, world)
+                full = torch.as_tensor(_DevArray(ctx.xyz_devptr(), chunk * world * rec, "<f8"), device=dev)
+                dist.all_gather_into_tensor(full, full[rank * chunk * rec:(rank + 1) * chunk * rec])
                 step()
                 return ctx.download()
         e2e_step()
@@ -332,7 +337,7 @@ def run_ours(args):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dt = float(tt[0])
         e2e = {"value": pairs_step / dt, "unit": UNIT,
-               "h2d_bytes_per_step": int(xyz.nbytes + er.nbytes + at.nbytes),
+               "h2d_bytes_per_step": int(xyz.nbytes + world * (er.nbytes + at.nbytes)),
                "d2h_bytes_per_step": int(nall * 4 + nall * 24 + 8), "ms_per_step": dt * 1e3,
                "api": api}
         assert np.array_equal(r2["dup"], res["dup"])
@@ -343,6 +348,10 @@ def run_ours(args):
         achieved = 18.0 * A * my_pairs / (pair_ms * 1e-3) / 1e12
         variant = {0: "pair_tile (DMMA row tiles)", 1: "pair_col (DMMA column sweep)",
                    2: "pair_tf32 (tcgen05 TF32 screen) + exact_cand (FP64 list)"}[info["variant"]]
+        # dram__bytes_read.sum + dram__bytes_write.sum of pair_tf32_kernel<8>, one launch, from the
+        # committed ncu --set full capture of this command (profiles/r01_v9_pair_tf32_ncu_full_summary.txt)
+        traffic = (230705408 + 6848000 if (info["variant"] == 2 and args.workload == "C3" and
+                                           args.nall is None and world == 1 and args.ethr > 1e8) else None)
         if info["variant"] == 2:
             peak = tf32_peak_tflops(torch, dev)
             note = ("tensor roofline of the dominant kernel pair_tf32_kernel (tcgen05.mma kind::tf32): "
@@ -369,7 +378,7 @@ def run_ours(args):
                         "atoms_padded": info["A_padded"], "launches_per_step": info["launches"],
                         "exact_candidates": info["candidates"], "overflow": info["overflow"]},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": achieved / peak, "traffic": None,
+                         "frac": achieved / peak, "traffic": traffic,
                          "fp64_tensor_peak": fp64_peak, "fp64_tensor_equiv": achieved / fp64_peak,
                          "note": note},
             "clocks": clocks, "e2e": e2e,

@@ -41,6 +41,8 @@ SYMBOLS = {
     "crest_cuda_ctx_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
     "crest_cuda_ctx_destroy": (None, [C.c_void_p]),
     "crest_cuda_ctx_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_int, c_ip, c_dp, c_dp, c_ip, C.c_int]),
+    "crest_cuda_ctx_upload_xyz_rows": (C.c_int, [C.c_void_p, C.c_int, C.c_int, c_dp]),
+    "crest_cuda_ctx_xyz_devptr": (C.c_void_p, [C.c_void_p]),
     "crest_cuda_ctx_pack": (C.c_int, [C.c_void_p, C.c_void_p]),
     "crest_cuda_ctx_pairs": (C.c_int, [C.c_void_p, C.c_int, _THR, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "crest_cuda_ctx_dup_devptr": (C.c_void_p, [C.c_void_p]),

@@ -249,6 +249,28 @@ class CregenContext:
                                                  _ip(mask), rfm))
         self.nall, self.nat = nall, nat
 
+    def upload_rows(self, env: Env, at, xyz, er, rank, world):
+        """Multi-GPU upload: reserve the ensemble, copy only this rank's slice of xyz host->device.
+        Returns (chunk, first, count); the caller all-gathers `chunk` rows per rank into
+        xyz_devptr() (crest_b200/multi.py)."""
+        at = np.ascontiguousarray(at, np.int32)
+        xyz = np.ascontiguousarray(xyz, np.float64)
+        er = np.ascontiguousarray(er, np.float64)
+        nall, nat, _ = xyz.shape
+        mask, rfm = rmsd_mask(env, nat, at)
+        _lib.check(self._L.crest_cuda_ctx_upload(self._h, nat, nall, _ip(at), None, _dp(er),
+                                                 _ip(mask), rfm))
+        self.nall, self.nat = nall, nat
+        chunk = (nall + world - 1) // world
+        first = min(rank * chunk, nall)
+        count = min(chunk, nall - first)
+        rows = xyz[first:first + count]
+        _lib.check(self._L.crest_cuda_ctx_upload_xyz_rows(self._h, first, count, _dp(rows)))
+        return chunk, first, count
+
+    def xyz_devptr(self):
+        return self._L.crest_cuda_ctx_xyz_devptr(self._h)
+
     def pack(self, stream=0):
         _lib.check(self._L.crest_cuda_ctx_pack(self._h, C.c_void_p(stream)))
 

@@ -414,7 +414,9 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
                           const double* er, const int* rmsd_mask, int rot_from_mask) {
   if (!c) { set_error("ctx is NULL"); return 1; }
   if (nat <= 0 || nall < 0) { set_error("bad sizes nat=%d nall=%d", nat, nall); return 1; }
-  if (!at || (!xyz && nall > 0) || (!er && nall > 0)) { set_error("NULL input array"); return 1; }
+  // xyz == NULL: reserve only; the geometry arrives through crest_cuda_ctx_upload_xyz_rows and/or a
+  // device-side all-gather into crest_cuda_ctx_xyz_devptr (multi-GPU: each rank uploads a slice)
+  if (!at || (!er && nall > 0)) { set_error("NULL input array"); return 1; }
   for (int i = 1; i < nall; ++i)
     if (er[i] < er[i - 1]) {
       set_error("energies must ascend (cregen_esort post-condition): er[%d] < er[%d]", i, i - 1);
@@ -436,7 +438,7 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
   c->h_er.assign(er, er + nall);
   c->tiles_ethr = std::numeric_limits<double>::quiet_NaN();
 
-  const size_t nxyz = (size_t)3 * nat * nall;
+  const size_t nxyz = (size_t)3 * nat * ((size_t)nall + 64);   // 64 rows of slack: equal slices for <= 64 ranks
   if ((size_t)nat > c->cap_at) {
     cudaFree(c->d_at); cudaFree(c->d_sel);
     c->d_at = nullptr; c->d_sel = nullptr; c->cap_at = 0;
@@ -499,11 +501,29 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
   CREST_CUDA_TRY(cudaMemcpy(c->d_at, at, sizeof(int) * nat, cudaMemcpyHostToDevice));
   CREST_CUDA_TRY(cudaMemcpy(c->d_sel, sel.data(), sizeof(int) * sel.size(), cudaMemcpyHostToDevice));
   if (nall > 0) {
-    CREST_CUDA_TRY(cudaMemcpy(c->d_xyz, xyz, sizeof(double) * nxyz, cudaMemcpyHostToDevice));
+    if (xyz)
+      CREST_CUDA_TRY(cudaMemcpy(c->d_xyz, xyz, sizeof(double) * 3 * nat * (size_t)nall,
+                                cudaMemcpyHostToDevice));
     CREST_CUDA_TRY(cudaMemcpy(c->d_er, er, sizeof(double) * nall, cudaMemcpyHostToDevice));
   }
   return 0;
 }
+
+int crest_cuda_ctx_upload_xyz_rows(crest_cuda_ctx* c, int first, int count, const double* xyz_rows) {
+  if (!c) { set_error("ctx is NULL"); return 1; }
+  if (first < 0 || count < 0 || first + count > c->nall || (!xyz_rows && count > 0)) {
+    set_error("bad row range [%d, %d) of %d", first, first + count, c->nall);
+    return 1;
+  }
+  CREST_CUDA_TRY(cudaSetDevice(c->device));
+  const size_t rec = (size_t)3 * c->nat;
+  if (count > 0)
+    CREST_CUDA_TRY(cudaMemcpy(c->d_xyz + rec * first, xyz_rows, sizeof(double) * rec * count,
+                              cudaMemcpyHostToDevice));
+  return 0;
+}
+
+void* crest_cuda_ctx_xyz_devptr(crest_cuda_ctx* c) { return c ? (void*)c->d_xyz : nullptr; }
 
 int crest_cuda_ctx_pack(crest_cuda_ctx* c, void* stream) {
   if (!c) { set_error("ctx is NULL"); return 1; }

@@ -41,6 +41,19 @@ class CudaEngine:
                                   device=self.device)
         self._np_t = t.as_tensor(_DevArray(self.ctx.npairs_devptr(), 1, "<i8"), device=self.device)
 
+    def upload_rows(self, env, at, xyz, er, rank, world):
+        """This rank's slice host->device; returns (full view, my slice view) of the device xyz
+        buffer for the in-place all-gather (equal slices of `chunk` rows)."""
+        chunk, first, count = self.ctx.upload_rows(env, at, xyz, er, rank, world)
+        t = self.torch
+        rec = 3 * self.ctx.nat
+        full = t.as_tensor(_DevArray(self.ctx.xyz_devptr(), chunk * world * rec, "<f8"),
+                           device=self.device)
+        self._dup_t = t.as_tensor(_DevArray(self.ctx.dup_devptr(), max(self.ctx.nall, 1), "<i4"),
+                                  device=self.device)
+        self._np_t = t.as_tensor(_DevArray(self.ctx.npairs_devptr(), 1, "<i8"), device=self.device)
+        return full, full[rank * chunk * rec:(rank + 1) * chunk * rec]
+
     def stream(self):
         return self.torch.cuda.current_stream().cuda_stream
 
@@ -94,7 +107,13 @@ class DistributedCregen:
 
     def dup(self, env: Env, at, xyz, er):
         """Upload (every rank holds the full ensemble), run one step, return rank-identical results."""
-        self.engine.upload(env, np.asarray(at), np.asarray(xyz), np.asarray(er))
+        if self.world > 1 and hasattr(self.engine, "upload_rows"):
+            # each rank pulls 1/world of the geometry over PCIe; NVLink all-gather replicates it
+            full, mine = self.engine.upload_rows(env, np.asarray(at), np.asarray(xyz),
+                                                 np.asarray(er), self.rank, self.world)
+            self.dist.all_gather_into_tensor(full, mine, group=self.group)
+        else:
+            self.engine.upload(env, np.asarray(at), np.asarray(xyz), np.asarray(er))
         self.step(env)
         out = self.engine.download()
         out["npairs"] = self.npairs_total()

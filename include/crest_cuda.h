@@ -96,10 +96,18 @@ int crest_cuda_rmat_allpairs(int nat, int nall, const int* at, const double* xyz
 int crest_cuda_ctx_create(crest_cuda_ctx** ctx, int device /* -1 = current */);
 void crest_cuda_ctx_destroy(crest_cuda_ctx* ctx);
 
-/* Copy the ensemble host->device (pinned staging) and keep it resident. Does not launch math. */
+/* Copy the ensemble host->device and keep it resident. Does not launch math.  xyz may be NULL
+ * (reserve only, see crest_cuda_ctx_upload_xyz_rows). */
 int crest_cuda_ctx_upload(crest_cuda_ctx* ctx, int nat, int nall, const int* at,
                           const double* xyz, const double* er, const int* rmsd_mask,
                           int rot_from_mask);
+
+/* Multi-GPU upload: after crest_cuda_ctx_upload(..., xyz = NULL, ...) each rank copies only ITS rows
+ * [first, first+count) of xyz(3,nat,nall) host->device; the caller then all-gathers the slices
+ * over NVLink into the buffer crest_cuda_ctx_xyz_devptr returns (capacity 3*nat*(nall+64) doubles,
+ * so equal slices of ceil(nall/ranks) rows fit for up to 64 ranks). */
+int crest_cuda_ctx_upload_xyz_rows(crest_cuda_ctx* ctx, int first, int count, const double* xyz_rows);
+void* crest_cuda_ctx_xyz_devptr(crest_cuda_ctx* ctx);
 
 /* K0 on the device-resident ensemble: CMA shift, principal axes, rot, aniso, pack (kernel 1). */
 int crest_cuda_ctx_pack(crest_cuda_ctx* ctx, void* stream);
