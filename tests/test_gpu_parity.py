@@ -462,3 +462,70 @@ def test_tf32_sharded_equals_single(cb):
     many = ctx.download()
     ctx.close()
     assert np.array_equal(many["dup"], one["dup"]) and many["npairs"] == one["npairs"]
+
+
+@pytest.mark.parametrize("rthr,bthr", [(0.1, 0.01), (0.2, 0.02), (0.05, 0.005)])
+def test_tf32_other_thresholds(cb, oracle, rthr, bthr):
+    """Non-default RMSD / rot. thresholds (rthr not exactly representable in float32 shifts the
+    float32-emulated boundary, cregen.f90:1286,1359-1367) through the tensor-core path vs the oracle."""
+    ens = synth.make_ensemble(900, 40, 40, copies=10, seed=17, frac_straddle=0.3)
+    ens["heavy"] = False
+    at, xyz, er = ens["at"], ens["xyz"], ens["er"]
+    env = cb.Env(ethr=1e9, rthr=rthr, bthr2=bthr)
+    links, root, info = _stage_a(cb, ens, env)
+    assert info["variant"] == 2
+    ref = oracle.cregen_cre(at, xyz, er, ethr=1e9, rthr=rthr, bthr=bthr, want_rmat=True)
+    listed = boundary_rows(rows_of_allpairs(ref["rmat"], len(er)), rthr)
+    bad = set(np.where(root != ref["dup"])[0].tolist())
+    assert bad <= listed, sorted(bad - listed)
+
+
+def test_tf32_far_from_origin(cb):
+    """Centring happens in FP64 before the TF32 rounding: a 5 km offset of every structure must not
+    change a single decision."""
+    ens = synth.make_config("C1", nall=600, seed=23)
+    env = cb.Env(ethr=1e9)
+    a, ra, _ = _stage_a(cb, ens, env)
+    ens2 = dict(ens)
+    ens2["xyz"] = ens["xyz"] + np.array([5.0e4, -3.0e4, 1.0e4])
+    b, rb, info = _stage_a(cb, ens2, env)
+    assert info["variant"] == 2
+    # the FP64 reference of the shifted ensemble (cancellation in the centroid costs ~1e-11 A)
+    c, rc, _ = _stage_a(cb, ens2, env, "notf32")
+    assert np.array_equal(rb, rc)
+    assert np.mean(ra != rb) < 0.01
+
+
+def test_full_size_properties_c5(cb, oracle):
+    """BASELINE config C5 at FULL size (1 000 000 x 40, 5.0e11 pairs) on one GPU: pair count,
+    structure of the link array, and complete oracle rows for sampled conformers."""
+    ens = synth.make_config("C5")
+    at, xyz, er = ens["at"], ens["xyz"], ens["er"]
+    n = len(er)
+    env = cb.Env(ethr=1e9)
+    ctx = cb.CregenContext()
+    ctx.upload(env, at, xyz, er)
+    ctx.pack()
+    ctx.pairs(env)
+    links = ctx.download(want_xyz=True)
+    info = ctx.info(env)
+    assert info["variant"] == 2 and info["overflow"] == 0
+    assert links["npairs"] == n * (n - 1) // 2
+    dup = links["dup"]
+    assert np.all(dup <= np.arange(n))
+    ctx.sweep()
+    root = ctx.download()["dup"]
+    ctx.close()
+    assert np.all((root == 0) == (dup == 0))
+    assert np.all(root[root[root > 0] - 1] == 0)
+    xa, rot = links["xyz_axis"], links["rot"]
+    rows = sorted(np.random.default_rng(5).integers(n // 2, n, 6).tolist())
+    for i in rows:
+        _, rr = oracle.pair_rows(xa[: i + 1], er[: i + 1], i, i + 1, ethr=1e9)
+        r = rr.astype(np.float64)
+        exp = 0
+        for j in np.where(r < 0.25)[0]:
+            if r[j] < 0.125 or oracle.equalrotaniso(rot[i], rot[j], 0.005):
+                exp = j + 1
+        listed = np.any(np.abs(r - 0.125) <= RMSD_TOL) or np.any(np.abs(r - 0.25) <= RMSD_TOL)
+        assert dup[i] == exp or listed, (i, dup[i], exp)
