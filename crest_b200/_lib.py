@@ -37,6 +37,8 @@ SYMBOLS = {
                                         C.c_int, _THR, c_dp, c_ip, c_ip, c_ip, c_llp]),
     "crest_cuda_rmsd_pairs": (C.c_int, [C.c_int, C.c_int, c_dp, C.c_longlong, c_ip, c_ip, c_dp, c_dp]),
     "crest_cuda_rotconst": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp]),
+    "crest_cuda_cregen_esort": (C.c_int, [C.c_int, C.c_int, c_dp, c_dp, C.c_double, c_ip, c_ip]),
+    "crest_cuda_rmsdalign": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp]),
     "crest_cuda_rmat_allpairs": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_ip, C.c_int, c_fp]),
     "crest_cuda_ctx_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
     "crest_cuda_ctx_destroy": (None, [C.c_void_p]),

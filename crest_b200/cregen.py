@@ -204,6 +204,33 @@ def rotconst(at, xyz):
     return rot
 
 
+def cregen_esort(xyz, energies, ewin=1e9):
+    """cregen_esort (cregen.f90:1038-1121): returns (xyz_sorted, er_sorted, order, nallout);
+    order[i] = new 1-based position of input structure i.  xyz may be None."""
+    L = _lib.lib()
+    er = np.array(energies, np.float64, copy=True)
+    nall = len(er)
+    xs, nat = None, 1
+    if xyz is not None:
+        xs = np.array(xyz, np.float64, order="C", copy=True)
+        nat = xs.shape[1]
+    order = np.zeros(max(nall, 1), np.int32)
+    nout = C.c_int(0)
+    _lib.check(L.crest_cuda_cregen_esort(nat, nall, _dp(xs), _dp(er), float(ewin), _ip(order),
+                                         C.byref(nout)))
+    return xs, er, order[:nall], nout.value
+
+
+def rmsdalign(at, xyz):
+    """cregen_rmsdalign (cregen.f90:2229-2283) on the GPU; returns the aligned copy of xyz."""
+    L = _lib.lib()
+    at = np.ascontiguousarray(at, np.int32)
+    out = np.array(xyz, np.float64, order="C", copy=True)
+    nall, nat, _ = out.shape
+    _lib.check(L.crest_cuda_rmsdalign(nat, nall, _ip(at), _dp(out)))
+    return out
+
+
 def rmat_allpairs(env: Env, at, xyz):
     """float32 band as the reference's rmat with ethr=inf: row i at offset i*(i-1)/2."""
     L = _lib.lib()

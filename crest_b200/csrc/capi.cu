@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <utility>
 #include <vector>
 
 namespace crest {
@@ -873,6 +874,91 @@ int crest_cuda_rmsd_pairs(int A, int n, const double* packed, long long npairs, 
   }
   cudaFree(d_p); cudaFree(d_r); cudaFree(d_m); cudaFree(d_i); cudaFree(d_j);
   return rc;
+}
+
+int crest_cuda_rmsdalign(int nat, int nall, const int* at, double* xyz) {
+  if (nat <= 0 || nall < 0 || !at || (!xyz && nall)) { set_error("bad argument"); return 1; }
+  crest_cuda_ctx* c;
+  if (global_ctx(&c)) return 1;
+  CREST_CUDA_TRY(cudaSetDevice(c->device));
+  if (nall <= 1) return 0;
+  int* d_at = nullptr; double* d_xyz = nullptr;
+  const size_t bytes = sizeof(double) * 3 * nat * (size_t)nall;
+  CREST_CUDA_TRY(cudaMalloc(&d_at, sizeof(int) * nat));
+  if (cudaMalloc(&d_xyz, bytes) != cudaSuccess) {
+    cudaFree(d_at);
+    set_error("cudaMalloc failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return 1;
+  }
+  int rc = 1;
+  do {
+    if (cudaMemcpy(d_at, at, sizeof(int) * nat, cudaMemcpyHostToDevice) != cudaSuccess) break;
+    if (cudaMemcpy(d_xyz, xyz, bytes, cudaMemcpyHostToDevice) != cudaSuccess) break;
+    if (launch_rmsdalign(nat, nall, d_at, d_xyz, 0)) { rc = 2; break; }
+    if (cudaMemcpy(xyz, d_xyz, bytes, cudaMemcpyDeviceToHost) != cudaSuccess) break;
+    rc = 0;
+  } while (0);
+  if (rc == 1) set_error("CUDA error in rmsdalign: %s", cudaGetErrorString(cudaGetLastError()));
+  cudaFree(d_at); cudaFree(d_xyz);
+  return rc;
+}
+
+// Host-side: the reference's energy sort is an UNSTABLE Hoare quicksort with middle pivot
+// (src/quicksort.f90:140-165), so the order of equal energies - which every later index inherits -
+// is a property of that exact partition sequence.  Restated with an explicit stack (the two
+// sub-ranges are disjoint, their order does not matter); then maskinvert (quicksort.f90:278-291)
+// and the ewin cut of cregen_esort (src/cregen.f90:1096-1113).
+int crest_cuda_cregen_esort(int nat, int nall, double* xyz, double* energies, double ewin,
+                            int* order, int* nallout) {
+  if (nall < 0 || (!energies && nall) || !order || !nallout || (xyz && nat <= 0)) {
+    set_error("bad argument");
+    return 1;
+  }
+  std::vector<int> was(nall);              // after sorting: element at position p WAS at was[p]
+  for (int i = 0; i < nall; ++i) was[i] = i;
+  double* a = energies;
+  std::vector<std::pair<int, int>> stack;
+  if (nall > 0) stack.emplace_back(0, nall - 1);
+  while (!stack.empty()) {
+    const int first = stack.back().first, last = stack.back().second;
+    stack.pop_back();
+    // 1-based (first+last)/2 of the reference == 0-based (first+last+2)/2 - 1
+    const double x = a[(first + last + 2) / 2 - 1];
+    int i = first, j = last;
+    for (;;) {
+      while (a[i] < x) ++i;
+      while (x < a[j]) --j;
+      if (i >= j) break;
+      std::swap(a[i], a[j]);
+      std::swap(was[i], was[j]);
+      ++i; --j;
+    }
+    if (first < i - 1) stack.emplace_back(first, i - 1);
+    if (j + 1 < last) stack.emplace_back(j + 1, last);
+  }
+  for (int p = 0; p < nall; ++p) order[was[p]] = p + 1;     // structure i IS NOW at order[i] (1-based)
+  if (xyz && nall > 0) {
+    const size_t rec = (size_t)3 * nat;
+    std::vector<double> tmp(rec * nall);
+    for (int p = 0; p < nall; ++p)
+      std::memcpy(tmp.data() + rec * p, xyz + rec * was[p], rec * sizeof(double));
+    std::memcpy(xyz, tmp.data(), rec * nall * sizeof(double));
+  }
+  int nout = nall;
+  if (nall > 0) {
+    double emax = a[0];
+    for (int i = 1; i < nall; ++i) emax = std::max(emax, a[i]);
+    double de = (emax - a[0]) * kAutokcal;
+    if (de > ewin) {
+      nout = 1;
+      for (int i = 1; i < nall; ++i) {
+        de = (a[i] - a[0]) * kAutokcal;
+        if (de < ewin) ++nout; else break;
+      }
+    }
+  }
+  *nallout = nout;
+  return 0;
 }
 
 int crest_cuda_rmat_allpairs(int nat, int nall, const int* at, const double* xyz,

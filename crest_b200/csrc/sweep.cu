@@ -183,4 +183,124 @@ int launch_rmsd_pairs(int A, int n, const double* d_packed, long long npairs, co
   return 0;
 }
 
+// ---- cregen_rmsdalign: rotate every structure onto the first one (heavy atoms at > 2) ---------
+// reference src/cregen.f90:2229-2283: rmsd(n, c1 = structure k, c0 = structure 1, option 1) gives the
+// rotation U (src/ls_rmsd.f90:122-160: R(a,b) = sum x_a y_b on centroid-free coordinates, key matrix
+// S, eigenvector q of lambda_max, rotation_matrix 176-221), then xyz(:,:,k) <- U * xyz(:,:,k) for ALL
+// atoms, without any translation.  One warp per structure; q from a cyclic Jacobi with accumulated
+// rotations (U is quadratic in q, so the sign of q does not matter).
+static __device__ void jacobi4_vec(double S[4][4], double V[4][4]) {
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) V[i][j] = (i == j) ? 1.0 : 0.0;
+  for (int sweep = 0; sweep < 60; ++sweep) {
+    double off = 0.0, diag = 0.0;
+    for (int i = 0; i < 4; ++i) {
+      diag += S[i][i] * S[i][i];
+      for (int j = i + 1; j < 4; ++j) off += S[i][j] * S[i][j];
+    }
+    if (off <= 1e-36 * diag || off == 0.0) break;
+    for (int p = 0; p < 3; ++p)
+      for (int q = p + 1; q < 4; ++q) {
+        const double apq = S[p][q];
+        if (apq == 0.0) continue;
+        const double theta = (S[q][q] - S[p][p]) / (2.0 * apq);
+        const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+        const double c = 1.0 / sqrt(t * t + 1.0), sn = t * c;
+        for (int k = 0; k < 4; ++k) {
+          const double akp = S[k][p], akq = S[k][q];
+          S[k][p] = c * akp - sn * akq;
+          S[k][q] = sn * akp + c * akq;
+        }
+        for (int k = 0; k < 4; ++k) {
+          const double apk = S[p][k], aqk = S[q][k];
+          S[p][k] = c * apk - sn * aqk;
+          S[q][k] = sn * apk + c * aqk;
+        }
+        for (int k = 0; k < 4; ++k) {
+          const double vkp = V[k][p], vkq = V[k][q];
+          V[k][p] = c * vkp - sn * vkq;
+          V[k][q] = sn * vkp + c * vkq;
+        }
+      }
+  }
+}
+
+__global__ void __launch_bounds__(128)
+rmsdalign_kernel(int nat, int nall, const int* __restrict__ at, double* __restrict__ xyz) {
+  const int lane = threadIdx.x & 31;
+  const int k = 1 + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);   // structure 0 is the target
+  if (k >= nall) return;
+  const double* ref = xyz;
+  double* cur = xyz + (size_t)3 * nat * k;
+  // centroids of the heavy atoms (ls_rmsd.f90:105-119)
+  double cx[3] = {0, 0, 0}, cy[3] = {0, 0, 0};
+  int n = 0;
+  for (int j = lane; j < nat; j += 32)
+    if (at[j] > 2) {
+      ++n;
+      for (int a = 0; a < 3; ++a) { cx[a] += cur[3 * j + a]; cy[a] += ref[3 * j + a]; }
+    }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    n += __shfl_xor_sync(0xffffffffu, n, o);
+    for (int a = 0; a < 3; ++a) {
+      cx[a] += __shfl_xor_sync(0xffffffffu, cx[a], o);
+      cy[a] += __shfl_xor_sync(0xffffffffu, cy[a], o);
+    }
+  }
+  if (n == 0) return;                       // no heavy atom: nothing to align on
+  for (int a = 0; a < 3; ++a) { cx[a] /= (double)n; cy[a] /= (double)n; }
+  double r[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  for (int j = lane; j < nat; j += 32)
+    if (at[j] > 2) {
+      double xv[3], yv[3];
+      for (int a = 0; a < 3; ++a) { xv[a] = cur[3 * j + a] - cx[a]; yv[a] = ref[3 * j + a] - cy[a]; }
+      for (int a = 0; a < 3; ++a)
+        for (int b = 0; b < 3; ++b) r[3 * a + b] = fma(xv[a], yv[b], r[3 * a + b]);
+    }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+    for (int z = 0; z < 9; ++z) r[z] += __shfl_xor_sync(0xffffffffu, r[z], o);
+  // key matrix (ls_rmsd.f90:129-147), R(a,b) = r[3a+b]
+  double S[4][4], V[4][4];
+  S[0][0] = r[0] + r[4] + r[8];
+  S[1][0] = r[5] - r[7];
+  S[2][0] = r[6] - r[2];
+  S[3][0] = r[1] - r[3];
+  S[1][1] = r[0] - r[4] - r[8];
+  S[2][1] = r[1] + r[3];
+  S[3][1] = r[2] + r[6];
+  S[2][2] = -r[0] + r[4] - r[8];
+  S[3][2] = r[5] + r[7];
+  S[3][3] = -r[0] - r[4] + r[8];
+  for (int i = 0; i < 4; ++i)
+    for (int j = i + 1; j < 4; ++j) S[i][j] = S[j][i];
+  jacobi4_vec(S, V);
+  int m = 0;
+  for (int i = 1; i < 4; ++i)
+    if (S[i][i] > S[m][m]) m = i;
+  const double q0 = V[0][m], q1 = V[1][m], q2 = V[2][m], q3 = V[3][m];
+  // rotation_matrix (ls_rmsd.f90:176-221)
+  const double b0 = 2.0 * q0, b1 = 2.0 * q1, b2 = 2.0 * q2, b3 = 2.0 * q3;
+  const double q00 = b0 * q0 - 1.0, q01 = b0 * q1, q02 = b0 * q2, q03 = b0 * q3;
+  const double q11 = b1 * q1, q12 = b1 * q2, q13 = b1 * q3, q22 = b2 * q2, q23 = b2 * q3, q33 = b3 * q3;
+  const double U[3][3] = {{q00 + q11, q12 - q03, q13 + q02},
+                          {q12 + q03, q00 + q22, q23 - q01},
+                          {q13 - q02, q23 + q01, q00 + q33}};
+  for (int j = lane; j < nat; j += 32) {
+    const double x = cur[3 * j], y = cur[3 * j + 1], z = cur[3 * j + 2];
+    cur[3 * j] = U[0][0] * x + U[0][1] * y + U[0][2] * z;
+    cur[3 * j + 1] = U[1][0] * x + U[1][1] * y + U[1][2] * z;
+    cur[3 * j + 2] = U[2][0] * x + U[2][1] * y + U[2][2] * z;
+  }
+}
+
+int launch_rmsdalign(int nat, int nall, const int* d_at, double* d_xyz, cudaStream_t stream) {
+  if (nall <= 1) return 0;
+  const int wpb = 4;
+  rmsdalign_kernel<<<(nall - 1 + wpb - 1) / wpb, wpb * 32, 0, stream>>>(nat, nall, d_at, d_xyz);
+  CREST_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 }  // namespace crest

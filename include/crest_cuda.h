@@ -84,6 +84,19 @@ int crest_cuda_rmsd_pairs(int A, int n, const double* packed, long long npairs, 
 /* Rot. constants only: axis(nat,at,coord,rot,avmom) = axis_1 -> axis_0 (axis_module.f90:96-176). */
 int crest_cuda_rotconst(int nat, int n, const int* at, const double* xyz, double* rot);
 
+/* ---- rows either side of cregen_CRE ----
+ * cregen_esort (cregen.f90:1038-1121) without the file/comment handling: sorts energies ascending
+ * with the reference's own unstable quicksort (quicksort.f90:140-165; tie order is part of the
+ * contract), permutes xyz(3,nat,nall) with it (xyz may be NULL), returns order(nall) = new 1-based
+ * position of input structure i (what the caller permutes `comments` with) and nallout after the
+ * energy-window cut `ewin` (kcal/mol).  Host code: O(N log N), serial in the reference too. */
+int crest_cuda_cregen_esort(int nat, int nall, double* xyz, double* energies, double ewin,
+                            int* order, int* nallout);
+
+/* cregen_rmsdalign (cregen.f90:2229-2283): rotate structures 2..nall onto structure 1 by the
+ * optimal heavy-atom (at > 2) rotation of rmsd() (ls_rmsd.f90:72-221, option 1), in place. */
+int crest_cuda_rmsdalign(int nat, int nall, const int* at, double* xyz);
+
 /* All-pairs float32 RMSD band exactly as the reference's rmat (cregen.f90:1260-1349): row i holds
  * j = 0..i-1 at offset i*(i-1)/2 (ethr = infinity layout).  For tests on small ensembles. */
 int crest_cuda_rmat_allpairs(int nat, int nall, const int* at, const double* xyz,

@@ -54,6 +54,37 @@ double oracle_bthrerf(double bthr, double aniso, double bthrmax, double bthrshif
 }
 double oracle_rotaniso(const double* rot3) { return rotaniso(1, rot3); }
 
+// cregen.f90:2229-2283 cregen_rmsdalign: structures 2..nall rotated onto structure 1 by the
+// heavy-atom (at > 2) rotation of rmsd(..., option 1) (ls_rmsd.f90:72-221); xyz (nall,nat,3) in place.
+// Returns the number of structures whose 4x4 eigen-solve failed (left unrotated).
+int oracle_rmsdalign(int nat, int nall, const int* at, double* xyz) {
+  int nath = 0;
+  for (int j = 0; j < nat; ++j) nath += at[j] > 2;
+  if (nath == 0 || nall < 2) return 0;
+  std::vector<double> c0(3 * (size_t)nath), c1(3 * (size_t)nath), x(3 * (size_t)nath),
+      y(3 * (size_t)nath), c2(3 * (size_t)nat);
+  int i = 0;
+  for (int j = 0; j < nat; ++j)
+    if (at[j] > 2) { for (int a = 0; a < 3; ++a) c0[3 * i + a] = xyz[3 * j + a]; ++i; }
+  int nfail = 0;
+  for (int k = 1; k < nall; ++k) {
+    double* cur = xyz + (size_t)3 * nat * k;
+    i = 0;
+    for (int j = 0; j < nat; ++j)
+      if (at[j] > 2) { for (int a = 0; a < 3; ++a) c1[3 * i + a] = cur[3 * j + a]; ++i; }
+    RmsdOut o;
+    rmsd_full(nath, c1.data(), c0.data(), x.data(), y.data(), o);
+    if (o.error < 0.0) { ++nfail; continue; }
+    double U[3][3];
+    rotation_matrix(o.q, U);
+    for (int j = 0; j < nat; ++j)                      // c2 = matmul(U, xyz(:,:,k))
+      for (int a = 0; a < 3; ++a)
+        c2[3 * j + a] = U[a][0] * cur[3 * j] + U[a][1] * cur[3 * j + 1] + U[a][2] * cur[3 * j + 2];
+    for (int j = 0; j < 3 * nat; ++j) cur[j] = c2[j];
+  }
+  return nfail;
+}
+
 int oracle_esort(int nall, double* energies, int* pos, double ewin) {
   return esort(nall, energies, pos, ewin);
 }

@@ -38,6 +38,8 @@ def lib():
         L.oracle_bthrerf.argtypes = [C.c_double] * 4
         L.oracle_rotaniso.restype = C.c_double
         L.oracle_rotaniso.argtypes = [c_dp]
+        L.oracle_rmsdalign.restype = C.c_int
+        L.oracle_rmsdalign.argtypes = [C.c_int, C.c_int, c_ip, c_dp]
         L.oracle_esort.restype = C.c_int
         L.oracle_esort.argtypes = [C.c_int, c_dp, c_ip, C.c_double]
         L.oracle_backtrack.argtypes = [C.c_int, c_ip]
@@ -102,6 +104,15 @@ def equalrotaniso(ri, rj, bthr, bthrmax=0.025, bthrshift=0.5):
     ri = np.ascontiguousarray(ri, np.float64)
     rj = np.ascontiguousarray(rj, np.float64)
     return bool(lib().oracle_equalrotaniso(_dp(ri), _dp(rj), bthr, bthrmax, bthrshift))
+
+
+def rmsdalign(at, xyz):
+    """Oracle cregen_rmsdalign (cregen.f90:2229-2283); returns (aligned copy, nfail)."""
+    at = np.ascontiguousarray(at, np.int32)
+    out = np.array(xyz, np.float64, order="C", copy=True)
+    nall, nat, _ = out.shape
+    nfail = lib().oracle_rmsdalign(nat, nall, _ip(at), _dp(out))
+    return out, nfail
 
 
 def esort(energies, ewin=1e9):

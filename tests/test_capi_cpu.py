@@ -129,3 +129,26 @@ def test_argument_checks(cuda_lib):
     rc = cuda_lib.crest_cuda_cregen_dup(3, 2, None, None, None, None, 0, 1, None, None, None, None,
                                         None)
     assert rc != 0 and len(cuda_lib.crest_cuda_last_error()) > 0
+
+
+def test_host_esort_matches_oracle(cuda_lib):
+    """crest_cuda_cregen_esort (host code of the product) reproduces the reference's unstable
+    quicksort permutation incl. the order of EQUAL energies (quicksort.f90:140-165)
+    and the ewin cut (cregen.f90:1096-1113)."""
+    import oracle_lib as O
+    from crest_b200 import cregen as cg
+    rng = np.random.default_rng(4)
+    for n, ties, ewin in ((0, False, 6.0), (1, False, 6.0), (2, True, 6.0), (17, True, 1e9),
+                          (1000, False, 3.0), (1000, True, 2.0), (5000, True, 1e9)):
+        en = rng.uniform(0, 6.0, n) / 627.50947428 - 40.0
+        if ties and n > 1:
+            en = np.round(en * 2000) / 2000           # many exact duplicates
+        xyz = rng.normal(size=(n, 3, 3))
+        es_ref, pos_ref, nout_ref = O.esort(en, ewin=ewin)
+        xs, es, order, nout = cg.cregen_esort(xyz, en, ewin)
+        assert np.array_equal(es, es_ref)
+        assert np.array_equal(order, np.asarray(pos_ref) + (1 - int(np.min(pos_ref, initial=1))))
+        assert nout == nout_ref
+        if n:
+            assert np.array_equal(xs[order - 1], xyz)          # structure i now sits at order[i]
+            assert np.all(np.diff(es) >= 0)

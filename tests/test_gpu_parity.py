@@ -529,3 +529,22 @@ def test_full_size_properties_c5(cb, oracle):
                 exp = j + 1
         listed = np.any(np.abs(r - 0.125) <= RMSD_TOL) or np.any(np.abs(r - 0.25) <= RMSD_TOL)
         assert dup[i] == exp or listed, (i, dup[i], exp)
+
+
+def test_rmsdalign_entry(cb, oracle):
+    """crest_cuda_rmsdalign (cregen.f90:2229-2283) against the oracle: aligned
+    coordinates within 1e-8 A; the first structure is untouched; hydrogens do not steer."""
+    for cfg, nall in (("C1", 300), ("C4", 40), ("C2", 500)):
+        ens = synth.make_config(cfg, nall=nall, seed=41)
+        at, xyz = ens["at"], ens["xyz"]
+        ref, nfail = oracle.rmsdalign(at, xyz)
+        assert nfail == 0
+        got = cb.rmsdalign(at, xyz)
+        assert np.array_equal(got[0], xyz[0])
+        assert np.abs(got - ref).max() < 1e-8
+    # only hydrogens / helium: nothing to align on, input returned unchanged
+    at = np.array([1, 1, 2, 1], np.int32)
+    xyz = np.random.default_rng(0).normal(size=(5, 4, 3))
+    assert np.array_equal(cb.rmsdalign(at, xyz), xyz)
+    # nall = 0 / 1
+    assert cb.rmsdalign(np.array([6, 8], np.int32), np.zeros((1, 2, 3))).shape == (1, 2, 3)

@@ -340,3 +340,27 @@ def test_golden_pairs_kat(oracle):
         assert a["rmsd"] == rec[0] and a["lam"] == rec[2]
         assert abs(min(rec[0], rec[1]) - min(kabsch_rmsd(X[i], X[j]),
                                              kabsch_rmsd(X[i], X[j] * [-1, 1, 1]))) < 1e-8
+
+
+def test_rmsdalign_oracle_vs_kabsch():
+    """Oracle cregen_rmsdalign (cregen.f90:2229-2283) against an independent numpy Kabsch-SVD:
+    same rotation (up to 1e-10) for generic structures; heavy atoms only (at > 2), no translation."""
+    import oracle_lib as O
+    rng = np.random.default_rng(12)
+    nat = 30
+    at = rng.choice([1, 6, 7, 8], size=nat, p=[0.4, 0.4, 0.1, 0.1]).astype(np.int32)
+    base = rng.normal(size=(nat, 3)) * 3
+    R = synth._random_rotations(rng, 40)
+    xyz = np.einsum("nij,aj->nai", R, base) + rng.normal(size=(40, nat, 3)) * 0.1 + rng.normal(size=(40, 1, 3))
+    out, nfail = O.rmsdalign(at, xyz)
+    assert nfail == 0
+    assert np.array_equal(out[0], xyz[0])
+    hv = at > 2
+    y = xyz[0][hv] - xyz[0][hv].mean(0)
+    for k in range(1, 40):
+        x = xyz[k][hv] - xyz[k][hv].mean(0)
+        H = x.T @ y
+        Uu, S, Vt = np.linalg.svd(H)
+        d = np.sign(np.linalg.det(Vt.T @ Uu.T))
+        Rk = Vt.T @ np.diag([1, 1, d]) @ Uu.T          # rotates x onto y
+        assert np.abs(out[k] - xyz[k] @ Rk.T).max() < 1e-9
