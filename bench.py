@@ -342,6 +342,17 @@ def run_ours(args):
                "api": api}
         assert np.array_equal(r2["dup"], res["dup"])
 
+    # ---- whole cregen_CRE (duplicates + partition + enuc + rotamer groups) from host buffers:
+    # the "CREGEN wall time" half of the metric, N = 1 only (stage B is one sequential sweep)
+    cregen_wall = None
+    if world == 1 and not args.no_e2e:
+        cb.cregen_CRE(env, nat, nall, at, xyz, er)
+        t0 = time.perf_counter()
+        full = cb.cregen_CRE(env, nat, nall, at, xyz, er)
+        cregen_wall = {"ms": (time.perf_counter() - t0) * 1e3, "api": "crest_cuda_cregen_cre (one call, host buffers; "
+                       "includes the host copies of the ctypes mirror)", "kept": int(full.nallout),
+                       "groups": int(full.group[0])}
+
     if rank == 0:
         A = info["A"]
         fp64_peak = fp64_peak_tflops(torch, dev)
@@ -381,7 +392,7 @@ def run_ours(args):
                          "frac": achieved / peak, "traffic": traffic,
                          "fp64_tensor_peak": fp64_peak, "fp64_tensor_equiv": achieved / fp64_peak,
                          "note": note},
-            "clocks": clocks, "e2e": e2e,
+            "clocks": clocks, "e2e": e2e, "cregen_wall": cregen_wall,
         }
         if world == 1 and not args.no_cpu_baseline:
             cbase = cpu_sample(ens, args, args.cpu_seconds)

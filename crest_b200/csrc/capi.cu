@@ -787,35 +787,61 @@ int crest_cuda_cregen_cre(int nat, int nall, const int* at, double* xyz, double*
                           const crest_cuda_thresholds* thr, double* rot, int* order, int* group,
                           int* nallout, long long* npairs) {
   if (!rot || !order || !group || !nallout) { set_error("NULL output array"); return 1; }
+  if (check_thr(thr)) return 1;
+  crest_cuda_ctx* c;
+  if (global_ctx(&c)) return 1;
+  // stage A on the device; only the link array (4 B per structure) comes back for the partition
+  if (crest_cuda_ctx_upload(c, nat, nall, at, xyz, er, rmsd_mask, rot_from_mask)) return 1;
+  if (crest_cuda_ctx_pack(c, nullptr)) return 1;
+  if (crest_cuda_ctx_pairs(c, enantio, thr, 0, 1, 0, nullptr)) return 1;
+  if (crest_cuda_ctx_sweep(c, nullptr)) return 1;
   std::vector<int> dup((size_t)(nall > 0 ? nall : 1));
-  std::vector<double> xa((size_t)3 * nat * (nall > 0 ? nall : 1));
-  if (crest_cuda_cregen_dup(nat, nall, at, xyz, er, rmsd_mask, rot_from_mask, enantio, thr, rot,
-                            xa.data(), dup.data(), npairs))
-    return 1;
+  if (crest_cuda_ctx_download(c, nullptr, nullptr, dup.data(), npairs, nullptr)) return 1;
+  for (int i = 0; i <= nall; ++i) group[i] = 0;
+  if (nall == 0) { *nallout = 0; return 0; }
   // kept-first partition, duplicates appended in reverse encounter order (cregen.f90:1397-1419)
   int ndup = 0;
   for (int i = 0; i < nall; ++i) ndup += dup[i] != 0;
   int nout = nall - ndup;
+  std::vector<int> src((size_t)nall);
   if (nosort) {
     nout = nall;
-    for (int i = 0; i < nall; ++i) order[i] = i + 1;
-    std::memcpy(xyz, xa.data(), sizeof(double) * 3 * nat * (size_t)nall);
+    for (int i = 0; i < nall; ++i) { order[i] = i + 1; src[i] = i; }
   } else {
     int j = 0, l = nall + 1;
-    for (int i = 0; i < nall; ++i) order[i] = (dup[i] == 0) ? ++j : --l;
-    std::vector<double> e2(nall), r2((size_t)3 * nall);
-    const size_t rec = (size_t)3 * nat;
     for (int i = 0; i < nall; ++i) {
-      const size_t d = (size_t)order[i] - 1;
-      std::memcpy(xyz + d * rec, xa.data() + (size_t)i * rec, rec * sizeof(double));
-      e2[d] = er[i];
-      r2[3 * d] = rot[3 * i]; r2[3 * d + 1] = rot[3 * i + 1]; r2[3 * d + 2] = rot[3 * i + 2];
+      order[i] = (dup[i] == 0) ? ++j : --l;
+      src[order[i] - 1] = i;
     }
-    std::memcpy(er, e2.data(), sizeof(double) * nall);
-    std::memcpy(rot, r2.data(), sizeof(double) * 3 * nall);
   }
-  for (int i = 0; i <= nall; ++i) group[i] = 0;
-  if (crest_cuda_cregen_group(nat, nout, at, xyz, er, rot, thr, group, nullptr)) return 1;
+  // permutation, K5 and K6 on the device; geometry crosses PCIe once per direction
+  const size_t n = (size_t)nall;
+  int *d_src = nullptr, *d_group = nullptr;
+  double *d_er2 = nullptr, *d_rot2 = nullptr, *d_enuc = nullptr;
+  int rc = 1;
+  do {
+    if (cudaMalloc(&d_src, sizeof(int) * n) != cudaSuccess) break;
+    if (cudaMalloc(&d_group, sizeof(int) * (n + 1)) != cudaSuccess) break;
+    if (cudaMalloc(&d_er2, sizeof(double) * n) != cudaSuccess) break;
+    if (cudaMalloc(&d_rot2, sizeof(double) * 3 * n) != cudaSuccess) break;
+    if (cudaMalloc(&d_enuc, sizeof(double) * n) != cudaSuccess) break;
+    if (cudaMemcpy(d_src, src.data(), sizeof(int) * n, cudaMemcpyHostToDevice) != cudaSuccess) break;
+    // d_xyz (the input copy) is free now: it receives the permuted principal-axis geometries
+    if (launch_permute(nat, nall, d_src, c->d_xyz_axis, c->d_er, c->d_rot, c->d_xyz, d_er2, d_rot2, 0)) { rc = 2; break; }
+    if (cudaMemset(d_group, 0, sizeof(int) * (n + 1)) != cudaSuccess) break;
+    if (launch_enuc(nat, nout, c->d_at, c->d_xyz, d_enuc, 0)) { rc = 2; break; }
+    if (launch_group(nout, d_er2, d_rot2, d_enuc, thr->ethr, thr->bthr, thr->bthrmax, thr->bthrshift,
+                     d_group, 0)) { rc = 2; break; }
+    if (cudaMemcpy(xyz, c->d_xyz, sizeof(double) * 3 * nat * n, cudaMemcpyDeviceToHost) != cudaSuccess) break;
+    if (cudaMemcpy(er, d_er2, sizeof(double) * n, cudaMemcpyDeviceToHost) != cudaSuccess) break;
+    if (cudaMemcpy(rot, d_rot2, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost) != cudaSuccess) break;
+    if (cudaMemcpy(group, d_group, sizeof(int) * ((size_t)nout + 1), cudaMemcpyDeviceToHost) != cudaSuccess) break;
+    rc = 0;
+  } while (0);
+  if (rc == 1) set_error("CUDA error in cregen_cre: %s", cudaGetErrorString(cudaGetLastError()));
+  cudaFree(d_src); cudaFree(d_group); cudaFree(d_er2); cudaFree(d_rot2); cudaFree(d_enuc);
+  if (rc) return rc;
+  c->launches += 3;
   if (nosort) nout = group[0];
   *nallout = nout;
   return 0;

@@ -168,6 +168,9 @@ int launch_backtrack(int nall, int* d_dup, cudaStream_t stream);
 int launch_rmsd_pairs(int A, int n, const double* d_packed, long long npairs, const int* d_i,
                       const int* d_j, double* d_rmsd, double* d_rmsd_m, cudaStream_t stream);
 int launch_rmsdalign(int nat, int nall, const int* d_at, double* d_xyz, cudaStream_t stream);
+int launch_permute(int nat, int nall, const int* d_src, const double* d_xyz_in, const double* d_er_in,
+                   const double* d_rot_in, double* d_xyz_out, double* d_er_out, double* d_rot_out,
+                   cudaStream_t stream);
 int launch_enuc(int nat, int n, const int* d_at, const double* d_xyz, double* d_enuc,
                 cudaStream_t stream);
 int launch_group(int n, const double* d_er, const double* d_rot, const double* d_enuc,

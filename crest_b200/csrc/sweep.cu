@@ -71,11 +71,14 @@ int launch_enuc(int nat, int n, const int* d_at, const double* d_xyz, double* d_
 __global__ void __launch_bounds__(1024)
 group_kernel(int n, const double* __restrict__ er, const double* __restrict__ rot,
              const double* __restrict__ enuc, double ethr, double bthr, double bthrmax,
-             double bthrshift, int* __restrict__ group, unsigned char* __restrict__ head) {
+             double bthrshift, int* __restrict__ group, unsigned char* __restrict__ head,
+             double* __restrict__ aniso) {
   __shared__ int s_min[32];
   __shared__ int s_ng;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s_ng = 0;
+  // rotaniso of every structure once (rotcompare.f90:109-122), not once per candidate pair
+  for (int k = tid; k < n; k += blockDim.x) aniso[k] = rotaniso_dev(rot[3 * k], rot[3 * k + 1], rot[3 * k + 2]);
   __syncthreads();
   int jlo = 0;   // energies ascend: the |dE| window start only moves forward
   for (int i = 0; i < n; ++i) {
@@ -85,18 +88,20 @@ group_kernel(int n, const double* __restrict__ er, const double* __restrict__ ro
     int best = 0x7fffffff;
     if (jlo < i) {
       const double ri[3] = {rot[3 * i], rot[3 * i + 1], rot[3 * i + 2]};
-      const double ai = rotaniso_dev(ri[0], ri[1], ri[2]);
+      const double ai = aniso[i];
       const double eni = enuc[i];
       for (int j = jlo + tid; j < i; j += blockDim.x) {
         if (!head[j]) continue;
         const double de = __dmul_rn(__dsub_rn(ei, er[j]), kAutokcal);
         if (!(fabs(de) < ethr)) continue;
-        const double rj[3] = {rot[3 * j], rot[3 * j + 1], rot[3 * j + 2]};
-        const double aj = rotaniso_dev(rj[0], rj[1], rj[2]);
-        if (!equalrotaniso_dev(ri, rj, ai, aj, bthr, bthrmax, bthrshift)) continue;
+        // the three conditions of cregen.f90:1444-1448 are a conjunction: cheapest first
         const double enj = enuc[j];
         const double rel = __ddiv_rn(__dmul_rn(2.0, fabs(__dsub_rn(eni, enj))), __dadd_rn(eni, enj));
-        if (rel < 1.0e-3) { best = j; break; }
+        if (!(rel < 1.0e-3)) continue;
+        const double rj[3] = {rot[3 * j], rot[3 * j + 1], rot[3 * j + 2]};
+        if (!equalrotaniso_dev(ri, rj, ai, aniso[j], bthr, bthrmax, bthrshift)) continue;
+        best = j;
+        break;
       }
     }
 #pragma unroll
@@ -121,11 +126,14 @@ int launch_group(int n, const double* d_er, const double* d_rot, const double* d
                  double ethr, double bthr, double bthrmax, double bthrshift, int* d_group,
                  cudaStream_t stream) {
   unsigned char* head = nullptr;
+  double* aniso = nullptr;
   CREST_CUDA_TRY(cudaMallocAsync(&head, (size_t)(n > 0 ? n : 1), stream));
+  CREST_CUDA_TRY(cudaMallocAsync(&aniso, sizeof(double) * (size_t)(n > 0 ? n : 1), stream));
   group_kernel<<<1, 1024, 0, stream>>>(n, d_er, d_rot, d_enuc, ethr, bthr, bthrmax, bthrshift,
-                                       d_group, head);
+                                       d_group, head, aniso);
   CREST_CUDA_TRY(cudaGetLastError());
   CREST_CUDA_TRY(cudaFreeAsync(head, stream));
+  CREST_CUDA_TRY(cudaFreeAsync(aniso, stream));
   return 0;
 }
 
@@ -299,6 +307,33 @@ int launch_rmsdalign(int nat, int nall, const int* d_at, double* d_xyz, cudaStre
   if (nall <= 1) return 0;
   const int wpb = 4;
   rmsdalign_kernel<<<(nall - 1 + wpb - 1) / wpb, wpb * 32, 0, stream>>>(nat, nall, d_at, d_xyz);
+  CREST_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// ---- kept-first partition (cregen.f90:1397-1419) applied on the device: dst position d takes input
+// structure src[d]; geometry, energy and rot. constants move together.  One warp per structure.
+__global__ void __launch_bounds__(128)
+permute_kernel(int nat, int nall, const int* __restrict__ src, const double* __restrict__ xyz_in,
+               const double* __restrict__ er_in, const double* __restrict__ rot_in,
+               double* __restrict__ xyz_out, double* __restrict__ er_out, double* __restrict__ rot_out) {
+  const int lane = threadIdx.x & 31;
+  const int d = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (d >= nall) return;
+  const int sidx = src[d];
+  const double* a = xyz_in + (size_t)3 * nat * sidx;
+  double* b = xyz_out + (size_t)3 * nat * d;
+  for (int k = lane; k < 3 * nat; k += 32) b[k] = a[k];
+  if (lane == 0) er_out[d] = er_in[sidx];
+  if (lane < 3) rot_out[3 * d + lane] = rot_in[3 * sidx + lane];
+}
+
+int launch_permute(int nat, int nall, const int* d_src, const double* d_xyz_in, const double* d_er_in,
+                   const double* d_rot_in, double* d_xyz_out, double* d_er_out, double* d_rot_out,
+                   cudaStream_t stream) {
+  if (nall <= 0) return 0;
+  permute_kernel<<<(nall + 3) / 4, 128, 0, stream>>>(nat, nall, d_src, d_xyz_in, d_er_in, d_rot_in,
+                                                     d_xyz_out, d_er_out, d_rot_out);
   CREST_CUDA_TRY(cudaGetLastError());
   return 0;
 }
