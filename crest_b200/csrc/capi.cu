@@ -434,7 +434,9 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
   c->L = c->use_col ? make_col_layout(c->nsel, nall) : make_layout(c->nsel, nall);
   c->items_ethr = std::numeric_limits<double>::quiet_NaN();
   c->tf_items_ethr = std::numeric_limits<double>::quiet_NaN();
-  c->use_tf32 = c->use_col && !tune().no_tf32 && nall >= 2 && tf32_smem_bytes(c->L.KU, nullptr) > 0;
+  c->use_tf32 = !tune().no_tf32 && nall >= 2;
+  if (c->use_col) { c->tf.nslab = 1; c->tf.kslab = c->L.KU; }
+  else { c->tf.kslab = kTfSlabSlots; c->tf.nslab = (c->L.nslab * c->L.KU + kTfSlabSlots - 1) / kTfSlabSlots; }
   c->ntile = (nall + 127) / 128;
   c->h_er.assign(er, er + nall);
   c->tiles_ethr = std::numeric_limits<double>::quiet_NaN();
@@ -472,7 +474,7 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
     c->cap_X = nX;
   }
   if (c->use_tf32) {
-    const size_t nx = (size_t)c->ntile * 128 * 3 * c->L.KU;    // floats, same for Xa and Xb
+    const size_t nx = (size_t)c->ntile * 128 * 3 * c->tf.kslab * c->tf.nslab;    // floats, same for Xa and Xb
     if (nx > c->cap_tf_x) {
       cudaFree(c->tf.Xa); cudaFree(c->tf.Xb); c->tf.Xa = c->tf.Xb = nullptr; c->cap_tf_x = 0;
       CREST_CUDA_TRY(cudaMalloc(&c->tf.Xa, sizeof(float) * nx));
@@ -540,7 +542,8 @@ int crest_cuda_ctx_pack(crest_cuda_ctx* c, void* stream) {
     return 1;
   if (c->nall > 0) c->launches += 1;
   if (c->use_tf32) {
-    if (launch_tf32_convert(c->d_X, c->d_xn, c->nall, c->L, c->ntile, c->tf.Xa, c->tf.Xb, c->tf.hn, st))
+    if (launch_tf32_convert(c->d_X, c->d_xn, c->nall, c->L, c->ntile, c->tf.nslab, c->tf.kslab, c->tf.Xa,
+                            c->tf.Xb, c->tf.hn, st))
       return 1;
     c->launches += 1;
   }
@@ -605,7 +608,14 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
     // the fallback covers the WHOLE triangle on this rank: the tf32 and column work lists shard
     // the pair space differently, so a per-shard re-run would leave holes in a multi-rank job
     int g2 = 0, s2 = 0;
-    if (launch_pair_cols(fb, c->d_items, 0, (int)(c->items.size() / 4), st, &g2, &s2)) return 1;
+    if (c->use_col) {
+      if (launch_pair_cols(fb, c->d_items, 0, (int)(c->items.size() / 4), st, &g2, &s2)) return 1;
+    } else {
+      int nsf = 0;
+      pair_smem_bytes(c->L, &nsf);
+      fb.tile_begin = 0; fb.tile_end = c->rowstart.back();
+      if (launch_pair_tiles(fb, nsf, st, &g2, &s2)) return 1;
+    }
     if (g2 > 0) c->launches += 1;
     c->last_variant = 2;
     return 0;

@@ -157,10 +157,14 @@ struct Tf32Buffers {
   void* cand = nullptr;       // int2[cand_cap] candidate pairs (i, j)
   unsigned cand_cap = 0;
   unsigned* cand_count = nullptr;   // [0] appended, [1] overflow, [2] debug violations, [3] spare
+  int nslab = 1;              // TF32 K slabs (1 for A <= 88; slabs of 48 slots for the row-tile layout)
+  int kslab = 0;              // atom slots per slab (multiple of 8)
 };
+constexpr int kTfSlabSlots = 48;
 int tf32_smem_bytes(int KU, int* nbstage_out);
 int launch_tf32_convert(const double* d_X, const double* d_xn, int nall, const PackLayout& L,
-                        int ntile, float* d_Xa, float* d_Xb, float* d_hn, cudaStream_t stream);
+                        int ntile, int nslab_t, int kslab, float* d_Xa, float* d_Xb, float* d_hn,
+                        cudaStream_t stream);
 // items = device array of {I, g_begin, g_end, g_gate_end} int quadruples
 int launch_pair_tf32(const PairArgs& a, const Tf32Buffers& tb, const void* d_items, int item_begin,
                      int item_end, int all_cand, cudaStream_t stream, int* grid_out, int* smem_out);

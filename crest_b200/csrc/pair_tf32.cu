@@ -134,7 +134,8 @@ struct TfArgs {
   const TfItem* items;
   int item_begin, item_end;
   int nall;
-  int KU;                 // K extent (multiple of 8)
+  int KU;                 // K extent (multiple of 8); per slab in the slab kernel
+  int nslab;              // K slabs (slab kernel only)
   int nbstage;
   float cE;               // -0.5 * E2_up
   double ethr;
@@ -383,12 +384,179 @@ __device__ __forceinline__ float to_tf32_rn(double x) {
   return __uint_as_float(u);
 }
 
+// ---- K-slab variant for A > 88 atoms (BASELINE config C4: 300 atoms) -----------------------------
+// Same decomposition, but a conformer's K extent no longer fits on chip, so K is cut into slabs of
+// 48 atom slots and the accumulators of a BLOCK of three consecutive j-groups (= the three TMEM
+// stages) stay live across the slab loop:
+//     for slab s:  A slab (i-tile, 72 KB) -> smem ring of 2
+//        for g in block:  B slab (9 KB) -> ring;  18 MMAs accumulate into stage(g)   (overwrite at s = 0)
+// after the last slab each stage is committed to the epilogue, which is the same code as above.
+// Operand traffic from L2 per 3 groups: nslab x (72 + 27) KB; the MMAs read A from shared memory
+// (SS mode).  With 5400 FLOP per pair this shape is tensor-bound, not screen-bound.
+constexpr int kSlabKsteps = 6;                       // 48 atom slots per slab
+constexpr int kSlabBlock = 3;                        // j-groups per block = TMEM stages
+
+__global__ void __launch_bounds__(kTfThreads, 1)
+pair_tf32_slab_kernel(const TfArgs a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t a_full[2], a_empty[2];
+  __shared__ __align__(8) uint64_t b_full[kTfBStagesMax], b_empty[kTfBStagesMax];
+  __shared__ __align__(8) uint64_t d_full[kSlabBlock], d_empty[kSlabBlock];
+  __shared__ uint32_t tmem_base_smem;
+  constexpr int nchunk = 2 * kSlabKsteps;
+  constexpr uint32_t a_comp_bytes = (uint32_t)nchunk * 2048u;
+  constexpr uint32_t a_bytes = 3u * a_comp_bytes;            // one slab of the i-tile
+  constexpr uint32_t b_bytes = (uint32_t)nchunk * 768u;      // one slab of a j-group
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char* const sA = smem_raw;
+  unsigned char* const sB = smem_raw + 2 * a_bytes;
+  const int nbs = a.nbstage, nslab = a.nslab;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 2; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
+    for (int s = 0; s < nbs; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+    for (int t = 0; t < kSlabBlock; ++t) { mbar_init(&d_full[t], 1); mbar_init(&d_empty[t], kTfEpiWarps); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kTfEpiWarps) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 ::"r"(smem_u32(&tmem_base_smem)), "r"((uint32_t)kTfCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp == kTfEpiWarps) {
+    // ===================== producer =====================
+    if (lane == 0) {
+      uint32_t ua = 0, sb = 0, phb = 0;
+      for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
+        const TfItem item = a.items[k];
+        for (int gb = item.g_begin; gb < item.g_end; gb += kSlabBlock) {
+          const int ge = min(gb + kSlabBlock, item.g_end);
+          for (int s = 0; s < nslab; ++s) {
+            const uint32_t slot = ua & 1u;
+            mbar_wait(&a_empty[slot], ((ua >> 1) & 1u) ^ 1u);
+            mbar_expect_tx(&a_full[slot], a_bytes);
+            bulk_g2s(sA + (size_t)slot * a_bytes,
+                     a.Xa + ((size_t)item.I * nslab + s) * (a_bytes >> 2), a_bytes, &a_full[slot]);
+            ++ua;
+            for (int g = gb; g < ge; ++g) {
+              mbar_wait(&b_empty[sb], phb ^ 1u);
+              mbar_expect_tx(&b_full[sb], b_bytes);
+              bulk_g2s(sB + (size_t)sb * b_bytes, a.Xb + ((size_t)g * nslab + s) * (b_bytes >> 2),
+                       b_bytes, &b_full[sb]);
+              if (++sb == (uint32_t)nbs) { sb = 0; phb ^= 1u; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == kTfEpiWarps + 1) {
+    // ===================== MMA issuer =====================
+    uint32_t ua = 0, sb = 0, phb = 0, nd = 0;
+    const uint32_t a_lo00 = ((smem_u32(sA) >> 4) & 0x3FFFu) | ((2048u >> 4) << 16);
+    const uint32_t b_lo00 = ((smem_u32(sB) >> 4) & 0x3FFFu) | ((768u >> 4) << 16);
+    constexpr uint32_t desc_hi = (128u >> 4) | (1u << 14);
+    for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
+      const int g_begin = a.items[k].g_begin, g_end = a.items[k].g_end;
+      for (int gb = g_begin; gb < g_end; gb += kSlabBlock) {
+        const int cnt = min(kSlabBlock, g_end - gb);
+        for (int s = 0; s < nslab; ++s) {
+          const uint32_t slot = ua & 1u;
+          mbar_wait(&a_full[slot], (ua >> 1) & 1u);
+          ++ua;
+          const uint32_t a_lo0 = a_lo00 + slot * (a_bytes >> 4);
+          for (int gi = 0; gi < cnt; ++gi) {
+            const uint32_t my = nd + (uint32_t)gi, t = my % kSlabBlock;
+            if (s == 0) mbar_wait(&d_empty[t], ((my / kSlabBlock) & 1u) ^ 1u);
+            mbar_wait(&b_full[sb], phb);
+            tc_fence_after();
+            if (elect_one()) {
+              const uint32_t b_lo0 = b_lo00 + sb * (b_bytes >> 4);
+              const uint32_t d0 = tmem_base + t * kTfStageStride;
+#pragma unroll
+              for (int ks = 0; ks < kSlabKsteps; ++ks) {
+                const uint64_t bdesc = ((uint64_t)desc_hi << 32) | (b_lo0 + (uint32_t)ks * (2u * 768u >> 4));
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                  const uint64_t adesc = ((uint64_t)desc_hi << 32) |
+                                         (a_lo0 + (((uint32_t)c * a_comp_bytes + (uint32_t)ks * 4096u) >> 4));
+                  tc_mma_tf32(d0 + (uint32_t)(c * kTfAccStride), adesc, bdesc, kTfIdesc,
+                              (s > 0 || ks > 0) ? 1u : 0u);
+                }
+              }
+              tc_commit(&b_empty[sb]);
+              if (s == nslab - 1) tc_commit(&d_full[t]);
+            }
+            __syncwarp();
+            if (++sb == (uint32_t)nbs) { sb = 0; phb ^= 1u; }
+          }
+          if (elect_one()) tc_commit(&a_empty[slot]);      // slab slot reusable once its MMAs are done
+          __syncwarp();
+        }
+        nd += (uint32_t)cnt;
+      }
+    }
+  } else {
+    // ===================== epilogue (as in pair_tf32_kernel, three stages, D at column 0) =====
+    const int q = warp & 3, sq = warp >> 2;
+    uint32_t n = 0;
+    unsigned long long my_pairs = 0;
+    for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
+      const TfItem item = a.items[k];
+      const int i = item.I * 128 + q * 32 + lane;
+      const bool iok = i < a.nall;
+      const float hi = a.hn[i];
+      const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(sq * 4);
+      for (int g = item.g_begin; g < item.g_end; ++g) {
+        const uint32_t my = n++;
+        const uint32_t t = my % kSlabBlock, ph = (my / kSlabBlock) & 1u;
+        const bool gate = g < item.g_gate_end;
+        const bool slow = gate || (g * 16 + 15 >= item.I * 128);
+        uint32_t v[9][4];
+        mbar_wait(&d_full[t], ph);
+        tc_fence_after();
+        ld_batch(lane_base + t * kTfStageStride, v);
+        tc_wait_ld();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&d_empty[t]);
+        screen_batch(a, v, g * 16 + sq * 4, i, iok, hi, gate, slow, my_pairs);
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) my_pairs += __shfl_xor_sync(0xffffffffu, my_pairs, o);
+    if (lane == 0 && my_pairs) atomicAdd(a.npairs, my_pairs);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kTfEpiWarps) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;"
+                 ::"r"(tmem_base), "r"((uint32_t)kTfCols) : "memory");
+  }
+}
+
+// FP64 operand as pack_axis wrote it: chunks [panel][slab][comp][rows][KS]; column layout (A <= 88):
+// rows = 16, one slab; row-tile layout (A > 88): rows = 32, slabs of KU atom slots.
+struct XView {
+  const double* X;
+  int rows, nslab, KU, KS, npanel;
+  __device__ __forceinline__ const double* row(int i, int comp, int slab) const {
+    return X + ((((size_t)(i / rows) * nslab + slab) * 3 + comp) * rows + (i % rows)) * KS;
+  }
+};
+
+// One thread per (conformer, TF32 slab, comp, 4-slot chunk).  TF32 slot t = FP64 slot t (slabs of the
+// FP64 layout concatenated); kslab slots per TF32 slab, zero beyond the FP64 extent.
 __global__ void __launch_bounds__(256)
-tf32_convert_kernel(const double* __restrict__ X, const double* __restrict__ xn, int nall, int nunit,
-                    int KS, int KU, int ntile, float* __restrict__ Xa, float* __restrict__ Xb,
+tf32_convert_kernel(const XView xv, const double* __restrict__ xn, int nall, int ntile, int nslab_t,
+                    int kslab, float* __restrict__ Xa, float* __restrict__ Xb,
                     float* __restrict__ hn, double kappa) {
-  const int nchunk = KU >> 2;
-  const long long total = (long long)ntile * 128 * 3 * nchunk;
+  const int nchunk = kslab >> 2;
+  const long long total = (long long)ntile * 128 * 3 * nchunk * nslab_t;
   const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid < (long long)ntile * 128) {
     const int i = (int)tid;
@@ -398,29 +566,29 @@ tf32_convert_kernel(const double* __restrict__ X, const double* __restrict__ xn,
   const int r = (int)(tid % 128);
   long long rest = tid / 128;
   const int c = (int)(rest % nchunk); rest /= nchunk;
-  const int comp = (int)(rest % 3);
-  const int I = (int)(rest / 3);
+  const int comp = (int)(rest % 3); rest /= 3;
+  const int sl = (int)(rest % nslab_t);
+  const int I = (int)(rest / nslab_t);
   const int i = I * 128 + r;
   float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-  const int unit = i >> 4;
-  if (i < nall && unit < nunit) {
-    const double* src = X + ((size_t)(unit * 3 + comp) * 16 + (i & 15)) * KS + 4 * c;
+  const int t = sl * kslab + 4 * c;                   // first of 4 consecutive slots (same FP64 slab)
+  if (i < nall && i / xv.rows < xv.npanel && t < xv.nslab * xv.KU) {
+    const double* src = xv.row(i, comp, t / xv.KU) + (t % xv.KU);
     const double2 p0 = *reinterpret_cast<const double2*>(src);
     const double2 p1 = *reinterpret_cast<const double2*>(src + 2);
     o = make_float4(to_tf32_rn(p0.x), to_tf32_rn(p0.y), to_tf32_rn(p1.x), to_tf32_rn(p1.y));
   }
-  reinterpret_cast<float4*>(Xa)[(((size_t)I * 3 + comp) * nchunk + c) * 128 + r] = o;
+  reinterpret_cast<float4*>(Xa)[((((size_t)I * nslab_t + sl) * 3 + comp) * nchunk + c) * 128 + r] = o;
   const int g = i >> 4, jj = i & 15;
-  reinterpret_cast<float4*>(Xb)[((size_t)g * nchunk + c) * 48 + comp * 16 + jj] = o;
+  reinterpret_cast<float4*>(Xb)[(((size_t)g * nslab_t + sl) * nchunk + c) * 48 + comp * 16 + jj] = o;
 }
 
 // ---- exact pass over the candidate list: FP64 covariance, Newton/Jacobi, gates, atomicMax --------
 // 8 lanes per pair.  Decisions are those of pair_col.cu's unit_exact (same second-level screen,
 // same pair_e_exact, same float32-threshold emulation and rot gate).
 struct ExactArgs {
-  const double* X; const double* xn; const double* rot; const double* aniso;
+  XView xv; const double* xn; const double* rot; const double* aniso;
   const int2* cand; const unsigned* cand_count; unsigned cand_cap;
-  int KS, KU;
   Gates g;
   int* dup;
   unsigned* violations;   // debug (all_cand): pairs the screen called far whose exact e < E2
@@ -436,18 +604,20 @@ exact_cand_kernel(const ExactArgs a) {
     const int2 ij = live ? a.cand[p] : make_int2(0, 0);
     const int i = ij.x, j = ij.y & 0x7fffffff;
     const bool screen_far_flag = ij.y < 0;
-    const double* xi = a.X + ((size_t)(i >> 4) * 3 * 16 + (i & 15)) * a.KS;
-    const double* xj = a.X + ((size_t)(j >> 4) * 3 * 16 + (j & 15)) * a.KS;
-    const size_t cs = (size_t)16 * a.KS;
+    const size_t cs = (size_t)a.xv.rows * a.xv.KS;         // distance between components
     double r[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     if (live)
-      for (int k = sub; k < a.KU; k += 8) {
+     for (int sd = 0; sd < a.xv.nslab; ++sd) {
+      const double* xi = a.xv.row(i, 0, sd);
+      const double* xj = a.xv.row(j, 0, sd);
+      for (int k = sub; k < a.xv.KU; k += 8) {
         const double x0 = xi[k], x1 = xi[cs + k], x2 = xi[2 * cs + k];
         const double y0 = xj[k], y1 = xj[cs + k], y2 = xj[2 * cs + k];
         r[0] = fma(x0, y0, r[0]); r[1] = fma(x0, y1, r[1]); r[2] = fma(x0, y2, r[2]);
         r[3] = fma(x1, y0, r[3]); r[4] = fma(x1, y1, r[4]); r[5] = fma(x1, y2, r[5]);
         r[6] = fma(x2, y0, r[6]); r[7] = fma(x2, y1, r[7]); r[8] = fma(x2, y2, r[8]);
       }
+     }
 #pragma unroll
     for (int z = 0; z < 9; ++z) {
       r[z] += __shfl_xor_sync(gmask, r[z], 1);
@@ -484,13 +654,20 @@ int tf32_smem_bytes(int KU, int* nbstage_out) {
   return (int)(a_bytes + (size_t)ns * b_bytes);
 }
 
+static XView make_xview(const double* d_X, const PackLayout& L) {
+  XView v;
+  v.X = d_X; v.rows = L.rows; v.nslab = L.nslab; v.KU = L.KU; v.KS = L.KS; v.npanel = L.npanel;
+  return v;
+}
+
 int launch_tf32_convert(const double* d_X, const double* d_xn, int nall, const PackLayout& L,
-                        int ntile, float* d_Xa, float* d_Xb, float* d_hn, cudaStream_t stream) {
-  const long long total = (long long)ntile * 128 * 3 * (L.KU / 4);
+                        int ntile, int nslab_t, int kslab, float* d_Xa, float* d_Xb, float* d_hn,
+                        cudaStream_t stream) {
+  const long long total = (long long)ntile * 128 * 3 * (kslab / 4) * nslab_t;
   if (total <= 0) return 0;
   const int blocks = (int)((total + 255) / 256);
-  tf32_convert_kernel<<<blocks, 256, 0, stream>>>(d_X, d_xn, nall, L.npanel, L.KS, L.KU, ntile, d_Xa,
-                                                  d_Xb, d_hn, kTfKappa);
+  tf32_convert_kernel<<<blocks, 256, 0, stream>>>(make_xview(d_X, L), d_xn, nall, ntile, nslab_t, kslab,
+                                                  d_Xa, d_Xb, d_hn, kTfKappa);
   CREST_CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -513,9 +690,17 @@ int launch_pair_tf32(const PairArgs& pa, const Tf32Buffers& tb, const void* d_it
   a.Xa = tb.Xa; a.Xb = tb.Xb; a.hn = tb.hn; a.er = pa.er;
   a.items = static_cast<const TfItem*>(d_items);
   a.item_begin = item_begin; a.item_end = item_end;
-  a.nall = pa.nall; a.KU = pa.L.KU;
+  a.nall = pa.nall; a.KU = tb.kslab; a.nslab = tb.nslab;
+  const bool slab = tb.nslab > 1 || tb.kslab != pa.L.KU;
   int ns = 0;
-  const int smem = tf32_smem_bytes(a.KU, &ns);
+  int smem = 0;
+  if (slab) {
+    if (tb.kslab != 8 * kSlabKsteps) { set_error("tf32 slab kernel: slab of %d slots", tb.kslab); return 1; }
+    ns = kTfBStagesMax;
+    smem = 2 * 3 * (tb.kslab / 4) * 2048 + ns * (tb.kslab / 4) * 768;
+  } else {
+    smem = tf32_smem_bytes(a.KU, &ns);
+  }
   if (ns < 2) { set_error("tf32 kernel: K extent %d does not fit shared memory", a.KU); return 1; }
   a.nbstage = ns;
   a.cE = -0.5f * pa.g.E2_up;
@@ -527,6 +712,12 @@ int launch_pair_tf32(const PairArgs& pa, const Tf32Buffers& tb, const void* d_it
   CREST_CUDA_TRY(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
   const int grid = nitems < nsm ? nitems : nsm;
   int rc = 1;
+  if (slab) {
+    CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_slab_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    pair_tf32_slab_kernel<<<grid, kTfThreads, smem, stream>>>(a);
+    CREST_CUDA_TRY(cudaGetLastError());
+    rc = 0;
+  } else
   switch (a.KU / 8) {
     case 1: rc = launch_tf32_inst<1>(a, grid, smem, stream); break;
     case 2: rc = launch_tf32_inst<2>(a, grid, smem, stream); break;
@@ -543,9 +734,9 @@ int launch_pair_tf32(const PairArgs& pa, const Tf32Buffers& tb, const void* d_it
   }
   if (rc) return rc;
   ExactArgs e{};
-  e.X = pa.X; e.xn = pa.xn; e.rot = pa.rot; e.aniso = pa.aniso;
+  e.xv = make_xview(pa.X, pa.L); e.xn = pa.xn; e.rot = pa.rot; e.aniso = pa.aniso;
   e.cand = a.cand; e.cand_count = tb.cand_count; e.cand_cap = tb.cand_cap;
-  e.KS = pa.L.KS; e.KU = pa.L.KU; e.g = pa.g; e.dup = pa.dup;
+  e.g = pa.g; e.dup = pa.dup;
   e.violations = all_cand ? tb.cand_count + 2 : nullptr;
   exact_cand_kernel<<<nsm * 4, 256, 0, stream>>>(e);
   CREST_CUDA_TRY(cudaGetLastError());

@@ -55,6 +55,7 @@ struct TileCursor {
 
 __global__ void __launch_bounds__(kPairThreads, 1)
 pair_tile_kernel(const PairArgs a, const int nstage) {
+  if (a.run_if && *a.run_if == 0u) return;   // fallback behind the tensor-core screen: idle unless it overflowed
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kMaxStages];
   __shared__ __align__(8) uint64_t empty_bar[kMaxStages];

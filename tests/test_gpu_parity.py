@@ -366,14 +366,16 @@ def _stage_a(cb, ens, env, tune=None, debug=None):
 
 @pytest.mark.parametrize("cfg,nall,ethr", [("C1", 1000, 1e9), ("C1", 1000, 0.05), ("C1", 1000, 0.0),
                                            ("C2", 3000, 1e9), ("C2", 3000, 0.1), ("C5", 5000, 1e9),
-                                           ("C5", 4097, 0.3), ("C3", 20000, 1e9)])
+                                           ("C5", 4097, 0.3), ("C3", 20000, 1e9),
+                                           ("C4", 1500, 1e9), ("C4", 1100, 0.3)])
 def test_tf32_equals_fp64_kernels(cb, cfg, nall, ethr):
     ens = synth.make_config(cfg, nall=nall, seed=99)
     env = cb.Env(ethr=ethr, heavyrmsd=ens["heavy"])
     l_tf, r_tf, i_tf = _stage_a(cb, ens, env)
     l_col, r_col, i_col = _stage_a(cb, ens, env, "notf32")
     l_til, r_til, i_til = _stage_a(cb, ens, env, "notf32,tile")
-    assert (i_tf["variant"], i_col["variant"], i_til["variant"]) == (2, 1, 0)
+    # A <= 88: one-slab kernel vs column + row-tile DMMA; A > 88 (C4): K-slab kernel vs row-tile DMMA
+    assert (i_tf["variant"], i_col["variant"], i_til["variant"]) == (2, 1 if i_tf["A"] <= 88 else 0, 0)
     assert i_tf["overflow"] == 0
     assert l_tf["npairs"] == l_col["npairs"] == l_til["npairs"]
     assert np.array_equal(l_tf["dup"], l_col["dup"]) and np.array_equal(l_tf["dup"], l_til["dup"])
@@ -394,6 +396,7 @@ def test_tf32_screen_selfcheck(cb):
     ens = synth.make_ensemble(1400, 40, 40, copies=20, seed=8, frac_straddle=0.6, frac_mirror=0.2)
     ens["heavy"] = False
     cases.append((ens, cb.Env(ethr=1e9)))
+    cases.append((synth.make_config("C4", nall=500, seed=6), cb.Env(ethr=1e9)))     # K-slab kernel
     for name in ("adv_chiral", "adv_linear", "adv_planar"):
         g = np.load(os.path.join(GOLDEN, name + ".npz"))
         cases.append((dict(at=g["at"], xyz=g["xyz"], er=g["er"], heavy=False),
