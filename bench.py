@@ -32,7 +32,7 @@ UNIT = "pairs/s"
 def parse():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--steps", type=int, default=20)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--workload", default="C3", choices=["C1", "C2", "C3", "C4", "C5"])
@@ -59,24 +59,44 @@ def workload_config(args, ens):
 
 
 class ClockSampler:
-    """nvidia-smi clock / throttle sampling during the timed region (B200_PROFILING.md)."""
+    """nvidia-smi clock / throttle sampling during the timed region (B200_PROFILING.md).
+
+    The nvidia-smi process is started BEFORE the warm-up (a fork inside the timed region stalls the
+    launching thread for milliseconds); `begin()` / `stop()` bracket the timed region by wall clock and
+    only the samples stamped inside that window (plus the one straddling its end) are reported."""
+
+    PERIOD_MS = 20
 
     def __init__(self, index):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
-        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+        self.t0 = self.t1 = None
+        q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
              "clocks_event_reasons.sw_power_cap")
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={q}",
-                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                       "--format=csv,noheader,nounits", "-lms", str(self.PERIOD_MS)],
                                       stdout=self.f, stderr=subprocess.DEVNULL)
         except OSError:
             self.p = None
 
+    def begin(self):
+        self.t0 = time.time()
+
+    @staticmethod
+    def _stamp(txt):
+        import datetime
+        try:
+            return datetime.datetime.strptime(txt, "%Y/%m/%d %H:%M:%S.%f").timestamp()
+        except ValueError:
+            return None
+
     def stop(self):
+        self.t1 = time.time()
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
         if self.p is None:
             return out
+        time.sleep(2.5 * self.PERIOD_MS * 1e-3)   # let the sample straddling the end land
         self.p.terminate()
         try:
             self.p.wait(timeout=5)
@@ -84,30 +104,34 @@ class ClockSampler:
             self.p.kill()
         self.f.flush()
         self.f.seek(0)
-        sm, reasons, mx = [], set(), None
+        rows = []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in self.f.read().splitlines():
             parts = [x.strip() for x in line.split(",")]
-            if len(parts) < 7:
+            if len(parts) < 8:
                 continue
             try:
-                sm.append(float(parts[0]))
-                mx = float(parts[1])
+                rows.append((self._stamp(parts[0]), float(parts[1]), float(parts[2]),
+                             [nm for nm, v in zip(names, parts[4:8]) if v.lower().startswith("active")]))
             except ValueError:
                 continue
-            for nm, v in zip(names, parts[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
         self.f.close()
         try:
             os.unlink(self.f.name)
         except OSError:
             pass
-        if sm:
-            out["sm_mhz"] = float(np.median(sm))
-            out["sm_max_mhz"] = mx
-            out["samples"] = len(sm)
-        out["reasons"] = sorted(reasons)
+        t0 = self.t0 if self.t0 is not None else 0.0
+        slack = self.PERIOD_MS * 1e-3
+        inside = [r for r in rows if r[0] is not None and t0 <= r[0] <= self.t1 + slack]
+        if not inside:          # timed region shorter than one period: take the first sample after it began
+            later = [r for r in rows if r[0] is not None and r[0] >= t0]
+            inside = later[:1] if later else rows[-1:]
+        if inside:
+            out["sm_mhz"] = float(np.median([r[1] for r in inside]))
+            out["sm_max_mhz"] = inside[-1][2]
+            out["samples"] = len(inside)
+            out["period_ms"] = self.PERIOD_MS
+            out["reasons"] = sorted({nm for r in inside for nm in r[3]})
         return out
 
 
@@ -268,10 +292,12 @@ def run_ours(args):
             dist.barrier()
             torch.cuda.synchronize()
 
+    sampler = ClockSampler(local) if rank == 0 else None
     for _ in range(args.warmup):
         step()
     sync_all()
-    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.begin()
     t_beg = torch.cuda.Event(enable_timing=True)
     t_end = torch.cuda.Event(enable_timing=True)
     kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
@@ -360,8 +386,8 @@ def run_ours(args):
         variant = {0: "pair_tile (DMMA row tiles)", 1: "pair_col (DMMA column sweep)",
                    2: "pair_tf32 (tcgen05 TF32 screen) + exact_cand (FP64 list)"}[info["variant"]]
         # dram__bytes_read.sum + dram__bytes_write.sum of pair_tf32_kernel<8>, one launch, from the
-        # committed ncu --set full capture of this command (profiles/r01_v9_pair_tf32_ncu_full_summary.txt)
-        traffic = (230705408 + 6848000 if (info["variant"] == 2 and args.workload == "C3" and
+        # committed ncu --set full capture of this command (profiles/r01_v10_pair_tf32_ncu_full_summary.txt)
+        traffic = (228115712 + 7774208 if (info["variant"] == 2 and args.workload == "C3" and
                                            args.nall is None and world == 1 and args.ethr > 1e8) else None)
         if info["variant"] == 2:
             peak = tf32_peak_tflops(torch, dev)
