@@ -150,7 +150,7 @@ struct TfArgs {
 
 // FP32 screen of the 4 pairs (i, j0..j0+3) of this lane + candidate emission
 __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v)[9][4], int j0, int i,
-                                             bool iok, float hi, bool gate, bool slow,
+                                             bool iok, f2_t hic2, bool gate, bool slow,
                                              unsigned long long& my_pairs) {
   const float4 h0 = __ldg(reinterpret_cast<const float4*>(a.hn + j0));
   const float hj[4] = {h0.x, h0.y, h0.z, h0.w};
@@ -182,8 +182,7 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
       f2_t rp[9];
 #pragma unroll
       for (int z = 0; z < 9; ++z) rp[z] = f2_pack_u(v[z][p], v[z][p + 1]);
-      const f2_t lam2 = f2_pack(__fadd_rd(__fadd_rd(hi, hj[p]), a.cE),
-                                __fadd_rd(__fadd_rd(hi, hj[p + 1]), a.cE));
+      const f2_t lam2 = f2_add_rd(hic2, f2_pack(hj[p], hj[p + 1]));   // rd(rd(hn_i + cE) + hn_j) <= the exact sum
       farbits |= screen_far_f32x2(rp, lam2, a.enantio) << p;
     }
   }
@@ -324,7 +323,8 @@ pair_tf32_kernel(const TfArgs a) {
       const TfItem item = a.items[k];
       const int i = item.I * 128 + q * 32 + lane;
       const bool iok = i < a.nall;
-      const float hi = a.hn[i];
+      const float hic = __fadd_rd(a.hn[i], a.cE);
+      const f2_t hic2 = f2_pack(hic, hic);
       if (TS && warp < 4) {
         // move the i-tile shared memory -> TMEM: this lane's row, 3 x K columns.  The previous
         // tile's MMAs must have completed (at_empty), the new tile must have landed (a_full).
@@ -361,7 +361,7 @@ pair_tf32_kernel(const TfArgs a) {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&d_empty[t]);       // this warp's 4 pairs are in registers
-        screen_batch(a, v, g * 16 + sq * 4, i, iok, hi, gate, slow, my_pairs);
+        screen_batch(a, v, g * 16 + sq * 4, i, iok, hic2, gate, slow, my_pairs);
       }
     }
 #pragma unroll
@@ -509,7 +509,8 @@ pair_tf32_slab_kernel(const TfArgs a) {
       const TfItem item = a.items[k];
       const int i = item.I * 128 + q * 32 + lane;
       const bool iok = i < a.nall;
-      const float hi = a.hn[i];
+      const float hic = __fadd_rd(a.hn[i], a.cE);
+      const f2_t hic2 = f2_pack(hic, hic);
       const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(sq * 4);
       for (int g = item.g_begin; g < item.g_end; ++g) {
         const uint32_t my = n++;
@@ -524,7 +525,7 @@ pair_tf32_slab_kernel(const TfArgs a) {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&d_empty[t]);
-        screen_batch(a, v, g * 16 + sq * 4, i, iok, hi, gate, slow, my_pairs);
+        screen_batch(a, v, g * 16 + sq * 4, i, iok, hic2, gate, slow, my_pairs);
       }
     }
 #pragma unroll

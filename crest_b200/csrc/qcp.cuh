@@ -233,9 +233,7 @@ __device__ __forceinline__ bool screen_far_f32(const float* r, float lam, int en
 // modifier in PTX): I2 comes from the Gram matrix G = R^T R,
 //     4*I2 = 2*(I1^2 - ||G||_F^2),  I1 = tr G,
 // so the only differences of products left are the three cofactors of det R, which use
-// sign-flipped copies of row 2 (integer XOR, ALU pipe).  Same test point, same floors and the same
-// proof as screen_far_f32; P, P' and P''/2*... are evaluated as
-//     u = lam^2 - I1,  P = u^2 + 2||G||^2 - 2 I1^2 + c1*lam,  P' = 4 lam u + c1,  P'' = 6 lam^2 - 2 I1.
+// sign-flipped copies of row 2 (integer XOR, ALU pipe).  Same test point and floors as screen_far_f32.
 typedef unsigned long long f2_t;   // two floats: lo = first pair, hi = second pair
 __device__ __forceinline__ f2_t f2_pack(float lo, float hi) {
   f2_t r;
@@ -273,8 +271,26 @@ __device__ __forceinline__ f2_t f2_sub(f2_t a, f2_t b) {
 __device__ __forceinline__ f2_t f2_neg(f2_t a) { return a ^ 0x8000000080000000ull; }
 __device__ __forceinline__ f2_t f2_abs(f2_t a) { return a & 0x7FFFFFFF7FFFFFFFull; }
 
+__device__ __forceinline__ f2_t f2_add_rd(f2_t a, f2_t b) {   // round toward -inf (test points)
+  f2_t r;
+  asm("add.rm.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+
 // r[3a+b] packed covariance of two pairs, lam packed test points.  Returns bit 0 / bit 1 = pair
-// 0 / 1 is PROVEN far (same meaning as screen_far_f32).
+// 0 / 1 is PROVEN far, i.e. lambda_max < lam.
+//
+// Two signs instead of the four of Budan-Fourier: the key matrix is symmetric and traceless, so its
+// eigenvalues l1 >= l2 >= l3 >= l4 satisfy sum = 0 and sum of squares = 4*I1 (the lambda^2
+// coefficient of P).  With l1 >= l2 = a >= 0: l3 + l4 <= -2a, hence l3^2 + l4^2 >= 2a^2 and
+// 4*I1 >= 4a^2, i.e.  l2 <= sqrt(I1)  always.  Therefore
+//     lam > 0,  lam^2 > I1,  P(lam) > 0     =>     lam > l2 and P > 0     =>     lam > l1
+// (between l2 and l1 the quartic is negative).  With both det signs wanted (enantio) P is evaluated
+// with -8*|det|*lam, the smaller of the two.  Evaluation: u = lam^2 - I1,
+//     P = u^2 + 2*(||G||^2 - I1^2) - 8*det*lam = u^2 + 2*x,  x = ||G||^2 - I1^2 - 4*det*lam,
+// every term bounded by lam^4 once u > 0; FP32 evaluation error < 100 * 2^-24 of lam^2 (u) and
+// lam^4 (P); both signs are required with a floor of 2e-4 of those scales.  NaN / Inf compare
+// false => undecided.  45 packed FMA-pipe instructions per two pairs (52 for the four-sign form).
 __device__ __forceinline__ unsigned screen_far_f32x2(const f2_t* r, f2_t lam, int enantio) {
   // Gram matrix G = R^T R (columns of R): g_bc = sum_a r[3a+b] r[3a+c]
   const f2_t g00 = f2_fma(r[6], r[6], f2_fma(r[3], r[3], f2_mul(r[0], r[0])));
@@ -286,33 +302,26 @@ __device__ __forceinline__ unsigned screen_far_f32x2(const f2_t* r, f2_t lam, in
   const f2_t i1 = f2_add(f2_add(g00, g11), g22);
   const f2_t hoff = f2_fma(g12, g12, f2_fma(g02, g02, f2_mul(g01, g01)));
   const f2_t dsq = f2_fma(g22, g22, f2_fma(g11, g11, f2_mul(g00, g00)));
-  const f2_t two = f2_pack(2.0f, 2.0f);
-  const f2_t ng = f2_fma(two, hoff, dsq);                      // ||G||_F^2
+  const f2_t ng = f2_fma(f2_pack(2.0f, 2.0f), hoff, dsq);      // ||G||_F^2
   // det R by row 0; cofactors k0b = minors of rows 1,2 with n = -row 2
   const f2_t n6 = f2_neg(r[6]), n7 = f2_neg(r[7]), n8 = f2_neg(r[8]);
   const f2_t k00 = f2_fma(r[5], n7, f2_mul(r[4], r[8]));       // r4 r8 - r5 r7
   const f2_t k01 = f2_fma(r[3], n8, f2_mul(r[5], r[6]));       // r5 r6 - r3 r8
   const f2_t k02 = f2_fma(r[4], n6, f2_mul(r[3], r[7]));       // r3 r7 - r4 r6
   const f2_t det = f2_fma(r[0], k00, f2_fma(r[1], k01, f2_mul(r[2], k02)));
-  const f2_t c1 = f2_mul(enantio ? f2_abs(det) : det, f2_pack(-8.0f, -8.0f));
   const f2_t l2 = f2_mul(lam, lam);
   const f2_t u = f2_sub(l2, i1);
-  const f2_t w1 = f2_fma(u, u, f2_add(ng, ng));                // u^2 + 2||G||^2
-  const f2_t i1sq2 = f2_mul(f2_add(i1, i1), i1);               // 2 I1^2
-  const f2_t P = f2_fma(c1, lam, f2_sub(w1, i1sq2));
-  const f2_t dP = f2_fma(f2_mul(lam, f2_pack(4.0f, 4.0f)), u, c1);
-  const f2_t ddP = f2_fma(f2_pack(-2.0f, -2.0f), i1, f2_mul(l2, f2_pack(6.0f, 6.0f)));
-  float l2a, l2b, i1a, i1b;
-  f2_unpack(l2, l2a, l2b);
-  f2_unpack(i1, i1a, i1b);
-  const f2_t M = f2_pack(fmaxf(l2a, i1a), fmaxf(l2b, i1b));
-  const f2_t fl = f2_mul(M, f2_pack(2e-4f, 2e-4f));
-  const f2_t flM = f2_mul(fl, M), fll = f2_mul(fl, lam);
-  float Pa, Pb, dPa, dPb, ddPa, ddPb, fa, fb, fMa, fMb, fla, flb, la, lb;
-  f2_unpack(P, Pa, Pb); f2_unpack(dP, dPa, dPb); f2_unpack(ddP, ddPa, ddPb);
-  f2_unpack(fl, fa, fb); f2_unpack(flM, fMa, fMb); f2_unpack(fll, fla, flb); f2_unpack(lam, la, lb);
-  const bool far0 = (la > 0.0f) & (la < 6.0e29f) & (Pa > fMa) & (dPa > fla) & (ddPa > fa);
-  const bool far1 = (lb > 0.0f) & (lb < 6.0e29f) & (Pb > fMb) & (dPb > flb) & (ddPb > fb);
+  const f2_t x0 = f2_fma(f2_neg(i1), i1, ng);                  // ||G||^2 - I1^2
+  const f2_t lm4 = f2_mul(lam, f2_pack(-4.0f, -4.0f));
+  const f2_t x = f2_fma(enantio ? f2_abs(det) : det, lm4, x0);
+  const f2_t P = f2_fma(x, f2_pack(2.0f, 2.0f), f2_mul(u, u));
+  const f2_t fl = f2_mul(l2, f2_pack(2e-4f, 2e-4f));
+  const f2_t flM = f2_mul(fl, l2);
+  float Pa, Pb, ua, ub, fa, fb, fMa, fMb, la, lb;
+  f2_unpack(P, Pa, Pb); f2_unpack(u, ua, ub);
+  f2_unpack(fl, fa, fb); f2_unpack(flM, fMa, fMb); f2_unpack(lam, la, lb);
+  const bool far0 = (la > 0.0f) & (ua > fa) & (Pa > fMa);
+  const bool far1 = (lb > 0.0f) & (ub > fb) & (Pb > fMb);
   return (far0 ? 1u : 0u) | (far1 ? 2u : 0u);
 }
 
