@@ -149,10 +149,14 @@ struct TfArgs {
 };
 
 // FP32 screen of the 4 pairs (i, j0..j0+3) of this lane + candidate emission
-__device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v)[9][4], int j0, int i,
-                                             bool iok, f2_t hic2, bool gate, bool slow,
-                                             unsigned long long& my_pairs) {
-  const float4 h0 = __ldg(reinterpret_cast<const float4*>(a.hn + j0));
+// DBG = false is the production instantiation: no timing switches, no self-check tagging.
+// farmask = 0xF when the row's half test point rd(hn_i + cE) is positive (then every lam of the row is,
+// because hn_j >= 0 and rounding down is monotone), else 0: the row goes to the exact pass.
+template <bool DBG>
+__device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v)[9][4], const float* hnp,
+                                             int j0, int i, bool iok, f2_t hic2, unsigned farmask,
+                                             bool gate, bool slow, unsigned long long& my_pairs) {
+  const float4 h0 = __ldg(reinterpret_cast<const float4*>(hnp));
   const float hj[4] = {h0.x, h0.y, h0.z, h0.w};
   // which pairs count: j < i, inside the ensemble, inside the energy band (cregen.f90:1275)
   unsigned ok = iok ? 0xFu : 0u;
@@ -169,7 +173,7 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
   }
   my_pairs += __popc(ok);
   unsigned farbits = 0;
-  if (a.dbg == 4 || a.dbg >= 6) {   // timing experiment: keep the loads live, skip the screen
+  if (DBG && (a.dbg == 4 || a.dbg >= 6)) {   // timing experiment: keep the loads live, skip the screen
     unsigned x = 0;
 #pragma unroll
     for (int z = 0; z < 9; ++z)
@@ -186,7 +190,8 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
       farbits |= screen_far_f32x2(rp, lam2, a.enantio) << p;
     }
   }
-  unsigned cand = a.all_cand ? 0xFu : (~farbits & 0xFu);
+  farbits &= farmask;
+  unsigned cand = (DBG && a.all_cand) ? 0xFu : (~farbits & 0xFu);
   cand &= ok;
   if (cand) {
 #pragma unroll 1
@@ -195,7 +200,7 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
       const unsigned idx = atomicAdd(a.cand_count, 1u);
       if (idx < a.cand_cap) {
         int jj = j0 + p;
-        if (a.all_cand && ((farbits >> p) & 1u)) jj |= (int)0x80000000u;
+        if (DBG && a.all_cand && ((farbits >> p) & 1u)) jj |= (int)0x80000000u;
         a.cand[idx] = make_int2(i, jj);
       } else {
         a.cand_count[1] = 1u;
@@ -204,7 +209,36 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
   }
 }
 
-template <int KSTEPS>
+// Epilogue of one work item, shared by both kernels: per j-group wait for the accumulator stage, pull
+// this warp's 4 pairs per lane out of TMEM, hand the stage back, screen.  Barrier addresses and the
+// ring position live in registers (pinned through an empty asm so that they are not rematerialised
+// from special registers every group).
+template <int NST, bool DBG>
+__device__ __forceinline__ void epilogue_groups(const TfArgs& a, const TfItem& item, int i, bool iok, int sq, int lane,
+                                                uint32_t lane_base, uint32_t dfull0, uint32_t dempty0,
+                                                uint32_t& t, uint32_t& ph, unsigned long long& my_pairs) {
+  const float hic = __fadd_rd(a.hn[i], a.cE);
+  const f2_t hic2 = f2_pack(hic, hic);
+  const unsigned farmask = hic > 0.0f ? 0xFu : 0u;
+  const float* hnp = a.hn + item.g_begin * 16 + sq * 4;
+  const int g_diag = item.I * 8;                          // first group with g*16 + 15 >= I*128
+  for (int g = item.g_begin; g < item.g_end; ++g, hnp += 16) {
+    const bool gate = g < item.g_gate_end;
+    const bool slow = gate || (g >= g_diag);
+    uint32_t v[9][4];
+    mbar_wait_a(dfull0 + 8u * t, ph);
+    tc_fence_after();
+    ld_batch(lane_base + t * (uint32_t)kTfStageStride, v);
+    tc_wait_ld();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive_a(dempty0 + 8u * t);      // this warp's 4 pairs are in registers
+    screen_batch<DBG>(a, v, hnp, g * 16 + sq * 4, i, iok, hic2, farmask, gate, slow, my_pairs);
+    if (++t == (uint32_t)NST) { t = 0; ph ^= 1u; }
+  }
+}
+
+template <int KSTEPS, bool DBG>
 __global__ void __launch_bounds__(kTfThreads, 1)
 pair_tf32_kernel(const TfArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -278,7 +312,7 @@ pair_tf32_kernel(const TfArgs a) {
         mbar_wait(&d_empty[td], phd ^ 1);              // epilogue drained this TMEM stage
         mbar_wait(&b_full[sb], phb);
         tc_fence_after();
-        if (a.dbg < 5 && elect_one()) {
+        if (!(DBG && a.dbg >= 5) && elect_one()) {
           const uint32_t b_lo0 = b_lo00 + sb * (b_bytes >> 4);
           const uint32_t d0 = tmem_base + kDBase + td * kTfStageStride;
 #pragma unroll
@@ -299,7 +333,7 @@ pair_tf32_kernel(const TfArgs a) {
           }
           tc_commit(&b_empty[sb]);     // smem slot reusable once these MMAs have read it
           tc_commit(&d_full[td]);      // accumulators of this group complete
-        } else if (a.dbg >= 5 && elect_one()) {
+        } else if (DBG && a.dbg >= 5 && elect_one()) {
           tc_commit(&b_empty[sb]);
           tc_commit(&d_full[td]);
         }
@@ -316,15 +350,17 @@ pair_tf32_kernel(const TfArgs a) {
     // pulls its 4 pairs per lane (36 registers of covariance) out of TMEM, hands the accumulator
     // stage back at once and screens them.  Four warps per SM sub-partition at different points of
     // wait / load / screen keep the FMA pipe fed.
-    const int q = warp & 3, sq = warp >> 2;
-    uint32_t n = 0, pht = 0;
+    int q = warp & 3, sq = warp >> 2, lane_p = lane;
+    asm volatile("" : "+r"(q), "+r"(sq), "+r"(lane_p));   // keep them in registers (no S2R per group)
+    uint32_t t = 0, ph = 0, pht = 0;
+    uint32_t dfull0 = smem_u32(&d_full[0]), dempty0 = smem_u32(&d_empty[0]);
+    asm volatile("" : "+r"(dfull0), "+r"(dempty0));
     unsigned long long my_pairs = 0;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + kDBase + (uint32_t)(sq * 4);
     for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
       const TfItem item = a.items[k];
       const int i = item.I * 128 + q * 32 + lane;
       const bool iok = i < a.nall;
-      const float hic = __fadd_rd(a.hn[i], a.cE);
-      const f2_t hic2 = f2_pack(hic, hic);
       if (TS && warp < 4) {
         // move the i-tile shared memory -> TMEM: this lane's row, 3 x K columns.  The previous
         // tile's MMAs must have completed (at_empty), the new tile must have landed (a_full).
@@ -347,22 +383,7 @@ pair_tf32_kernel(const TfArgs a) {
         __syncwarp();
         if (lane == 0) { mbar_arrive(&at_full); mbar_arrive(&a_empty); }
       }
-      const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + kDBase + (uint32_t)(sq * 4);
-      for (int g = item.g_begin; g < item.g_end; ++g) {
-        const uint32_t my = n++;
-        const uint32_t t = my % kTfDStages, ph = (my / kTfDStages) & 1u;
-        const bool gate = g < item.g_gate_end;
-        const bool slow = gate || (g * 16 + 15 >= item.I * 128);
-        uint32_t v[9][4];
-        mbar_wait(&d_full[t], ph);
-        tc_fence_after();
-        ld_batch(lane_base + t * kTfStageStride, v);
-        tc_wait_ld();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&d_empty[t]);       // this warp's 4 pairs are in registers
-        screen_batch(a, v, g * 16 + sq * 4, i, iok, hic2, gate, slow, my_pairs);
-      }
+      epilogue_groups<kTfDStages, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, my_pairs);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) my_pairs += __shfl_xor_sync(0xffffffffu, my_pairs, o);
@@ -396,6 +417,7 @@ __device__ __forceinline__ float to_tf32_rn(double x) {
 constexpr int kSlabKsteps = 6;                       // 48 atom slots per slab
 constexpr int kSlabBlock = 3;                        // j-groups per block = TMEM stages
 
+template <bool DBG>
 __global__ void __launch_bounds__(kTfThreads, 1)
 pair_tf32_slab_kernel(const TfArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -502,31 +524,18 @@ pair_tf32_slab_kernel(const TfArgs a) {
     }
   } else {
     // ===================== epilogue (as in pair_tf32_kernel, three stages, D at column 0) =====
-    const int q = warp & 3, sq = warp >> 2;
-    uint32_t n = 0;
+    int q = warp & 3, sq = warp >> 2, lane_p = lane;
+    asm volatile("" : "+r"(q), "+r"(sq), "+r"(lane_p));   // keep them in registers (no S2R per group)
+    uint32_t t = 0, ph = 0;
+    uint32_t dfull0 = smem_u32(&d_full[0]), dempty0 = smem_u32(&d_empty[0]);
+    asm volatile("" : "+r"(dfull0), "+r"(dempty0));
     unsigned long long my_pairs = 0;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(sq * 4);
     for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
       const TfItem item = a.items[k];
       const int i = item.I * 128 + q * 32 + lane;
       const bool iok = i < a.nall;
-      const float hic = __fadd_rd(a.hn[i], a.cE);
-      const f2_t hic2 = f2_pack(hic, hic);
-      const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(sq * 4);
-      for (int g = item.g_begin; g < item.g_end; ++g) {
-        const uint32_t my = n++;
-        const uint32_t t = my % kSlabBlock, ph = (my / kSlabBlock) & 1u;
-        const bool gate = g < item.g_gate_end;
-        const bool slow = gate || (g * 16 + 15 >= item.I * 128);
-        uint32_t v[9][4];
-        mbar_wait(&d_full[t], ph);
-        tc_fence_after();
-        ld_batch(lane_base + t * kTfStageStride, v);
-        tc_wait_ld();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&d_empty[t]);
-        screen_batch(a, v, g * 16 + sq * 4, i, iok, hic2, gate, slow, my_pairs);
-      }
+      epilogue_groups<kSlabBlock, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, my_pairs);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) my_pairs += __shfl_xor_sync(0xffffffffu, my_pairs, o);
@@ -675,9 +684,16 @@ int launch_tf32_convert(const double* d_X, const double* d_xn, int nall, const P
 
 template <int KSTEPS>
 static int launch_tf32_inst(const TfArgs& a, int grid, int smem, cudaStream_t stream) {
-  CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_kernel<KSTEPS>,
+  if (a.dbg != 0 || a.all_cand) {
+    CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_kernel<KSTEPS, true>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    pair_tf32_kernel<KSTEPS, true><<<grid, kTfThreads, smem, stream>>>(a);
+    CREST_CUDA_TRY(cudaGetLastError());
+    return 0;
+  }
+  CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_kernel<KSTEPS, false>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  pair_tf32_kernel<KSTEPS><<<grid, kTfThreads, smem, stream>>>(a);
+  pair_tf32_kernel<KSTEPS, false><<<grid, kTfThreads, smem, stream>>>(a);
   CREST_CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -714,8 +730,13 @@ int launch_pair_tf32(const PairArgs& pa, const Tf32Buffers& tb, const void* d_it
   const int grid = nitems < nsm ? nitems : nsm;
   int rc = 1;
   if (slab) {
-    CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_slab_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    pair_tf32_slab_kernel<<<grid, kTfThreads, smem, stream>>>(a);
+    if (a.dbg != 0 || a.all_cand) {
+      CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_slab_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      pair_tf32_slab_kernel<true><<<grid, kTfThreads, smem, stream>>>(a);
+    } else {
+      CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_slab_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      pair_tf32_slab_kernel<false><<<grid, kTfThreads, smem, stream>>>(a);
+    }
     CREST_CUDA_TRY(cudaGetLastError());
     rc = 0;
   } else
