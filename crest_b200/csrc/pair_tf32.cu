@@ -116,12 +116,19 @@ __device__ __forceinline__ void tc_ld4(uint32_t taddr, uint32_t (&v)[4]) {
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(taddr));
 }
-// 9 x (32 lanes x 4 columns) TMEM loads: v[3c+b][p] = R_cb of pair (lane, p), a batch of 4 pairs
+// The 48 B rows of a j-group are ordered (j-quarter s, component b, j within the quarter), so TMEM
+// column 48a + 12s + 4b + p holds R_ab(lane, j0 + 4s + p): the 36 values of a warp's 4 pairs are three
+// runs of 12 columns, read with one x8 and one x4 load each.  v[3a+b][p] = R_ab of pair (lane, p).
 __device__ __forceinline__ void ld_batch(uint32_t taddr, uint32_t (&v)[9][4]) {
 #pragma unroll
-  for (int c = 0; c < 3; ++c)
-#pragma unroll
-    for (int b = 0; b < 3; ++b) tc_ld4(taddr + (uint32_t)(c * kTfAccStride + b * 16), v[3 * c + b]);
+  for (int c = 0; c < 3; ++c) {
+    const uint32_t t = taddr + (uint32_t)(c * kTfAccStride);
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(v[3 * c][0]), "=r"(v[3 * c][1]), "=r"(v[3 * c][2]), "=r"(v[3 * c][3]),
+                   "=r"(v[3 * c + 1][0]), "=r"(v[3 * c + 1][1]), "=r"(v[3 * c + 1][2]), "=r"(v[3 * c + 1][3])
+                 : "r"(t));
+    tc_ld4(t + 8u, v[3 * c + 2]);
+  }
 }
 
 struct TfItem { int I; int g_begin; int g_end; int g_gate_end; };
@@ -356,7 +363,7 @@ pair_tf32_kernel(const TfArgs a) {
     uint32_t dfull0 = smem_u32(&d_full[0]), dempty0 = smem_u32(&d_empty[0]);
     asm volatile("" : "+r"(dfull0), "+r"(dempty0));
     unsigned long long my_pairs = 0;
-    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + kDBase + (uint32_t)(sq * 4);
+    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + kDBase + (uint32_t)(sq * 12);
     for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
       const TfItem item = a.items[k];
       const int i = item.I * 128 + q * 32 + lane;
@@ -530,7 +537,7 @@ pair_tf32_slab_kernel(const TfArgs a) {
     uint32_t dfull0 = smem_u32(&d_full[0]), dempty0 = smem_u32(&d_empty[0]);
     asm volatile("" : "+r"(dfull0), "+r"(dempty0));
     unsigned long long my_pairs = 0;
-    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(sq * 4);
+    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(sq * 12);
     for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
       const TfItem item = a.items[k];
       const int i = item.I * 128 + q * 32 + lane;
@@ -590,7 +597,7 @@ tf32_convert_kernel(const XView xv, const double* __restrict__ xn, int nall, int
   }
   reinterpret_cast<float4*>(Xa)[((((size_t)I * nslab_t + sl) * 3 + comp) * nchunk + c) * 128 + r] = o;
   const int g = i >> 4, jj = i & 15;
-  reinterpret_cast<float4*>(Xb)[(((size_t)g * nslab_t + sl) * nchunk + c) * 48 + comp * 16 + jj] = o;
+  reinterpret_cast<float4*>(Xb)[(((size_t)g * nslab_t + sl) * nchunk + c) * 48 + (jj >> 2) * 12 + comp * 4 + (jj & 3)] = o;
 }
 
 // ---- exact pass over the candidate list: FP64 covariance, Newton/Jacobi, gates, atomicMax --------

@@ -268,7 +268,11 @@ __device__ __forceinline__ f2_t f2_sub(f2_t a, f2_t b) {
   asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
   return r;
 }
-__device__ __forceinline__ f2_t f2_neg(f2_t a) { return a ^ 0x8000000080000000ull; }
+__device__ __forceinline__ f2_t f2_neg(f2_t a) {   // written per half so that ptxas can fold it into an operand modifier
+  float lo, hi;
+  f2_unpack(a, lo, hi);
+  return f2_pack(-lo, -hi);
+}
 __device__ __forceinline__ f2_t f2_abs(f2_t a) { return a & 0x7FFFFFFF7FFFFFFFull; }
 
 __device__ __forceinline__ f2_t f2_add_rd(f2_t a, f2_t b) {   // round toward -inf (test points)
