@@ -488,7 +488,8 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
       c->cap_tf_hn = nh;
     }
     if (!c->tf.cand_count) {
-      CREST_CUDA_TRY(cudaMalloc(&c->tf.cand_count, sizeof(unsigned) * 4));
+      CREST_CUDA_TRY(cudaMalloc(&c->tf.cand_count, sizeof(unsigned) * 8));   // [4] = converter's unsafe flag
+      CREST_CUDA_TRY(cudaMemset(c->tf.cand_count, 0, sizeof(unsigned) * 8));
       CREST_CUDA_TRY(cudaMalloc(&c->d_npairs_scratch, sizeof(unsigned long long)));
     }
     // candidate list: duplicates + near-threshold pairs; sized for 64 per conformer (min 1M,
@@ -543,7 +544,7 @@ int crest_cuda_ctx_pack(crest_cuda_ctx* c, void* stream) {
   if (c->nall > 0) c->launches += 1;
   if (c->use_tf32) {
     if (launch_tf32_convert(c->d_X, c->d_xn, c->nall, c->L, c->ntile, c->tf.nslab, c->tf.kslab, c->tf.Xa,
-                            c->tf.Xb, c->tf.hn, st))
+                            c->tf.Xb, c->tf.hn, c->tf.cand_count + 4, st))
       return 1;
     c->launches += 1;
   }

@@ -164,7 +164,7 @@ constexpr int kTfSlabSlots = 48;
 int tf32_smem_bytes(int KU, int* nbstage_out);
 int launch_tf32_convert(const double* d_X, const double* d_xn, int nall, const PackLayout& L,
                         int ntile, int nslab_t, int kslab, float* d_Xa, float* d_Xb, float* d_hn,
-                        cudaStream_t stream);
+                        unsigned* d_unsafe, cudaStream_t stream);
 // items = device array of {I, g_begin, g_end, g_gate_end} int quadruples
 int launch_pair_tf32(const PairArgs& a, const Tf32Buffers& tb, const void* d_items, int item_begin,
                      int item_end, int all_cand, cudaStream_t stream, int* grid_out, int* smem_out);

@@ -151,42 +151,32 @@ struct TfArgs {
   int all_cand;           // debug: every pair goes to the exact kernel, bit 31 of j = screen said far
   int2* cand;             // candidate list
   unsigned cand_cap;
-  unsigned* cand_count;   // [0] = appended, [1] = overflow flag, [2] = screen violations (debug)
+  unsigned* cand_count;   // [0] = appended, [1] = overflow flag, [2] = screen violations (debug), [4] = converter: unsafe magnitudes
   unsigned long long* npairs;
 };
 
-// FP32 screen of the 4 pairs (i, j0..j0+3) of this lane + candidate emission
+// FP32 screen of the 4 pairs (i, j0..j0+3) of this lane + candidate emission.
 // DBG = false is the production instantiation: no timing switches, no self-check tagging.
-// farmask = 0xF when the row's half test point rd(hn_i + cE) is positive (then every lam of the row is,
-// because hn_j >= 0 and rounding down is monotone), else 0: the row goes to the exact pass.
+// rowfast (per lane): the row exists and its half test point rd(hn_i + cE) is positive, so every lam of
+// the row is (hn_j >= 0, rounding down is monotone).  The screen returns margin words whose sign bit is
+// clear iff the pair is proven far (screen_margin_f32x2; finiteness is guaranteed by the converter's
+// magnitude check, see tf32_convert_kernel).  Fast path (groups off the band edge and the diagonal,
+// live rows): all four pairs count, and one OR + sign test decides that nothing has to be emitted.
 template <bool DBG>
 __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v)[9][4], const float* hnp,
-                                             int j0, int i, bool iok, f2_t hic2, unsigned farmask,
+                                             int j0, int i, bool iok, f2_t hic2, bool rowfast,
                                              bool gate, bool slow, unsigned long long& my_pairs) {
   const float4 h0 = __ldg(reinterpret_cast<const float4*>(hnp));
   const float hj[4] = {h0.x, h0.y, h0.z, h0.w};
-  // which pairs count: j < i, inside the ensemble, inside the energy band (cregen.f90:1275)
-  unsigned ok = iok ? 0xFu : 0u;
-  if (slow) {
-    ok = 0;
-    const double eri = gate && iok ? a.er[i] : 0.0;
-#pragma unroll
-    for (int p = 0; p < 4; ++p) {
-      const int j = j0 + p;
-      bool o = iok && (j < i);
-      if (o && gate) o = __dmul_rn(__dsub_rn(eri, a.er[j]), kAutokcal) < a.ethr;
-      ok |= (o ? 1u : 0u) << p;
-    }
-  }
-  my_pairs += __popc(ok);
-  unsigned farbits = 0;
+  uint32_t sg[4];                        // sign bit set = not proven far
   if (DBG && (a.dbg == 4 || a.dbg >= 6)) {   // timing experiment: keep the loads live, skip the screen
     unsigned x = 0;
 #pragma unroll
     for (int z = 0; z < 9; ++z)
 #pragma unroll
       for (int p = 0; p < 4; ++p) x ^= v[z][p];
-    farbits = (x == 0x12345678u) ? 0xEu : 0xFu;
+    sg[0] = (x == 0x12345678u) ? 0x80000000u : 0u;
+    sg[1] = sg[2] = sg[3] = 0u;
   } else {
 #pragma unroll
     for (int p = 0; p < 4; p += 2) {     // two pairs per packed instruction (qcp.cuh)
@@ -194,12 +184,36 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
 #pragma unroll
       for (int z = 0; z < 9; ++z) rp[z] = f2_pack_u(v[z][p], v[z][p + 1]);
       const f2_t lam2 = f2_add_rd(hic2, f2_pack(hj[p], hj[p + 1]));   // rd(rd(hn_i + cE) + hn_j) <= the exact sum
-      farbits |= screen_far_f32x2(rp, lam2, a.enantio) << p;
+      const f2_t m = screen_margin_f32x2(rp, lam2, a.enantio);
+      sg[p] = (uint32_t)m;
+      sg[p + 1] = (uint32_t)(m >> 32);
     }
   }
-  farbits &= farmask;
-  unsigned cand = (DBG && a.all_cand) ? 0xFu : (~farbits & 0xFu);
-  cand &= ok;
+  unsigned cand, farbits = 0;
+  if (!DBG && !slow && rowfast) {
+    // pairs of this path are counted per item in epilogue_groups
+    if ((int)(sg[0] | sg[1] | sg[2] | sg[3]) >= 0) return;           // all four proven far
+    cand = (sg[0] >> 31) | ((sg[1] >> 31) << 1) | ((sg[2] >> 31) << 2) | ((sg[3] >> 31) << 3);
+  } else {
+    // which pairs count: j < i, inside the ensemble, inside the energy band (cregen.f90:1275)
+    unsigned ok = iok ? 0xFu : 0u;
+    if (slow) {
+      ok = 0;
+      const double eri = gate && iok ? a.er[i] : 0.0;
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        const int j = j0 + p;
+        bool o = iok && (j < i);
+        if (o && gate) o = __dmul_rn(__dsub_rn(eri, a.er[j]), kAutokcal) < a.ethr;
+        ok |= (o ? 1u : 0u) << p;
+      }
+    }
+    if (DBG || slow || !rowfast) my_pairs += __popc(ok);
+    farbits = ~((sg[0] >> 31) | ((sg[1] >> 31) << 1) | ((sg[2] >> 31) << 2) | ((sg[3] >> 31) << 3)) & 0xFu;
+    if (!rowfast) farbits = 0;
+    cand = (DBG && a.all_cand) ? 0xFu : (~farbits & 0xFu);
+    cand &= ok;
+  }
   if (cand) {
 #pragma unroll 1
     for (int p = 0; p < 4; ++p) {
@@ -226,10 +240,13 @@ __device__ __forceinline__ void epilogue_groups(const TfArgs& a, const TfItem& i
                                                 uint32_t& t, uint32_t& ph, unsigned long long& my_pairs) {
   const float hic = __fadd_rd(a.hn[i], a.cE);
   const f2_t hic2 = f2_pack(hic, hic);
-  const unsigned farmask = hic > 0.0f ? 0xFu : 0u;
+  const bool rowfast = iok && hic > 0.0f;
   const float* hnp = a.hn + item.g_begin * 16 + sq * 4;
   const int g_diag = item.I * 8;                          // first group with g*16 + 15 >= I*128
-  for (int g = item.g_begin; g < item.g_end; ++g, hnp += 16) {
+  if (!DBG && rowfast)                                    // the fast path's pairs: 4 per lane and group
+    my_pairs += 4ull * (unsigned)max(0, min(item.g_end, g_diag) - max(item.g_begin, item.g_gate_end));
+  int j0 = item.g_begin * 16 + sq * 4;
+  for (int g = item.g_begin; g < item.g_end; ++g, hnp += 16, j0 += 16) {
     const bool gate = g < item.g_gate_end;
     const bool slow = gate || (g >= g_diag);
     uint32_t v[9][4];
@@ -239,9 +256,10 @@ __device__ __forceinline__ void epilogue_groups(const TfArgs& a, const TfItem& i
     tc_wait_ld();
     tc_fence_before();
     __syncwarp();
-    if (lane == 0) mbar_arrive_a(dempty0 + 8u * t);      // this warp's 4 pairs are in registers
-    screen_batch<DBG>(a, v, hnp, g * 16 + sq * 4, i, iok, hic2, farmask, gate, slow, my_pairs);
-    if (++t == (uint32_t)NST) { t = 0; ph ^= 1u; }
+    if (elect_one()) mbar_arrive_a(dempty0 + 8u * t);    // this warp's 4 pairs are in registers
+    screen_batch<DBG>(a, v, hnp, j0, i, iok, hic2, rowfast, gate, slow, my_pairs);
+    if (NST == 2) { ph ^= t; t ^= 1u; }
+    else if (++t == (uint32_t)NST) { t = 0; ph ^= 1u; }
   }
 }
 
@@ -284,6 +302,7 @@ pair_tf32_kernel(const TfArgs a) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && a.cand_count[4]) a.cand_count[1] = 1u;   // converter's magnitude check
 
   if (warp == kTfEpiWarps) {
     // ===================== producer: bulk copies of the i-tile and the j-group ring ==========
@@ -456,6 +475,7 @@ pair_tf32_slab_kernel(const TfArgs a) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && a.cand_count[4]) a.cand_count[1] = 1u;   // converter's magnitude check
 
   if (warp == kTfEpiWarps) {
     // ===================== producer =====================
@@ -571,13 +591,18 @@ struct XView {
 __global__ void __launch_bounds__(256)
 tf32_convert_kernel(const XView xv, const double* __restrict__ xn, int nall, int ntile, int nslab_t,
                     int kslab, float* __restrict__ Xa, float* __restrict__ Xb,
-                    float* __restrict__ hn, double kappa) {
+                    float* __restrict__ hn, double kappa, unsigned* __restrict__ unsafe) {
   const int nchunk = kslab >> 2;
   const long long total = (long long)ntile * 128 * 3 * nchunk * nslab_t;
   const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid < (long long)ntile * 128) {
     const int i = (int)tid;
-    hn[i] = i < nall ? __double2float_rd(0.5 * xn[i] * (1.0 - kappa)) : 0.0f;
+    const float h = i < nall ? __double2float_rd(0.5 * xn[i] * (1.0 - kappa)) : 0.0f;
+    hn[i] = h;
+    // the screen's sign tests assume finite FP32 arithmetic: lam = hn_i + hn_j + cE < 1e9 keeps every
+    // intermediate (<= lam^4) below 1e36.  A structure beyond that (or a NaN) sends the whole launch
+    // to the FP64 kernel through the overflow flag.
+    if (!(h < 5.0e8f)) *unsafe = 1u;
   }
   if (tid >= total) return;
   const int r = (int)(tid % 128);
@@ -679,12 +704,13 @@ static XView make_xview(const double* d_X, const PackLayout& L) {
 
 int launch_tf32_convert(const double* d_X, const double* d_xn, int nall, const PackLayout& L,
                         int ntile, int nslab_t, int kslab, float* d_Xa, float* d_Xb, float* d_hn,
-                        cudaStream_t stream) {
+                        unsigned* d_unsafe, cudaStream_t stream) {
+  CREST_CUDA_TRY(cudaMemsetAsync(d_unsafe, 0, sizeof(unsigned), stream));
   const long long total = (long long)ntile * 128 * 3 * (kslab / 4) * nslab_t;
   if (total <= 0) return 0;
   const int blocks = (int)((total + 255) / 256);
   tf32_convert_kernel<<<blocks, 256, 0, stream>>>(make_xview(d_X, L), d_xn, nall, ntile, nslab_t, kslab,
-                                                  d_Xa, d_Xb, d_hn, kTfKappa);
+                                                  d_Xa, d_Xb, d_hn, kTfKappa, d_unsafe);
   CREST_CUDA_TRY(cudaGetLastError());
   return 0;
 }

@@ -281,8 +281,11 @@ __device__ __forceinline__ f2_t f2_add_rd(f2_t a, f2_t b) {   // round toward -i
   return r;
 }
 
-// r[3a+b] packed covariance of two pairs, lam packed test points.  Returns bit 0 / bit 1 = pair
-// 0 / 1 is PROVEN far, i.e. lambda_max < lam.
+// r[3a+b] packed covariance of two pairs, lam packed test points, which the CALLER guarantees to be
+// positive.  Returns a packed word per pair whose SIGN BIT IS CLEAR iff the pair is PROVEN far, i.e.
+// lambda_max < lam (the OR of the two margins below; +0 counts as far, the floors are 30x the
+// evaluation error).  The caller also guarantees finite arithmetic (lam < 1e9, |R_ab| <= ~lam): no
+// Inf/NaN can arise, so the sign test is a valid "both margins >= 0".
 //
 // Two signs instead of the four of Budan-Fourier: the key matrix is symmetric and traceless, so its
 // eigenvalues l1 >= l2 >= l3 >= l4 satisfy sum = 0 and sum of squares = 4*I1 (the lambda^2
@@ -293,9 +296,9 @@ __device__ __forceinline__ f2_t f2_add_rd(f2_t a, f2_t b) {   // round toward -i
 // with -8*|det|*lam, the smaller of the two.  Evaluation: u = lam^2 - I1,
 //     P = u^2 + 2*(||G||^2 - I1^2) - 8*det*lam = u^2 + 2*x,  x = ||G||^2 - I1^2 - 4*det*lam,
 // every term bounded by lam^4 once u > 0; FP32 evaluation error < 100 * 2^-24 of lam^2 (u) and
-// lam^4 (P); both signs are required with a floor of 2e-4 of those scales.  NaN / Inf compare
-// false => undecided.  45 packed FMA-pipe instructions per two pairs (52 for the four-sign form).
-__device__ __forceinline__ unsigned screen_far_f32x2(const f2_t* r, f2_t lam, int enantio) {
+// lam^4 (P); both signs are required with a floor of 2e-4 of those scales.
+// 46 packed FMA-pipe instructions per two pairs (52 for the four-sign form).
+__device__ __forceinline__ f2_t screen_margin_f32x2(const f2_t* r, f2_t lam, int enantio) {
   // Gram matrix G = R^T R (columns of R): g_bc = sum_a r[3a+b] r[3a+c]
   const f2_t g00 = f2_fma(r[6], r[6], f2_fma(r[3], r[3], f2_mul(r[0], r[0])));
   const f2_t g11 = f2_fma(r[7], r[7], f2_fma(r[4], r[4], f2_mul(r[1], r[1])));
@@ -319,14 +322,10 @@ __device__ __forceinline__ unsigned screen_far_f32x2(const f2_t* r, f2_t lam, in
   const f2_t lm4 = f2_mul(lam, f2_pack(-4.0f, -4.0f));
   const f2_t x = f2_fma(enantio ? f2_abs(det) : det, lm4, x0);
   const f2_t P = f2_fma(x, f2_pack(2.0f, 2.0f), f2_mul(u, u));
-  const f2_t fl = f2_mul(l2, f2_pack(2e-4f, 2e-4f));
-  const f2_t flM = f2_mul(fl, l2);
-  float Pa, Pb, ua, ub, fa, fb, fMa, fMb, la, lb;
-  f2_unpack(P, Pa, Pb); f2_unpack(u, ua, ub);
-  f2_unpack(fl, fa, fb); f2_unpack(flM, fMa, fMb); f2_unpack(lam, la, lb);
-  const bool far0 = (la > 0.0f) & (ua > fa) & (Pa > fMa);
-  const bool far1 = (lb > 0.0f) & (ub > fb) & (Pb > fMb);
-  return (far0 ? 1u : 0u) | (far1 ? 2u : 0u);
+  // margins over the floors: d1 = u - 2e-4*lam^2, d2 = P - 2e-4*lam^4
+  const f2_t d1 = f2_fma(l2, f2_pack(-2e-4f, -2e-4f), u);
+  const f2_t d2 = f2_fma(f2_mul(l2, f2_pack(-2e-4f, -2e-4f)), l2, P);
+  return d1 | d2;
 }
 
 // reference src/rotcompare.f90:109-122 (same operation order)

@@ -435,6 +435,28 @@ def test_tf32_overflow_falls_back_to_fp64(cb):
     assert got["npairs"] == ref["npairs"]
 
 
+@pytest.mark.parametrize("cfg,nall", [("C1", 700), ("C4", 300)])
+def test_tf32_unsafe_magnitudes_fall_back(cb, cfg, nall):
+    """The screen's sign tests assume finite FP32 arithmetic (test point < 1e9).  One structure blown
+    up beyond that makes the converter raise the overflow flag: the launch is redone by the FP64 kernel
+    and the result equals the FP64-only run."""
+    ens = synth.make_config(cfg, nall=nall, seed=9)
+    ens = dict(ens)
+    xyz = ens["xyz"].copy()
+    xyz[nall // 2] *= 3.0e4        # |x|^2 ~ 1e9 * (size in A)^2: half norm beyond 5e8
+    ens["xyz"] = xyz
+    env = cb.Env(ethr=1e9)
+    ref, rref, _ = _stage_a(cb, ens, env, "notf32")
+    got, rgot, info = _stage_a(cb, ens, env)
+    assert info["variant"] == 2 and info["overflow"] == 1
+    assert np.array_equal(got["dup"], ref["dup"]) and np.array_equal(rgot, rref)
+    assert got["npairs"] == ref["npairs"]
+    # and the flag is cleared by the next pack of a tame ensemble on a fresh context
+    tame = synth.make_config(cfg, nall=nall, seed=9)
+    _, _, info2 = _stage_a(cb, tame, env)
+    assert info2["variant"] == 2 and info2["overflow"] == 0
+
+
 @pytest.mark.parametrize("nall", [2, 15, 16, 17, 127, 128, 129, 255, 257, 1025])
 def test_tf32_ragged_tiles(cb, oracle, nall):
     """Ensemble sizes around the i-tile (128) and j-group (16) edges, against the oracle."""
