@@ -16,14 +16,14 @@
 //     ||dR||_F <= rho * |x||y| <= rho * s/2
 //     |lambda_max(R) - lambda_max(R~)| <= ||dR||_* <= sqrt(3) ||dR||_F <= 1.78e-3 * s/2
 // (S is linear in R and every eigenvalue of S(dR) is a signed sum of the singular values of dR), so
-// the Budan-Fourier sign test of qcp.cuh evaluated on R~ at lam = (1 - 1.8e-3) s/2 - E2/2 proves
-// lambda_max(R) < lam*.  B200's FP64 tensor path tops out at ~36 TFLOP/s; the TF32 path is >20x
+// the two-sign test of qcp.cuh (lam^2 > I1 and P(lam) > 0; screen_margin_f32x2) evaluated on R~ at
+// lam = (1 - 1.8e-3) s/2 - E2/2 proves lambda_max(R) < lam*.  B200's FP64 tensor path tops out at ~36 TFLOP/s; the TF32 path is >20x
 // wider, which moves the bound of this stage from the DMMA pipe to the FP32 screen arithmetic.
 //
 // Shape: a CTA owns one i-tile (128 conformers, all K, 3 components = 3 A operands [128 x K]) and
-// streams j-groups of 16 conformers past it; a j-group is ONE B operand [48 x K] (row n = 16*b + jj),
-// so three MMAs per K step (M = 128, N = 48, K = 8) leave, in TMEM lane i, the full 3x3 covariance of
-// the 16 pairs (i, j0..j0+15): D_a[i][16 b + jj].  Operands are written by tf32_convert_kernel in the
+// streams j-groups of 16 conformers past it; a j-group is ONE B operand [48 x K] (row n = 12*s + 4*b + p
+// for conformer j0 + 4*s + p), so three MMAs per K step (M = 128, N = 48, K = 8) leave, in TMEM lane i,
+// the full 3x3 covariance of the 16 pairs (i, j0..j0+15): D_a[i][12 s + 4 b + p].  Operands are written by tf32_convert_kernel in the
 // canonical no-swizzle K-major core-matrix layout, so one 1-D bulk copy (TMA engine) brings a
 // tile/group in exactly the byte order the UMMA descriptor describes.  For K <= 64 the i-tile is moved
 // once per work item from shared memory into TMEM (tcgen05.st) and the MMAs take A from TMEM: an MMA
@@ -32,9 +32,9 @@
 // Warp roles: warps 0-15 epilogue (TMEM -> registers -> screen), warp 16 producer (bulk copies),
 // warp 17 MMA issuer (one elected lane).  Pipelines: B ring (producer <-> MMA, mbarrier + tcgen05.commit),
 // TMEM accumulator stages (MMA <-> epilogue), i-tile (producer -> epilogue warps 0-3 -> MMA).
-// Measured bound: per j-group an SM moves 72 KB TMEM -> registers (~128 B/clk) and
-// issues ~880 clk of packed FP32 arithmetic per sub-partition; the two do not overlap on B200, so the
-// kernel runs at ~1500 clk per 2048 pairs.
+// Measured bound: ~770 clk of packed FP32 arithmetic per j-group and sub-partition;
+// the kernel runs at ~1120 clk per 2048 pairs (FMA pipe 71 % busy), limited by the instruction count of
+// the epilogue loop at 4 warps per sub-partition; TMEM loads hide completely (tools/microbench).
 #include "common.cuh"
 #include "qcp.cuh"
 #include "pipe.cuh"
