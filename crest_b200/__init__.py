@@ -5,3 +5,4 @@ mirror of the reference interface in crest_b200.cregen.  No CPU fallback exists.
 from .cregen import (Env, CregenContext, cregen_CRE, cregen_dup, cregen_group, rmsd_pairs,  # noqa: F401
                      rotconst, rmat_allpairs, cregen_esort, rmsdalign, CrestCudaError)
 from ._lib import Thresholds  # noqa: F401
+from .compare import compare_blocks, compare_correlate, intraconf  # noqa: F401

@@ -40,6 +40,11 @@ SYMBOLS = {
     "crest_cuda_cregen_esort": (C.c_int, [C.c_int, C.c_int, c_dp, c_dp, C.c_double, c_ip, c_ip]),
     "crest_cuda_rmsdalign": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp]),
     "crest_cuda_rmat_allpairs": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_ip, C.c_int, c_fp]),
+    "crest_cuda_compare_blocks": (C.c_int, [C.c_int, C.c_int, c_dp, C.c_int, c_ip, c_ip, C.c_int, c_dp,
+                                            C.c_int, c_ip, c_ip, c_dp]),
+    "crest_cuda_compare_correlate": (C.c_int, [C.c_int, C.c_int, c_dp, c_dp, c_dp, C.c_double, c_ip, c_ip]),
+    "crest_cuda_intraconf": (C.c_int, [C.c_int, C.c_int, c_dp, c_ip, C.c_int, c_ip, c_ip, C.c_char_p,
+                                       c_dp, c_dp]),
     "crest_cuda_ctx_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
     "crest_cuda_ctx_destroy": (None, [C.c_void_p]),
     "crest_cuda_ctx_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_int, c_ip, c_dp, c_dp, c_ip, C.c_int]),

@@ -97,6 +97,36 @@ int crest_cuda_cregen_esort(int nat, int nall, double* xyz, double* energies, do
  * optimal heavy-atom (at > 2) rotation of rmsd() (ls_rmsd.f90:72-221, option 1), in place. */
 int crest_cuda_rmsdalign(int nat, int nall, const int* at, double* xyz);
 
+/* ---- callers of rmsd() beside cregen_CRE ----
+ * compare_ensembles main loop (src/ensemblecomp.f90:213-248): rmat(i,j) = minimum all-atom RMSD
+ * (ls_rmsd.f90:72-174, no mirror) between any rotamer of conformer i of ensemble 1 and any rotamer
+ * of conformer j of ensemble 2 (the reference's seed `rmat2 = 100` never survives: every rotamer
+ * pair overwrites its slot before minval()).
+ *   xyz1(3,nat,nall1), xyz2(3,nat,nall2)   the two ensembles as rdensemble delivers them
+ *   b1/e1(nconf1), b2/e2(nconf2)           1-based inclusive rotamer ranges from the .cretrack
+ *                                          files (ensemblecomp.f90:123-126,161-164)
+ *   rmat(nconf1,nconf2)                    out, column-major double */
+int crest_cuda_compare_blocks(int nat, int nall1, const double* xyz1, int nconf1, const int* b1,
+                              const int* e1, int nall2, const double* xyz2, int nconf2,
+                              const int* b2, const int* e2, double* rmat);
+
+/* "Correlation between Conformers" walk (src/ensemblecomp.f90:258-300) as data instead of print
+ * lines: line n pairs left[n] with right[n] (1-based conformer numbers, 0 = blank column).
+ * en1(nconf1), en2(nconf2) energies of the lowest rotamers; left/right hold nconf1+nconf2 entries.
+ * Host code.  Returns the number of lines, -1 on a bad argument. */
+int crest_cuda_compare_correlate(int nconf1, int nconf2, const double* en1, const double* en2,
+                                 const double* rmat, double rthr, int* left, int* right);
+
+/* intraconfRMSD (src/entropy/entropic.f90:938-1097): for every conformer with nrot > 1, RMSDs
+ * between its rotamers low(c)..low(c)+nrot(c)-1 (1-based) on the atoms with inc(k) == 1;
+ * fac(c) = uniqueCore(rmat, nrot, 0.125) (1074-1095), enantiofac(c) = 2 when some pair has
+ * rmsd > 0.125 and mirror rmsd < 0.09375 (1024-1031), then spread over equal symmetry symbols
+ * symsym (3 characters per conformer, blank padded; symmap 1096-1116).  enantiofac is in/out
+ * (the caller seeds it with 1, entropic.f90:137).  sum(inc) < 2 sets fac = 1 and returns. */
+int crest_cuda_intraconf(int nat, int nall, const double* xyz, const int* inc, int nconf,
+                         const int* low, const int* nrot, const char* symsym, double* fac,
+                         double* enantiofac);
+
 /* All-pairs float32 RMSD band exactly as the reference's rmat (cregen.f90:1260-1349): row i holds
  * j = 0..i-1 at offset i*(i-1)/2 (ethr = infinity layout).  For tests on small ensembles. */
 int crest_cuda_rmat_allpairs(int nat, int nall, const int* at, const double* xyz,

@@ -3,6 +3,9 @@
 // through ctypes.  Nothing in crest_b200/ links or loads this library.
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
+#include <algorithm>
+#include <vector>
 #include <omp.h>
 #include "cregen_ref.hpp"
 
@@ -161,6 +164,147 @@ long long oracle_pair_rows(int n, int nall, const double* xyz, const double* er,
     off += (size_t)i;
   }
   return npairs;
+}
+
+// ---- ensemblecomp.f90:213-248 (rmat = block-wise minimum RMSD, seeded with 100) ----
+// xyz1(3,nat,nall1), xyz2(3,nat,nall2); b/e 1-based inclusive; rmat(nconf1,nconf2) column-major.
+void oracle_compare_blocks(int nat, const double* xyz1, int nconf1, const int* b1, const int* e1,
+                           const double* xyz2, int nconf2, const int* b2, const int* e2,
+                           double* rmat) {
+  const size_t stride = (size_t)3 * nat;
+  for (int i = 0; i < nconf1; ++i) {
+    for (int j = 0; j < nconf2; ++j) {
+      const int nrot1 = e1[i] - b1[i] + 1, nrot2 = e2[j] - b2[j] + 1;
+      std::vector<double> rmat2((size_t)nrot1 * nrot2, 100.0);
+      for (int k = 0; k < nrot1; ++k) {
+        const double* c1 = xyz1 + stride * (b1[i] - 1 + k);
+#pragma omp parallel
+        {
+          std::vector<double> wx(stride), wy(stride);
+#pragma omp for
+          for (int l = 0; l < nrot2; ++l) {
+            const double* c2 = xyz2 + stride * (b2[j] - 1 + l);
+            rmat2[(size_t)k * nrot2 + l] = rmsd(nat, c1, c2, wx.data(), wy.data());
+          }
+        }
+      }
+      double m = rmat2[0];
+      for (double v : rmat2) m = std::min(m, v);
+      rmat[i + (size_t)nconf1 * j] = m;
+    }
+  }
+}
+
+// ensemblecomp.f90:258-300 as data: returns the number of lines; left/right 1-based, 0 = blank
+int oracle_compare_correlate(int nconf1, int nconf2, const double* en1, const double* en2,
+                             const double* rmat, double rthr, int* left, int* right) {
+  int kk = nconf1, ll = nconf2, nl = 0;
+  if (kk == 0 && ll == 0) return 0;
+  for (;;) {
+    bool matching = false;
+    if (kk > 0 && ll > 0) {
+      const double rval = rmat[(kk - 1) + (size_t)nconf1 * (ll - 1)];
+      if (rval <= rthr) {
+        left[nl] = kk; right[nl] = ll; ++nl;
+        kk = kk - 1; ll = ll - 1;
+        matching = true;
+      }
+    }
+    if (!matching) {
+      if (kk > 0 && ll > 0) {
+        const double min_1 = en1[kk - 1], min_2 = en2[ll - 1];
+        if (min_1 >= min_2) { left[nl] = kk; right[nl] = 0; ++nl; kk = kk - 1; }
+        else { left[nl] = 0; right[nl] = ll; ++nl; ll = ll - 1; }
+      }
+      if (kk > 0 && ll == 0) { left[nl] = kk; right[nl] = 0; ++nl; kk = kk - 1; }
+      if (kk == 0 && ll > 0) { left[nl] = 0; right[nl] = ll; ++nl; ll = ll - 1; }
+    }
+    if (kk == 0 && ll == 0) break;
+  }
+  return nl;
+}
+
+// ---- entropy/entropic.f90:938-1097 intraconfRMSD, statement by statement ----
+static int unique_core(const std::vector<double>& mat, int n, double thr) {   // 1074-1095
+  std::vector<int> mp((size_t)n, 0);
+  int gr = 0;
+  for (int i = 0; i < n; ++i) {
+    if (mp[i] == 0) { gr = gr + 1; mp[i] = gr; }
+    for (int j = 0; j < n; ++j)
+      if (mat[(size_t)i + (size_t)n * j] < thr) mp[j] = gr;
+  }
+  return gr;
+}
+
+static int symmap_ref(char symlist[100][3], const char* symflag) {            // 1096-1116
+  auto len_trim = [](const char* s) { int n = 3; while (n > 0 && s[n - 1] == ' ') --n; return n; };
+  int res = 1;
+  for (int i = 1; i <= 100; ++i) {
+    if (std::memcmp(symlist[i - 1], symflag, 3) == 0) { res = i; break; }   // blank-padded compare
+    if (len_trim(symlist[i - 1]) < 1) { std::memcpy(symlist[i - 1], symflag, 3); res = i; break; }
+  }
+  return res;
+}
+
+// xyz(3,nat,nall); inc(nat) 0/1; low/nrot per conformer (1-based low); symsym 3 chars each;
+// fac(nconf) out, enantiofac(nconf) in/out.  rmat_out (optional) receives the rmat of conformer
+// `rmat_conf` (0-based) for RMSD-level checks, nrot x nrot column-major.
+void oracle_intraconf(int nat, int nall, const double* xyz, const int* inc, int nconf,
+                      const int* low, const int* nrot, const char* symsym, double* fac,
+                      double* enantiofac, int rmat_conf, double* rmat_out) {
+  int rednat = 0;
+  for (int k = 0; k < nat; ++k) rednat += inc[k];
+  if (rednat < 2) { for (int c = 0; c < nconf; ++c) fac[c] = 1.0; return; }
+  const double rthr = 0.125;
+  char symref[100][3];
+  std::memset(symref, ' ', sizeof(symref));
+  double symenantio[100];
+  for (double& v : symenantio) v = 1.0;
+  const size_t stride = (size_t)3 * nat;
+  auto cpincluded = [&](const double* c, bool flipx, double* cr) {
+    int k = 0;
+    for (int i = 0; i < nat; ++i)
+      if (inc[i] == 1) {
+        cr[3 * k] = flipx ? -c[3 * i] : c[3 * i];
+        cr[3 * k + 1] = c[3 * i + 1]; cr[3 * k + 2] = c[3 * i + 2];
+        ++k;
+      }
+  };
+  std::vector<double> c1r((size_t)3 * rednat), c2r((size_t)3 * rednat), wx((size_t)3 * rednat),
+      wy((size_t)3 * rednat);
+  for (int co = 0; co < nconf; ++co) {
+    const int nr = nrot[co];
+    int groups = 1;
+    if (nr > 1) {
+      std::vector<double> rmat((size_t)nr * nr, 0.0);
+      bool enantio = false;
+      const double* base = xyz + stride * (low[co] - 1);
+      for (int i = 0; i < nr; ++i) {
+        cpincluded(base + stride * i, false, c1r.data());
+        for (int j = 0; j < i; ++j) {
+          cpincluded(base + stride * j, false, c2r.data());
+          const double r = rmsd(rednat, c1r.data(), c2r.data(), wx.data(), wy.data());
+          rmat[(size_t)i + (size_t)nr * j] = r;
+          rmat[(size_t)j + (size_t)nr * i] = r;
+          if (r > rthr) {
+            cpincluded(base + stride * j, true, c2r.data());
+            const double re = rmsd(rednat, c1r.data(), c2r.data(), wx.data(), wy.data());
+            if (re < rthr * 0.75) enantio = true;
+          }
+        }
+      }
+      groups = unique_core(rmat, nr, rthr);
+      if (enantio) enantiofac[co] = 2.0;
+      if (rmat_out && co == rmat_conf) std::memcpy(rmat_out, rmat.data(), sizeof(double) * rmat.size());
+    }
+    const int k = symmap_ref(symref, symsym + 3 * (size_t)co);
+    if (enantiofac[co] > symenantio[k - 1]) symenantio[k - 1] = enantiofac[co];
+    fac[co] = (double)groups;
+  }
+  for (int co = 0; co < nconf; ++co) {
+    const int k = symmap_ref(symref, symsym + 3 * (size_t)co);
+    enantiofac[co] = symenantio[k - 1];
+  }
 }
 
 int oracle_num_threads(void) { return omp_get_max_threads(); }

@@ -51,6 +51,14 @@ def lib():
         L.oracle_pair_rows.argtypes = [C.c_int, C.c_int, c_dp, c_dp, C.c_double, C.c_int, C.c_int,
                                        C.c_int, c_fp]
         L.oracle_num_threads.restype = C.c_int
+        L.oracle_compare_blocks.restype = None
+        L.oracle_compare_blocks.argtypes = [C.c_int, c_dp, C.c_int, c_ip, c_ip, c_dp, C.c_int, c_ip,
+                                            c_ip, c_dp]
+        L.oracle_compare_correlate.restype = C.c_int
+        L.oracle_compare_correlate.argtypes = [C.c_int, C.c_int, c_dp, c_dp, c_dp, C.c_double, c_ip, c_ip]
+        L.oracle_intraconf.restype = None
+        L.oracle_intraconf.argtypes = [C.c_int, C.c_int, c_dp, c_ip, C.c_int, c_ip, c_ip, C.c_char_p,
+                                       c_dp, c_dp, C.c_int, c_dp]
         _LIB = L
     return _LIB
 
@@ -171,3 +179,45 @@ def pair_rows(xyz_packed, er, i0, i1, *, ethr=1e9, enantio=True, want=True):
 
 def num_threads():
     return lib().oracle_num_threads()
+
+
+def compare_blocks(xyz1, b1, e1, xyz2, b2, e2):
+    """ensemblecomp.f90:213-248; returns rmat (nconf1, nconf2)."""
+    xyz1 = np.ascontiguousarray(xyz1, np.float64)
+    xyz2 = np.ascontiguousarray(xyz2, np.float64)
+    b1, e1, b2, e2 = (np.ascontiguousarray(a, np.int32) for a in (b1, e1, b2, e2))
+    out = np.zeros((len(b2), len(b1)))
+    lib().oracle_compare_blocks(xyz1.shape[1], _dp(xyz1), len(b1), _ip(b1), _ip(e1), _dp(xyz2), len(b2),
+                                _ip(b2), _ip(e2), _dp(out))
+    return out.T
+
+
+def compare_correlate(en1, en2, rmat, rthr):
+    en1 = np.ascontiguousarray(en1, np.float64)
+    en2 = np.ascontiguousarray(en2, np.float64)
+    rm = np.ascontiguousarray(np.asarray(rmat, np.float64).T)
+    left = np.zeros(len(en1) + len(en2) + 1, np.int32)
+    right = np.zeros_like(left)
+    nl = lib().oracle_compare_correlate(len(en1), len(en2), _dp(en1), _dp(en2), _dp(rm), float(rthr),
+                                        _ip(left), _ip(right))
+    return left[:nl].copy(), right[:nl].copy()
+
+
+def intraconf(xyz, inc, low, nrot, symsym, enantiofac=None, rmat_conf=-1):
+    """entropic.f90:938-1097; returns (fac, enantiofac[, rmat of conformer rmat_conf])."""
+    xyz = np.ascontiguousarray(xyz, np.float64)
+    inc = np.ascontiguousarray(inc, np.int32)
+    low = np.ascontiguousarray(low, np.int32)
+    nrot = np.ascontiguousarray(nrot, np.int32)
+    nconf = len(low)
+    sym = "".join(f"{s:<3.3}" for s in symsym).encode()
+    fac = np.ones(max(nconf, 1))
+    ef = np.ones(max(nconf, 1)) if enantiofac is None else np.array(enantiofac, np.float64, copy=True)
+    rm = None
+    if rmat_conf >= 0:
+        rm = np.zeros((nrot[rmat_conf], nrot[rmat_conf]))
+    lib().oracle_intraconf(xyz.shape[1], xyz.shape[0], _dp(xyz), _ip(inc), nconf, _ip(low), _ip(nrot),
+                           sym, _dp(fac), _dp(ef), rmat_conf, _dp(rm) if rm is not None else None)
+    if rm is not None:
+        return fac[:nconf], ef[:nconf], rm
+    return fac[:nconf], ef[:nconf]
