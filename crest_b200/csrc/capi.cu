@@ -11,6 +11,7 @@
 #include <limits>
 #include <utility>
 #include <vector>
+#include <chrono>
 
 namespace crest {
 
@@ -58,6 +59,8 @@ static void parse_tune(const char* e, Tune& t) {
   if (std::strstr(e, "tile")) t.force_tile = 1;
   if (std::strstr(e, "nohalf")) t.no_half = 1;
   if (std::strstr(e, "notf32")) t.no_tf32 = 1;
+  if (std::strstr(e, "seqgroup")) t.seq_group = 1;
+  if (const char* q = std::strstr(e, "groupcap=")) if (std::sscanf(q + 9, "%d", &v) == 1) t.group_cap = v;
   if (const char* q = std::strstr(e, "cap=")) if (std::sscanf(q + 4, "%d", &v) == 1) t.cand_cap = v;
   if (const char* q = std::strstr(e, "chunk=")) if (std::sscanf(q + 6, "%d", &v) == 1) t.chunk = v;
   if (const char* q = std::strstr(e, "skew=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.skew = v;
@@ -801,13 +804,28 @@ int crest_cuda_cregen_cre(int nat, int nall, const int* at, double* xyz, double*
   if (check_thr(thr)) return 1;
   crest_cuda_ctx* c;
   if (global_ctx(&c)) return 1;
+  // CREST_CUDA_TIMING=1: phase wall times of this call on stderr (developer aid; adds syncs)
+  static const bool timing = getenv("CREST_CUDA_TIMING") && atoi(getenv("CREST_CUDA_TIMING")) > 0;
+  auto t_last = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (!timing) return;
+    cudaDeviceSynchronize();
+    const auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "[cregen_cre] %-28s %8.3f ms\n", what,
+            std::chrono::duration<double, std::milli>(now - t_last).count());
+    t_last = now;
+  };
   // stage A on the device; only the link array (4 B per structure) comes back for the partition
   if (crest_cuda_ctx_upload(c, nat, nall, at, xyz, er, rmsd_mask, rot_from_mask)) return 1;
+  lap("upload (H2D xyz)");
   if (crest_cuda_ctx_pack(c, nullptr)) return 1;
+  lap("pack_axis + tf32_convert");
   if (crest_cuda_ctx_pairs(c, enantio, thr, 0, 1, 0, nullptr)) return 1;
+  lap("pair stage");
   if (crest_cuda_ctx_sweep(c, nullptr)) return 1;
   std::vector<int> dup((size_t)(nall > 0 ? nall : 1));
   if (crest_cuda_ctx_download(c, nullptr, nullptr, dup.data(), npairs, nullptr)) return 1;
+  lap("backtrack + D2H dup");
   for (int i = 0; i <= nall; ++i) group[i] = 0;
   if (nall == 0) { *nallout = 0; return 0; }
   // kept-first partition, duplicates appended in reverse encounter order (cregen.f90:1397-1419)
@@ -838,12 +856,17 @@ int crest_cuda_cregen_cre(int nat, int nall, const int* at, double* xyz, double*
     if (cudaMalloc(&d_enuc, sizeof(double) * n) != cudaSuccess) break;
     if (cudaMemcpy(d_src, src.data(), sizeof(int) * n, cudaMemcpyHostToDevice) != cudaSuccess) break;
     // d_xyz (the input copy) is free now: it receives the permuted principal-axis geometries
+    lap("partition (host) + alloc");
     if (launch_permute(nat, nall, d_src, c->d_xyz_axis, c->d_er, c->d_rot, c->d_xyz, d_er2, d_rot2, 0)) { rc = 2; break; }
+    lap("permute");
     if (cudaMemset(d_group, 0, sizeof(int) * (n + 1)) != cudaSuccess) break;
     if (launch_enuc(nat, nout, c->d_at, c->d_xyz, d_enuc, 0)) { rc = 2; break; }
+    lap("enuc");
     if (launch_group(nout, d_er2, d_rot2, d_enuc, thr->ethr, thr->bthr, thr->bthrmax, thr->bthrshift,
                      d_group, 0)) { rc = 2; break; }
+    lap("group");
     if (cudaMemcpy(xyz, c->d_xyz, sizeof(double) * 3 * nat * n, cudaMemcpyDeviceToHost) != cudaSuccess) break;
+    lap("D2H xyz");
     if (cudaMemcpy(er, d_er2, sizeof(double) * n, cudaMemcpyDeviceToHost) != cudaSuccess) break;
     if (cudaMemcpy(rot, d_rot2, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost) != cudaSuccess) break;
     if (cudaMemcpy(group, d_group, sizeof(int) * ((size_t)nout + 1), cudaMemcpyDeviceToHost) != cudaSuccess) break;

@@ -3,6 +3,7 @@
 //   enuc           reference src/cregen.f90:1422-1435   (K5)
 //   rotamer groups reference src/cregen.f90:1437-1469   (K6 + group ids)
 //   rmsd_pairs     reference src/ls_rmsd.f90:72-174      (diagnostic, explicit pair list)
+#include <vector>
 #include "common.cuh"
 #include "qcp.cuh"
 
@@ -122,18 +123,120 @@ group_kernel(int n, const double* __restrict__ er, const double* __restrict__ ro
   if (tid == 0) group[0] = s_ng;
 }
 
+// ---- K6, two phases.  The sequential part of the greedy sweep is only "is j still a head";
+// whether (i, j) satisfy the three conditions of cregen.f90:1444-1448 does not depend on the sweep.
+// Phase 1 (whole GPU, one warp per i): the first kGroupCap matching j < i in ascending order.
+// Phase 2 (host, O(n * kGroupCap)): i joins the first listed j that is a head, else opens a group.
+// A row whose listed matches are all non-heads AND whose list was cut needs the full row: then the
+// single-CTA kernel above redoes the sweep (never seen on the test ensembles: kept structures that
+// agree in energy window, rot. constants and enuc are rotamers of one another, a handful per group).
+constexpr int kGroupCap = 8;   // default list length; CREST_CUDA_TUNE `groupcap=<n>` (tests: 1 forces the fallback)
+
+__global__ void group_aniso_kernel(int n, const double* __restrict__ rot, double* __restrict__ aniso) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) aniso[k] = rotaniso_dev(rot[3 * k], rot[3 * k + 1], rot[3 * k + 2]);
+}
+
+__global__ void __launch_bounds__(256)
+group_match_kernel(int n, const double* __restrict__ er, const double* __restrict__ rot,
+                   const double* __restrict__ enuc, const double* __restrict__ aniso, double ethr,
+                   double bthr, double bthrmax, double bthrshift, int cap, int* __restrict__ cnt,
+                   int* __restrict__ list) {
+  const int lane = threadIdx.x & 31;
+  // heavy rows (large i) first: the tail of the grid is then the cheap rows
+  const int i = n - 1 - (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5));
+  if (i < 0) return;
+  const double ei = er[i];
+  // energies ascend, so |dE| < ethr holds on a suffix of 0..i-1 (same rounding as the test below)
+  int lo = 0, hi = i;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (fabs(__dmul_rn(__dsub_rn(ei, er[mid]), kAutokcal)) < ethr) hi = mid; else lo = mid + 1;
+  }
+  const double ri[3] = {rot[3 * i], rot[3 * i + 1], rot[3 * i + 2]};
+  const double ai = aniso[i];
+  const double eni = enuc[i];
+  int c = 0;
+  for (int j0 = lo; j0 < i && c <= cap; j0 += 32) {
+    const int j = j0 + lane;
+    bool m = false;
+    if (j < i) {
+      const double de = __dmul_rn(__dsub_rn(ei, er[j]), kAutokcal);
+      if (fabs(de) < ethr) {
+        const double enj = enuc[j];
+        const double rel = __ddiv_rn(__dmul_rn(2.0, fabs(__dsub_rn(eni, enj))), __dadd_rn(eni, enj));
+        if (rel < 1.0e-3) {
+          const double rj[3] = {rot[3 * j], rot[3 * j + 1], rot[3 * j + 2]};
+          m = equalrotaniso_dev(ri, rj, ai, aniso[j], bthr, bthrmax, bthrshift);
+        }
+      }
+    }
+    unsigned bal = __ballot_sync(0xffffffffu, m);
+    while (bal && c <= cap) {
+      const int b = __ffs(bal) - 1;
+      if (c < cap && lane == 0) list[(size_t)i * cap + c] = j0 + b;
+      ++c;
+      bal &= bal - 1;
+    }
+  }
+  if (lane == 0) cnt[i] = c;     // cap + 1 = list cut
+}
+
 int launch_group(int n, const double* d_er, const double* d_rot, const double* d_enuc,
                  double ethr, double bthr, double bthrmax, double bthrshift, int* d_group,
                  cudaStream_t stream) {
+  const size_t m = (size_t)(n > 0 ? n : 1);
+  const int cap = tune().group_cap > 0 ? tune().group_cap : kGroupCap;
   unsigned char* head = nullptr;
   double* aniso = nullptr;
-  CREST_CUDA_TRY(cudaMallocAsync(&head, (size_t)(n > 0 ? n : 1), stream));
-  CREST_CUDA_TRY(cudaMallocAsync(&aniso, sizeof(double) * (size_t)(n > 0 ? n : 1), stream));
-  group_kernel<<<1, 1024, 0, stream>>>(n, d_er, d_rot, d_enuc, ethr, bthr, bthrmax, bthrshift,
-                                       d_group, head, aniso);
-  CREST_CUDA_TRY(cudaGetLastError());
+  int *d_cnt = nullptr, *d_list = nullptr;
+  CREST_CUDA_TRY(cudaMallocAsync(&head, m, stream));
+  CREST_CUDA_TRY(cudaMallocAsync(&aniso, sizeof(double) * m, stream));
+  CREST_CUDA_TRY(cudaMallocAsync(&d_cnt, sizeof(int) * m, stream));
+  CREST_CUDA_TRY(cudaMallocAsync(&d_list, sizeof(int) * m * cap, stream));
+  // CREST_CUDA_TUNE knob `seqgroup`: force the single-CTA sweep (A/B test of the two paths)
+  bool need_full = tune().seq_group != 0;
+  if (n > 0) {
+    group_aniso_kernel<<<(n + 255) / 256, 256, 0, stream>>>(n, d_rot, aniso);
+    group_match_kernel<<<(n + 7) / 8, 256, 0, stream>>>(n, d_er, d_rot, d_enuc, aniso, ethr, bthr,
+                                                        bthrmax, bthrshift, cap, d_cnt, d_list);
+    CREST_CUDA_TRY(cudaGetLastError());
+    std::vector<int> cnt(m), list(m * cap), group(m + 1);
+    CREST_CUDA_TRY(cudaMemcpyAsync(cnt.data(), d_cnt, sizeof(int) * m, cudaMemcpyDeviceToHost, stream));
+    CREST_CUDA_TRY(cudaMemcpyAsync(list.data(), d_list, sizeof(int) * m * cap,
+                                   cudaMemcpyDeviceToHost, stream));
+    CREST_CUDA_TRY(cudaStreamSynchronize(stream));
+    std::vector<unsigned char> h((size_t)n);
+    int ng = 0;
+    for (int i = 0; i < n && !need_full; ++i) {
+      int parent = -1;
+      const int k = cnt[i] < cap ? cnt[i] : cap;
+      for (int t = 0; t < k; ++t) {
+        const int j = list[(size_t)i * cap + t];
+        if (h[j]) { parent = j; break; }
+      }
+      if (parent < 0 && cnt[i] > cap) { need_full = true; break; }
+      if (parent < 0) { h[i] = 1; group[i + 1] = ++ng; }
+      else { h[i] = 0; group[i + 1] = group[parent + 1]; }
+    }
+    if (!need_full) {
+      group[0] = ng;
+      CREST_CUDA_TRY(cudaMemcpyAsync(d_group, group.data(), sizeof(int) * ((size_t)n + 1),
+                                     cudaMemcpyHostToDevice, stream));
+      CREST_CUDA_TRY(cudaStreamSynchronize(stream));   // `group` leaves scope
+    }
+  } else {
+    need_full = true;   // n == 0: the kernel writes group[0] = 0
+  }
+  if (need_full) {
+    group_kernel<<<1, 1024, 0, stream>>>(n, d_er, d_rot, d_enuc, ethr, bthr, bthrmax, bthrshift,
+                                         d_group, head, aniso);
+    CREST_CUDA_TRY(cudaGetLastError());
+  }
   CREST_CUDA_TRY(cudaFreeAsync(head, stream));
   CREST_CUDA_TRY(cudaFreeAsync(aniso, stream));
+  CREST_CUDA_TRY(cudaFreeAsync(d_cnt, stream));
+  CREST_CUDA_TRY(cudaFreeAsync(d_list, stream));
   return 0;
 }
 

@@ -15,6 +15,7 @@ module crest_cuda
   private
   public :: crest_cuda_thresholds
   public :: cregen_dup_cuda, cregen_group_cuda
+  public :: compare_blocks_cuda, intraconf_cuda
 
   !> the scalars of type(systemdata) that cross the boundary (src/classes.f90:332-345)
   type, bind(C) :: crest_cuda_thresholds
@@ -59,6 +60,30 @@ module crest_cuda
       type(c_ptr),value :: enuc                  !< double(nkept) or c_null_ptr
       integer(c_int) :: rc
     end function crest_cuda_cregen_group
+
+    !> replaces the main loop of compare_ensembles (ensemblecomp.f90:213-248)
+    function crest_cuda_compare_blocks(nat,nall1,xyz1,nconf1,b1,e1,nall2,xyz2,nconf2,b2,e2,rmat) &
+        &    result(rc) bind(C,name="crest_cuda_compare_blocks")
+      import
+      integer(c_int),intent(in),value :: nat,nall1,nconf1,nall2,nconf2
+      real(c_double),intent(in) :: xyz1(3,*),xyz2(3,*)
+      integer(c_int),intent(in) :: b1(*),e1(*),b2(*),e2(*)
+      real(c_double),intent(out) :: rmat(nconf1,*)
+      integer(c_int) :: rc
+    end function crest_cuda_compare_blocks
+
+    !> replaces the CONF loop of intraconfRMSD (entropy/entropic.f90:1000-1062)
+    function crest_cuda_intraconf(nat,nall,xyz,inc,nconf,low,nrot,symsym,fac,enantiofac) &
+        &    result(rc) bind(C,name="crest_cuda_intraconf")
+      import
+      integer(c_int),intent(in),value :: nat,nall,nconf
+      real(c_double),intent(in) :: xyz(3,*)
+      integer(c_int),intent(in) :: inc(*),low(*),nrot(*)
+      character(kind=c_char),intent(in) :: symsym(3,*)
+      real(c_double),intent(out) :: fac(*)
+      real(c_double),intent(inout) :: enantiofac(*)
+      integer(c_int) :: rc
+    end function crest_cuda_intraconf
 
     function crest_cuda_last_error() result(msg) bind(C,name="crest_cuda_last_error")
       import
@@ -153,5 +178,40 @@ contains
     group = 0
     group(0:nallout) = int(cgroup(0:nallout))
   end subroutine cregen_group_cuda
+
+  !> compare_ensembles: rmat(nconf1,nconf2) = block-wise minimum RMSD (ensemblecomp.f90:213-248)
+  subroutine compare_blocks_cuda(nat,nall1,xyz1,nconf1,b1,e1,nall2,xyz2,nconf2,b2,e2,rmat)
+    integer,intent(in) :: nat,nall1,nconf1,nall2,nconf2
+    real(c_double),intent(in) :: xyz1(3,nat,nall1),xyz2(3,nat,nall2)
+    integer,intent(in) :: b1(nconf1),e1(nconf1),b2(nconf2),e2(nconf2)
+    real(c_double),intent(out) :: rmat(nconf1,nconf2)
+    integer(c_int) :: rc
+    rc = crest_cuda_compare_blocks(int(nat,c_int),int(nall1,c_int),xyz1,int(nconf1,c_int), &
+        &   int(b1,c_int),int(e1,c_int),int(nall2,c_int),xyz2,int(nconf2,c_int), &
+        &   int(b2,c_int),int(e2,c_int),rmat)
+    if (rc /= 0) call cuda_fail('crest_cuda_compare_blocks')
+  end subroutine compare_blocks_cuda
+
+  !> intraconfRMSD: fac(nconf), enantiofac(nconf) (entropy/entropic.f90:938-1097); the rotamers of
+  !> conformer co are zens%xyz(:,:,nmat(co,1):nmat(co,nrot(co)))
+  subroutine intraconf_cuda(nat,nall,xyz,inc,nconf,low,nrot,symsym,fac,enantiofac)
+    integer,intent(in) :: nat,nall,nconf
+    real(c_double),intent(in) :: xyz(3,nat,nall)
+    integer,intent(in) :: inc(nat),low(nconf),nrot(nconf)
+    character(len=3),intent(in) :: symsym(nconf)
+    real(c_double),intent(out) :: fac(nconf)
+    real(c_double),intent(inout) :: enantiofac(nconf)
+    character(kind=c_char) :: csym(3,max(nconf,1))
+    integer(c_int) :: rc
+    integer :: c,k
+    do c = 1,nconf
+      do k = 1,3
+        csym(k,c) = symsym(c) (k:k)
+      end do
+    end do
+    rc = crest_cuda_intraconf(int(nat,c_int),int(nall,c_int),xyz,int(inc,c_int),int(nconf,c_int), &
+        &   int(low,c_int),int(nrot,c_int),csym,fac,enantiofac)
+    if (rc /= 0) call cuda_fail('crest_cuda_intraconf')
+  end subroutine intraconf_cuda
 
 end module crest_cuda

@@ -181,6 +181,70 @@ def test_group_entry(cb, oracle):
     assert np.abs(enuc / ref["enuc"][:n] - 1).max() < 1e-12
 
 
+@pytest.mark.parametrize("ethr,frac_rotamer", [(0.05, 0.05), (1e9, 0.05), (1e9, 0.6), (0.2, 0.6)])
+def test_group_paths_agree(cb, oracle, ethr, frac_rotamer):
+    """K6 three ways: two-phase sweep (match lists on the whole GPU + host resolve, the default), the
+    same with a list cap of 1 (rows whose single listed match is not a head fall back to the
+    single-CTA sweep) and the single-CTA sweep alone -- identical to the oracle's group()."""
+    from crest_b200 import cregen
+    ens = synth.make_ensemble(2000, 50, 23, seed=17, frac_rotamer=frac_rotamer)
+    ref = oracle.cregen_cre(ens["at"], ens["xyz"], ens["er"], ethr=ethr)
+    n = ref["nallout"]
+    assert ref["group"][0] < n                  # rotamers present: some groups hold > 1 structure
+    env = cb.Env(ethr=ethr)
+    for tune in (None, "groupcap=1", "seqgroup"):
+        cregen.set_tune(tune)
+        try:
+            group, _ = cb.cregen_group(env, 50, n, ens["at"], ref["xyz"][:n], ref["er"][:n],
+                                       ref["rot"][:n])
+        finally:
+            cregen.set_tune(None)
+        assert np.array_equal(group, ref["group"][:n + 1]), tune
+
+
+def test_group_nontransitive_matches(cb, oracle):
+    """Rot. constants spread over a few thresholds make 'equal' dense and NOT transitive: rows whose
+    first matches are non-heads exercise the list resolve, and with a list cap of 1-2 the fall-back
+    to the single-CTA sweep.  Reference = the K6 loop (cregen.f90:1437-1469) on the oracle's
+    equalrotaniso."""
+    from crest_b200 import cregen
+    rng = np.random.default_rng(23)
+    n, nat = 300, 12
+    ens = synth.make_ensemble(1, nat, nat, seed=3)
+    xyz = np.repeat(ens["xyz"][:1], n, axis=0)            # identical geometry: identical enuc
+    er = np.full(n, -100.0)
+    base = np.array([3000.0, 1200.0, 900.0])
+    rot = base[None, :] * (1.0 + rng.uniform(0.0, 0.10, size=(n, 1)) + rng.uniform(0, 2e-3, size=(n, 3)))
+    env = cb.Env(ethr=0.05)
+    head = np.zeros(n, bool)
+    ref = np.zeros(n + 1, np.int32)
+    nonhead_first = 0
+    for i in range(n):
+        parent, seen_nonhead = -1, False
+        for j in range(i):
+            if oracle.equalrotaniso(rot[i], rot[j], env.bthr2, env.bthrmax, env.bthrshift):
+                if head[j]:
+                    parent = j
+                    break
+                seen_nonhead = True
+        nonhead_first += seen_nonhead
+        if parent < 0:
+            head[i] = True
+            ref[0] += 1
+            ref[i + 1] = ref[0]
+        else:
+            ref[i + 1] = ref[parent + 1]
+    assert 3 < ref[0] < n // 4 and nonhead_first > 20      # the interesting regime
+    for tune in (None, "groupcap=1", "groupcap=2", "seqgroup"):
+        cregen.set_tune(tune)
+        try:
+            group, enuc = cb.cregen_group(env, nat, n, ens["at"], xyz, er, rot)
+        finally:
+            cregen.set_tune(None)
+        assert np.array_equal(group, ref), tune
+    assert np.all(enuc == enuc[0])
+
+
 @pytest.mark.parametrize("nall", [0, 1, 2, 3, 31, 32, 33, 64, 65])
 def test_ragged_sizes(cb, oracle, nall):
     """Empty / tiny / tile-edge ensemble sizes (tile 32 x 64)."""
