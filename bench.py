@@ -372,11 +372,17 @@ def run_ours(args):
     # the "CREGEN wall time" half of the metric, N = 1 only (stage B is one sequential sweep)
     cregen_wall = None
     if world == 1 and not args.no_e2e:
-        cb.cregen_CRE(env, nat, nall, at, xyz, er)
-        t0 = time.perf_counter()
-        full = cb.cregen_CRE(env, nat, nall, at, xyz, er)
-        cregen_wall = {"ms": (time.perf_counter() - t0) * 1e3, "api": "crest_cuda_cregen_cre (one call, host buffers; "
-                       "includes the host copies of the ctypes mirror)", "kept": int(full.nallout),
+        # the call works in place like the reference's cregen_CRE (xyz, er are permuted), so every
+        # repetition gets its own copy of the inputs, made outside the timed region
+        walls = []
+        for _ in range(3):
+            xyz_io, er_io = xyz.copy(), er.copy()
+            t0 = time.perf_counter()
+            full = cb.cregen_CRE_inplace(env, nat, nall, at, xyz_io, er_io)
+            walls.append(time.perf_counter() - t0)
+        cregen_wall = {"ms": min(walls[1:]) * 1e3,
+                       "api": "crest_cuda_cregen_cre (one call, pageable host buffers, in place like the "
+                              "reference; best of 2 after one warm-up call)", "kept": int(full.nallout),
                        "groups": int(full.group[0])}
 
     if rank == 0:

@@ -3,6 +3,7 @@
 Product code: crest_b200/csrc (CUDA kernels + C ABI, include/crest_cuda.h) and the thin host-side
 mirror of the reference interface in crest_b200.cregen.  No CPU fallback exists."""
 from .cregen import (Env, CregenContext, cregen_CRE, cregen_dup, cregen_group, rmsd_pairs,  # noqa: F401
-                     rotconst, rmat_allpairs, cregen_esort, rmsdalign, CrestCudaError)
+                     rotconst, rmat_allpairs, cregen_esort, rmsdalign, cregen_CRE_inplace,
+                     CrestCudaError)
 from ._lib import Thresholds  # noqa: F401
 from .compare import compare_blocks, compare_correlate, intraconf  # noqa: F401

@@ -129,11 +129,21 @@ class CreResult:
 
 
 def cregen_CRE(env: Env, nat, nall, at, xyz, er, nosort=False) -> CreResult:
-    """Whole cregen_CRE (duplicates + rotamer groups) through crest_cuda_cregen_cre."""
-    L = _lib.lib()
-    at = np.ascontiguousarray(at, np.int32)
+    """Whole cregen_CRE (duplicates + rotamer groups) through crest_cuda_cregen_cre; the inputs are
+    copied first (the reference works in place, see cregen_CRE_inplace)."""
     xyz = np.array(xyz, np.float64, order="C", copy=True).reshape(nall, nat, 3)
     er = np.array(er, np.float64, copy=True)
+    return cregen_CRE_inplace(env, nat, nall, at, xyz, er, nosort)
+
+
+def cregen_CRE_inplace(env: Env, nat, nall, at, xyz, er, nosort=False) -> CreResult:
+    """As the reference's cregen_CRE (cregen.f90:1125): xyz (nall,nat,3) float64 C-order and er are
+    overwritten with the principal-axis-frame geometries / energies in the new order."""
+    L = _lib.lib()
+    at = np.ascontiguousarray(at, np.int32)
+    if not (isinstance(xyz, np.ndarray) and xyz.dtype == np.float64 and xyz.flags.c_contiguous and
+            isinstance(er, np.ndarray) and er.dtype == np.float64 and er.flags.c_contiguous):
+        raise TypeError("cregen_CRE_inplace needs C-contiguous float64 xyz and er")
     mask, rfm = rmsd_mask(env, nat, at)
     rot = np.zeros((max(nall, 1), 3))
     order = np.zeros(max(nall, 1), np.int32)
@@ -145,7 +155,8 @@ def cregen_CRE(env: Env, nat, nall, at, xyz, er, nosort=False) -> CreResult:
                                        0 if env.entropic else 1, 1 if nosort else 0, C.byref(thr),
                                        _dp(rot), _ip(order), _ip(group), C.byref(nout),
                                        C.byref(npairs)))
-    return CreResult(nout.value, group, order[:nall], rot[:nall], xyz, er, npairs.value)
+    return CreResult(nout.value, group, order[:nall], rot[:nall], xyz.reshape(nall, nat, 3), er,
+                     npairs.value)
 
 
 def cregen_dup(env: Env, nat, nall, at, xyz, er, want_xyz=True):
