@@ -7,3 +7,4 @@ from .cregen import (Env, CregenContext, cregen_CRE, cregen_dup, cregen_group, r
                      CrestCudaError)
 from ._lib import Thresholds  # noqa: F401
 from .compare import compare_blocks, compare_correlate, intraconf  # noqa: F401
+from .ensemble_io import rdensembleparam, rdensemble, wrensemble, grepenergy, e2i  # noqa: F401

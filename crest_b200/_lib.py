@@ -40,6 +40,13 @@ SYMBOLS = {
     "crest_cuda_cregen_esort": (C.c_int, [C.c_int, C.c_int, c_dp, c_dp, C.c_double, c_ip, c_ip]),
     "crest_cuda_rmsdalign": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp]),
     "crest_cuda_rmat_allpairs": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_ip, C.c_int, c_fp]),
+    "crest_cuda_rdensemble_param": (C.c_int, [C.c_char_p, c_ip, c_ip]),
+    "crest_cuda_rdensemble": (C.c_int, [C.c_char_p, C.c_int, C.c_int, c_ip, c_dp, c_dp, C.c_char_p,
+                                        C.c_int, c_ip]),
+    "crest_cuda_wrensemble": (C.c_int, [C.c_char_p, C.c_int, C.c_int, c_ip, c_dp, c_dp, C.c_char_p,
+                                        C.c_int]),
+    "crest_cuda_grepenergy": (C.c_double, [C.c_char_p]),
+    "crest_cuda_e2i": (C.c_int, [C.c_char_p]),
     "crest_cuda_compare_blocks": (C.c_int, [C.c_int, C.c_int, c_dp, C.c_int, c_ip, c_ip, C.c_int, c_dp,
                                             C.c_int, c_ip, c_ip, c_dp]),
     "crest_cuda_compare_correlate": (C.c_int, [C.c_int, C.c_int, c_dp, c_dp, c_dp, C.c_double, c_ip, c_ip]),

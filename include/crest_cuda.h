@@ -97,6 +97,31 @@ int crest_cuda_cregen_esort(int nat, int nall, double* xyz, double* energies, do
  * optimal heavy-atom (at > 2) rotation of rmsd() (ls_rmsd.f90:72-221, option 1), in place. */
 int crest_cuda_rmsdalign(int nat, int nall, const int* at, double* xyz);
 
+/* ---- ensemble files either side of CREGEN (host code, src/strucreader.f90) ----
+ * rdensembleparam (268-309): number of readable structures and the largest atom count of an
+ * xyz ensemble / trajectory file; a missing file gives nat = nall = 0 like the reference. */
+int crest_cuda_rdensemble_param(const char* fname, int* nat, int* nall);
+
+/* rdensemble_conf3 (433-481) + grepenergy (2225-2260): reads up to nall structures of nat atoms
+ * (structures with another atom count are skipped, ensemble_strucskip) into at(nat),
+ * xyz(3,nat,nall) and er(nall) = grepenergy(comment line); comments (nall records of comment_len
+ * blank-padded characters = the reference's character(len=*) array) may be NULL, so may er and
+ * nread (number of structures actually read).  Coordinate lines follow coordline (2005-2022):
+ * "x y z sym" or "sym x y z"; labels map through e2i (2120-2147).  An unreadable coordinate line
+ * or a truncated last structure is an error (the reference: `error stop` on the latter). */
+int crest_cuda_rdensemble(const char* fname, int nat, int nall, int* at, double* xyz, double* er,
+                          char* comments, int comment_len, int* nread);
+
+/* wrxyz_channel (1679-1698) for every structure, as the ensemble writers of cregen.f90:2143-2151
+ * do: '(2x,i0)' nat, the trimmed comment record, '(1x,a2,1x,3f20.10)' per atom with
+ * i2e(at,'nc').  comments == NULL writes the energy er(i) alone (blank line if er is NULL too). */
+int crest_cuda_wrensemble(const char* fname, int nat, int nall, const int* at, const double* xyz,
+                          const double* er, const char* comments, int comment_len);
+
+/* grepenergy (2225-2260) and e2i (2120-2147) on their own. */
+double crest_cuda_grepenergy(const char* line);
+int crest_cuda_e2i(const char* label);
+
 /* ---- callers of rmsd() beside cregen_CRE ----
  * compare_ensembles main loop (src/ensemblecomp.f90:213-248): rmat(i,j) = minimum all-atom RMSD
  * (ls_rmsd.f90:72-174, no mirror) between any rotamer of conformer i of ensemble 1 and any rotamer
