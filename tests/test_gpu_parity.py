@@ -245,6 +245,32 @@ def test_group_nontransitive_matches(cb, oracle):
     assert np.all(enuc == enuc[0])
 
 
+def test_staged_pageable_copies(cb):
+    """Transfers >= 32 MB from / to pageable caller memory go through the threaded pinned staging
+    (capi.cu big_copy): same bytes as plain cudaMemcpy (copythr=0), H2D and D2H, odd sizes."""
+    from crest_b200 import cregen
+    ens = synth.make_ensemble(30011, 50, 23, seed=31)          # 36 MB of xyz, not a chunk multiple
+    env = cb.Env(ethr=0.02)
+    nall, nat, _ = ens["xyz"].shape
+    out = {}
+    for tune in ("copythr=0", None, "copythr=3"):
+        cregen.set_tune(tune)
+        try:
+            d = cb.cregen_dup(env, nat, nall, ens["at"], ens["xyz"], ens["er"], want_xyz=True)
+            x, e = ens["xyz"].copy(), ens["er"].copy()
+            r = cb.cregen_CRE_inplace(env, nat, nall, ens["at"], x, e)
+        finally:
+            cregen.set_tune(None)
+        out[tune] = (d, r)
+    d0, r0 = out["copythr=0"]
+    for tune in (None, "copythr=3"):
+        d, r = out[tune]
+        assert np.array_equal(d["dup"], d0["dup"]) and np.array_equal(d["rot"], d0["rot"])
+        assert np.array_equal(d["xyz_axis"], d0["xyz_axis"])
+        assert np.array_equal(r.xyz, r0.xyz) and np.array_equal(r.order, r0.order)
+        assert np.array_equal(r.group, r0.group) and r.nallout == r0.nallout
+
+
 @pytest.mark.parametrize("nall", [0, 1, 2, 3, 31, 32, 33, 64, 65])
 def test_ragged_sizes(cb, oracle, nall):
     """Empty / tiny / tile-edge ensemble sizes (tile 32 x 64)."""
