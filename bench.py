@@ -186,7 +186,7 @@ def run_reference(args):
             "data": "synthetic", "config": workload_config(args, ens), "cpu_baseline": cb,
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_OUT, flush=True)
 
 
 class _DevArray:
@@ -430,14 +430,24 @@ def run_ours(args):
             cbase = cpu_sample(ens, args, args.cpu_seconds)
             cbase.pop("pairs"), cbase.pop("seconds")
             line["cpu_baseline"] = cbase
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_OUT, flush=True)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
 
 
+def _json_only_stdout():
+    """Libraries may write to fd 1 (NCCL prints its version banner there on some boxes): everything
+    except the final JSON line goes to stderr, so stdout carries exactly ONE line."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    return os.fdopen(real, "w")
+
+
 if __name__ == "__main__":
     a = parse()
+    _OUT = _json_only_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:

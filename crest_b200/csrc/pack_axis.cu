@@ -9,8 +9,8 @@
 // (cregen.f90:1293-1299, 2056-2101) and rmsd()'s unweighted centroid removal + norms
 // (src/ls_rmsd.f90:105-119), writing the packed operand X of the covariance contraction.
 //
-// One warp per conformer; lanes stride over atoms (24-byte records => fully coalesced), warp
-// shuffles reduce, every lane redoes the 3x3 eigenproblem redundantly (uniform control flow).
+// One warp per 32 conformers; in the memory passes groups of 8 lanes stride over the atoms of one
+// conformer each and group shuffles reduce; the 3x3 eigenproblems run one conformer per lane.
 // This file is compiled with -fmad=false: the eigen-solver follows the reference's operation
 // order so rot. constants agree to ~1e-12 relative away from degenerate moments.
 #include "common.cuh"
@@ -24,6 +24,14 @@ __constant__ double c_ams[CREST_NUM_ELEMENTS] = CREST_AMS_TABLE_INIT;
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// sum over aligned groups of G lanes (G = 32: the whole warp); every lane of a group gets the sum
+template <int G>
+__device__ __forceinline__ double group_sum(double v) {
+#pragma unroll
+  for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
 
@@ -145,22 +153,22 @@ __device__ void eigvec_sym3(Sym3 a, double w[3], Mat3& q) {
 
 // axis_0 core on coordinates supplied through a functor: returns rot (MHz), evec, CMA.
 // `get(k, z, px,py,pz)` yields atom k of the (sub)structure.  Lanes stride over atoms.
-template <class Get>
-__device__ void axis0_warp(int n, Get get, int lane, double rot[3], Mat3& evec, double cma[3]) {
-  // CMA (axis_module.f90:384-412; sumw seeded with 1e-20)
+template <int G, class Get>
+__device__ __forceinline__ void axis0_tensor(int n, Get get, int sl, Sym3& a, double cma[3]) {
+  // CMA (axis_module.f90:384-412; sumw seeded with 1e-20); sl = lane within the group of G lanes
   double sw = 0.0, sx = 0.0, sy = 0.0, sz = 0.0;
-  for (int k = lane; k < n; k += 32) {
+  for (int k = sl; k < n; k += G) {
     int z; double x, y, zc;
     get(k, z, x, y, zc);
     const double m = mass_of(z);
     sw += m; sx += m * x; sy += m * y; sz += m * zc;
   }
-  sw = warp_sum(sw) + 1.0e-20;
-  sx = warp_sum(sx) / sw; sy = warp_sum(sy) / sw; sz = warp_sum(sz) / sw;
+  sw = group_sum<G>(sw) + 1.0e-20;
+  sx = group_sum<G>(sx) / sw; sy = group_sum<G>(sy) / sw; sz = group_sum<G>(sz) / sw;
   cma[0] = sx; cma[1] = sy; cma[2] = sz;
   // inertia tensor (axis_module.f90:130-141)
   double t1 = 0, t2 = 0, t3 = 0, t4 = 0, t5 = 0, t6 = 0;
-  for (int k = lane; k < n; k += 32) {
+  for (int k = sl; k < n; k += G) {
     int z; double x, y, zc;
     get(k, z, x, y, zc);
     const double m = mass_of(z);
@@ -172,13 +180,17 @@ __device__ void axis0_warp(int n, Get get, int lane, double rot[3], Mat3& evec, 
     t5 -= m * y * zc;
     t6 += m * (x * x + y * y);
   }
-  Sym3 a;
-  a.a11 = warp_sum(t1) + 1.0e-10;
-  a.a12 = warp_sum(t2) + 2.0e-10;
-  a.a22 = warp_sum(t3) + 3.0e-10;
-  a.a13 = warp_sum(t4) + 4.0e-10;
-  a.a23 = warp_sum(t5) + 5.0e-10;
-  a.a33 = warp_sum(t6) + 6.0e-10;
+  a.a11 = group_sum<G>(t1) + 1.0e-10;
+  a.a12 = group_sum<G>(t2) + 2.0e-10;
+  a.a22 = group_sum<G>(t3) + 3.0e-10;
+  a.a13 = group_sum<G>(t4) + 4.0e-10;
+  a.a23 = group_sum<G>(t5) + 5.0e-10;
+  a.a33 = group_sum<G>(t6) + 6.0e-10;
+}
+
+// the eigenproblem of one structure: moments -> rot (MHz), eigenvectors.  Called per LANE by the
+// pack kernel (32 different structures per warp) and lane-uniformly by rotconst_kernel.
+__device__ __noinline__ void axis0_solve(const Sym3& a, double rot[3], Mat3& evec) {
   double eig[3];
   eigvec_sym3(a, eig, evec);
   for (int i = 0; i < 3; ++i) {
@@ -189,25 +201,64 @@ __device__ void axis0_warp(int n, Get get, int lane, double rot[3], Mat3& evec, 
   }
 }
 
+template <class Get>
+__device__ void axis0_warp(int n, Get get, int lane, double rot[3], Mat3& evec, double cma[3]) {
+  Sym3 a;
+  axis0_tensor<32>(n, get, lane, a, cma);
+  axis0_solve(a, rot, evec);
+}
+
+// One warp owns 32 consecutive conformers.  Memory passes (CMA, inertia tensor, rotation, packing):
+// groups of 8 lanes work on one conformer each, four conformers in flight per warp and eight rounds
+// per pass (lanes stride over atoms: 8 x 24 B = 192 B contiguous per step).  The two 3x3
+// eigenproblems per conformer -- FP64 trigonometry, divisions and square roots, by far the longest
+// instruction stream of the kernel -- run ONE CONFORMER PER LANE (they used to run 32 times
+// redundantly per warp).  Per-conformer arithmetic is the reference's operation order; only the
+// association of the atom sums differs from a serial loop, as it always did.
+constexpr int kPG = 8;                 // lanes per conformer in the memory passes
+constexpr int kPC = 32 / kPG;          // conformers in flight per warp
+
+__device__ __forceinline__ double take(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+
 __global__ void __launch_bounds__(128)
 pack_axis_kernel(int nat, int nall, const int* __restrict__ at, const double* __restrict__ xyz,
                  const int* __restrict__ sel, int nsel, int rot_from_mask, PackLayout L,
                  double* __restrict__ xyz_axis, double* __restrict__ rot_out,
                  double* __restrict__ aniso_out, double* __restrict__ X,
                  double* __restrict__ xn_out) {
-  const int lane = threadIdx.x & 31;
-  const int conf = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (conf >= nall) return;
-  const double* src = xyz + (size_t)3 * nat * conf;
-  double* dst = xyz_axis + (size_t)3 * nat * conf;
+  const int lane = threadIdx.x & 31, g = lane / kPG, sl = lane % kPG;
+  const int c0 = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 32;
+  if (c0 >= nall) return;
+  const int nc = min(32, nall - c0);
+  const int nround = (nc + kPC - 1) / kPC;
 
-  // ---- pass 1: axis_4 = CMA shift + rotation into the principal-axis frame
-  double rot[3], cma[3];
+  // ---- pass 1a: CMA + inertia tensor; afterwards lane c holds conformer c0+c
+  Sym3 myA{1.0, 0.0, 0.0, 2.0, 0.0, 3.0};     // idle lanes solve a harmless diagonal problem
+  double myCma[3] = {0.0, 0.0, 0.0};
+  for (int r = 0; r < nround; ++r) {
+    const int c = r * kPC + g;
+    const int cc = c < nc ? c : 0;             // idle groups recompute conformer c0 (discarded)
+    const double* src = xyz + (size_t)3 * nat * (c0 + cc);
+    auto get_all = [&](int k, int& z, double& x, double& y, double& zc) {
+      z = at[k]; x = src[3 * k]; y = src[3 * k + 1]; zc = src[3 * k + 2];
+    };
+    Sym3 a; double cma[3];
+    axis0_tensor<kPG>(nat, get_all, sl, a, cma);
+    // lane L in [4r, 4r+4) takes the result of group L-4r
+    const int from = kPG * (lane % kPC);
+    const bool mine = lane / kPC == r && lane < nc;
+    const double v[9] = {take(a.a11, from), take(a.a12, from), take(a.a13, from), take(a.a22, from),
+                         take(a.a23, from), take(a.a33, from), take(cma[0], from), take(cma[1], from),
+                         take(cma[2], from)};
+    if (mine) {
+      myA.a11 = v[0]; myA.a12 = v[1]; myA.a13 = v[2]; myA.a22 = v[3]; myA.a23 = v[4]; myA.a33 = v[5];
+      myCma[0] = v[6]; myCma[1] = v[7]; myCma[2] = v[8];
+    }
+  }
+  // ---- pass 1b: axis_4's eigenproblem, one conformer per lane
+  double rot[3];
   Mat3 ev;
-  auto get_all = [&](int k, int& z, double& x, double& y, double& zc) {
-    z = at[k]; x = src[3 * k]; y = src[3 * k + 1]; zc = src[3 * k + 2];
-  };
-  axis0_warp(nat, get_all, lane, rot, ev, cma);
+  axis0_solve(myA, rot, ev);
   {
     // calcxsum (axis_module.f90:372-378): keep a right-handed frame
     const double xsum = ev.m[0][0] * (ev.m[1][1] * ev.m[2][2] - ev.m[2][1] * ev.m[1][2]) +
@@ -215,72 +266,102 @@ pack_axis_kernel(int nat, int nall, const int* __restrict__ at, const double* __
                         ev.m[0][2] * (ev.m[1][0] * ev.m[2][1] - ev.m[1][1] * ev.m[2][0]);
     if (xsum < 0.0) { ev.m[0][0] = -ev.m[0][0]; ev.m[1][0] = -ev.m[1][0]; ev.m[2][0] = -ev.m[2][0]; }
   }
-  for (int k = lane; k < nat; k += 32) {
-    const double x = src[3 * k] - cma[0], y = src[3 * k + 1] - cma[1], z = src[3 * k + 2] - cma[2];
+  // ---- pass 1c + 2a: rotate into the principal-axis frame, then the tensor of the rotated
+  // structure (all atoms, or the subset if substruc) for axis_1
+  myA = Sym3{1.0, 0.0, 0.0, 2.0, 0.0, 3.0};
+  for (int r = 0; r < nround; ++r) {
+    const int c = r * kPC + g;
+    const bool live = c < nc;
+    const int cc = live ? c : 0;
+    const double* src = xyz + (size_t)3 * nat * (c0 + cc);
+    double* dst = xyz_axis + (size_t)3 * nat * (c0 + cc);
+    double e[3][3], cm[3];
 #pragma unroll
-    for (int j = 0; j < 3; ++j) {
-      double s = 0.0;
-      s = s + x * ev.m[0][j];
-      s = s + y * ev.m[1][j];
-      s = s + z * ev.m[2][j];
-      dst[3 * k + j] = s;
+    for (int i = 0; i < 3; ++i) {
+      cm[i] = take(myCma[i], cc);
+#pragma unroll
+      for (int j = 0; j < 3; ++j) e[i][j] = take(ev.m[i][j], cc);
     }
+    if (live)
+      for (int k = sl; k < nat; k += kPG) {
+        const double x = src[3 * k] - cm[0], y = src[3 * k + 1] - cm[1], z = src[3 * k + 2] - cm[2];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          double s = 0.0;
+          s = s + x * e[0][j];
+          s = s + y * e[1][j];
+          s = s + z * e[2][j];
+          dst[3 * k + j] = s;
+        }
+      }
+    __syncwarp();
+    Sym3 a; double cma2[3];
+    if (rot_from_mask) {
+      auto get_sub = [&](int k, int& z, double& x, double& y, double& zc) {
+        const int q = sel[k];
+        z = at[q]; x = dst[3 * q]; y = dst[3 * q + 1]; zc = dst[3 * q + 2];
+      };
+      axis0_tensor<kPG>(nsel, get_sub, sl, a, cma2);
+    } else {
+      auto get_rot = [&](int k, int& z, double& x, double& y, double& zc) {
+        z = at[k]; x = dst[3 * k]; y = dst[3 * k + 1]; zc = dst[3 * k + 2];
+      };
+      axis0_tensor<kPG>(nat, get_rot, sl, a, cma2);
+    }
+    const int from = kPG * (lane % kPC);
+    const bool mine = lane / kPC == r && lane < nc;
+    const double v[6] = {take(a.a11, from), take(a.a12, from), take(a.a13, from), take(a.a22, from),
+                         take(a.a23, from), take(a.a33, from)};
+    if (mine) { myA.a11 = v[0]; myA.a12 = v[1]; myA.a13 = v[2]; myA.a22 = v[3]; myA.a23 = v[4]; myA.a33 = v[5]; }
   }
-  __syncwarp();
-
-  // ---- pass 2: axis_1 on the rotated structure (all atoms, or the subset if substruc)
-  Mat3 ev2;
-  double cma2[3];
-  if (rot_from_mask) {
-    auto get_sub = [&](int k, int& z, double& x, double& y, double& zc) {
-      const int a = sel[k];
-      z = at[a]; x = dst[3 * a]; y = dst[3 * a + 1]; zc = dst[3 * a + 2];
-    };
-    axis0_warp(nsel, get_sub, lane, rot, ev2, cma2);
-  } else {
-    auto get_rot = [&](int k, int& z, double& x, double& y, double& zc) {
-      z = at[k]; x = dst[3 * k]; y = dst[3 * k + 1]; zc = dst[3 * k + 2];
-    };
-    axis0_warp(nat, get_rot, lane, rot, ev2, cma2);
-  }
-  if (lane == 0) {
-    rot_out[3 * conf + 0] = rot[0];
-    rot_out[3 * conf + 1] = rot[1];
-    rot_out[3 * conf + 2] = rot[2];
-    aniso_out[conf] = rotaniso_dev(rot[0], rot[1], rot[2]);
+  // ---- pass 2b: axis_1's eigenproblem per lane -> rot. constants
+  axis0_solve(myA, rot, ev);
+  if (lane < nc) {
+    rot_out[3 * (c0 + lane) + 0] = rot[0];
+    rot_out[3 * (c0 + lane) + 1] = rot[1];
+    rot_out[3 * (c0 + lane) + 2] = rot[2];
+    aniso_out[c0 + lane] = rotaniso_dev(rot[0], rot[1], rot[2]);
   }
 
   // ---- pass 3: RMSD subset, unweighted centroid (ls_rmsd.f90:105-119), packed operand + norm
-  double cx = 0.0, cy = 0.0, cz = 0.0;
-  for (int k = lane; k < nsel; k += 32) {
-    const int a = sel[k];
-    cx += dst[3 * a]; cy += dst[3 * a + 1]; cz += dst[3 * a + 2];
-  }
   const double inv_n = 1.0 / (double)nsel;
-  cx = warp_sum(cx) * inv_n; cy = warp_sum(cy) * inv_n; cz = warp_sum(cz) * inv_n;
-  const int panel = conf / L.rows, row = conf % L.rows;
-  double nrm = 0.0;
   const int kpad = L.nslab * L.KU;
   const int last0 = kpad - 8;          // first slot of the last 8-atom block
-  for (int k = lane; k < kpad; k += 32) {
-    // slot k holds selected atom ks (or nothing): identity, except in a half tail where the
-    // <= 4 atoms of the last block sit at its even slots
-    int ks = k;
-    if (L.half_tail && k >= last0) ks = ((k - last0) & 1) ? -1 : last0 + ((k - last0) >> 1);
-    double x = 0.0, y = 0.0, z = 0.0;
-    if (ks >= 0 && ks < nsel) {
-      const int a = sel[ks];
-      x = dst[3 * a] - cx; y = dst[3 * a + 1] - cy; z = dst[3 * a + 2] - cz;
-      nrm += x * x + y * y + z * z;
+  for (int r = 0; r < nround; ++r) {
+    const int c = r * kPC + g;
+    const bool live = c < nc;
+    const int conf = c0 + (live ? c : 0);
+    const double* dst = xyz_axis + (size_t)3 * nat * conf;
+    double cx = 0.0, cy = 0.0, cz = 0.0;
+    for (int k = sl; k < nsel; k += kPG) {
+      const int a = sel[k];
+      cx += dst[3 * a]; cy += dst[3 * a + 1]; cz += dst[3 * a + 2];
     }
-    const int slab = k / L.KU, kk = k % L.KU;
-    double* chunk = X + ((size_t)panel * L.nslab + slab) * L.chunk_doubles();
-    chunk[((size_t)0 * L.rows + row) * L.KS + kk] = x;
-    chunk[((size_t)1 * L.rows + row) * L.KS + kk] = y;
-    chunk[((size_t)2 * L.rows + row) * L.KS + kk] = z;
+    cx = group_sum<kPG>(cx) * inv_n; cy = group_sum<kPG>(cy) * inv_n; cz = group_sum<kPG>(cz) * inv_n;
+    const int panel = conf / L.rows, row = conf % L.rows;
+    double nrm = 0.0;
+    for (int k = sl; k < kpad; k += kPG) {
+      // slot k holds selected atom ks (or nothing): identity, except in a half tail where the
+      // <= 4 atoms of the last block sit at its even slots
+      int ks = k;
+      if (L.half_tail && k >= last0) ks = ((k - last0) & 1) ? -1 : last0 + ((k - last0) >> 1);
+      double x = 0.0, y = 0.0, z = 0.0;
+      if (ks >= 0 && ks < nsel) {
+        const int a = sel[ks];
+        x = dst[3 * a] - cx; y = dst[3 * a + 1] - cy; z = dst[3 * a + 2] - cz;
+        nrm += x * x + y * y + z * z;
+      }
+      if (live) {
+        const int slab = k / L.KU, kk = k % L.KU;
+        double* chunk = X + ((size_t)panel * L.nslab + slab) * L.chunk_doubles();
+        chunk[((size_t)0 * L.rows + row) * L.KS + kk] = x;
+        chunk[((size_t)1 * L.rows + row) * L.KS + kk] = y;
+        chunk[((size_t)2 * L.rows + row) * L.KS + kk] = z;
+      }
+    }
+    nrm = group_sum<kPG>(nrm);
+    if (live && sl == 0) xn_out[conf] = nrm;
   }
-  nrm = warp_sum(nrm);
-  if (lane == 0) xn_out[conf] = nrm;
 }
 
 __global__ void __launch_bounds__(128)
@@ -306,8 +387,10 @@ int launch_pack_axis(int nat, int nall, const int* d_at, const double* d_xyz, co
                      double* d_rot, double* d_aniso, double* d_X, double* d_xn,
                      cudaStream_t stream) {
   if (nall <= 0) return 0;
-  const int wpb = 4;
-  pack_axis_kernel<<<(nall + wpb - 1) / wpb, wpb * 32, 0, stream>>>(
+  // one warp per 32 conformers, 2 warps per block: C3 = 3125 warps over 148 SMs
+  const int wpb = 2;
+  const int nwarp = (nall + 31) / 32;
+  pack_axis_kernel<<<(nwarp + wpb - 1) / wpb, wpb * 32, 0, stream>>>(
       nat, nall, d_at, d_xyz, d_sel, nsel, rot_from_mask, L, d_xyz_axis, d_rot, d_aniso, d_X, d_xn);
   CREST_CUDA_TRY(cudaGetLastError());
   return 0;
