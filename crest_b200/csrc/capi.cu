@@ -61,6 +61,7 @@ static void parse_tune(const char* e, Tune& t) {
   if (std::strstr(e, "nohalf")) t.no_half = 1;
   if (std::strstr(e, "notf32")) t.no_tf32 = 1;
   if (std::strstr(e, "seqgroup")) t.seq_group = 1;
+  if (const char* q = std::strstr(e, "packg=")) if (std::sscanf(q + 6, "%d", &v) == 1) t.pack_g = v;
   if (const char* q = std::strstr(e, "copythr=")) if (std::sscanf(q + 8, "%d", &v) == 1) t.copy_threads = v;
   if (const char* q = std::strstr(e, "groupcap=")) if (std::sscanf(q + 9, "%d", &v) == 1) t.group_cap = v;
   if (const char* q = std::strstr(e, "cap=")) if (std::sscanf(q + 4, "%d", &v) == 1) t.cand_cap = v;

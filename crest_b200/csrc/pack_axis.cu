@@ -215,17 +215,19 @@ __device__ void axis0_warp(int n, Get get, int lane, double rot[3], Mat3& evec, 
 // instruction stream of the kernel -- run ONE CONFORMER PER LANE (they used to run 32 times
 // redundantly per warp).  Per-conformer arithmetic is the reference's operation order; only the
 // association of the atom sums differs from a serial loop, as it always did.
-constexpr int kPG = 8;                 // lanes per conformer in the memory passes
-constexpr int kPC = 32 / kPG;          // conformers in flight per warp
+// kPG = lanes per conformer in the memory passes (template parameter; CREST_CUDA_TUNE packg=4|8|16),
+// kPC = 32 / kPG conformers in flight per warp
 
 __device__ __forceinline__ double take(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 
-__global__ void __launch_bounds__(128)
+template <int kPG>
+__global__ void __launch_bounds__(64, 12)   // <= 85 registers: 24 warps per SM, C3's 3125 warps are one wave
 pack_axis_kernel(int nat, int nall, const int* __restrict__ at, const double* __restrict__ xyz,
                  const int* __restrict__ sel, int nsel, int rot_from_mask, PackLayout L,
                  double* __restrict__ xyz_axis, double* __restrict__ rot_out,
                  double* __restrict__ aniso_out, double* __restrict__ X,
                  double* __restrict__ xn_out) {
+  constexpr int kPC = 32 / kPG;
   const int lane = threadIdx.x & 31, g = lane / kPG, sl = lane % kPG;
   const int c0 = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 32;
   if (c0 >= nall) return;
@@ -390,8 +392,14 @@ int launch_pack_axis(int nat, int nall, const int* d_at, const double* d_xyz, co
   // one warp per 32 conformers, 2 warps per block: C3 = 3125 warps over 148 SMs
   const int wpb = 2;
   const int nwarp = (nall + 31) / 32;
-  pack_axis_kernel<<<(nwarp + wpb - 1) / wpb, wpb * 32, 0, stream>>>(
-      nat, nall, d_at, d_xyz, d_sel, nsel, rot_from_mask, L, d_xyz_axis, d_rot, d_aniso, d_X, d_xn);
+  const dim3 grid((nwarp + wpb - 1) / wpb), block(wpb * 32);
+#define CREST_PACK_ARGS nat, nall, d_at, d_xyz, d_sel, nsel, rot_from_mask, L, d_xyz_axis, d_rot, d_aniso, d_X, d_xn
+  switch (tune().pack_g) {
+    case 4: pack_axis_kernel<4><<<grid, block, 0, stream>>>(CREST_PACK_ARGS); break;
+    case 16: pack_axis_kernel<16><<<grid, block, 0, stream>>>(CREST_PACK_ARGS); break;
+    default: pack_axis_kernel<8><<<grid, block, 0, stream>>>(CREST_PACK_ARGS); break;
+  }
+#undef CREST_PACK_ARGS
   CREST_CUDA_TRY(cudaGetLastError());
   return 0;
 }
