@@ -394,6 +394,16 @@ int crest_cuda_ctx_create(crest_cuda_ctx** out, int device) {
   if (device < 0) CREST_CUDA_TRY(cudaGetDevice(&device));
   if (device >= ndev) { set_error("device %d out of range (%d devices)", device, ndev); return 1; }
   CREST_CUDA_TRY(cudaSetDevice(device));
+  {
+    // the small per-call scratch buffers come from cudaMallocAsync: keep the pool's memory across
+    // synchronisations instead of returning it to the driver every time (the default threshold is 0)
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+      unsigned long long keep = ~0ull;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+    cudaGetLastError();
+  }
   crest_cuda_ctx* c = new crest_cuda_ctx();
   c->device = device;
   if (cudaMalloc(&c->d_npairs, sizeof(unsigned long long)) != cudaSuccess) {

@@ -226,12 +226,14 @@ pack_axis_kernel(int nat, int nall, const int* __restrict__ at, const double* __
                  const int* __restrict__ sel, int nsel, int rot_from_mask, PackLayout L,
                  double* __restrict__ xyz_axis, double* __restrict__ rot_out,
                  double* __restrict__ aniso_out, double* __restrict__ X,
-                 double* __restrict__ xn_out) {
+                 double* __restrict__ xn_out, int W) {
   constexpr int kPC = 32 / kPG;
   const int lane = threadIdx.x & 31, g = lane / kPG, sl = lane % kPG;
-  const int c0 = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 32;
+  // W = conformers per warp (multiple of kPC, <= 32): 32 fills every lane of the eigen-solves; small
+  // ensembles take fewer per warp so that the grid still covers the SMs
+  const int c0 = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * W;
   if (c0 >= nall) return;
-  const int nc = min(32, nall - c0);
+  const int nc = min(W, nall - c0);
   const int nround = (nc + kPC - 1) / kPC;
 
   // ---- pass 1a: CMA + inertia tensor; afterwards lane c holds conformer c0+c
@@ -389,12 +391,21 @@ int launch_pack_axis(int nat, int nall, const int* d_at, const double* d_xyz, co
                      double* d_rot, double* d_aniso, double* d_X, double* d_xn,
                      cudaStream_t stream) {
   if (nall <= 0) return 0;
-  // one warp per 32 conformers, 2 warps per block: C3 = 3125 warps over 148 SMs
+  // Conformers per warp: 32 when that still gives every SM its 24 resident warps' worth of work
+  // (C3: 3125 warps, one wave); otherwise halve down to one round of 32/G conformers so that small
+  // ensembles (C4: 20 000 x 300) are not serialised inside a few hundred warps.
+  int G = tune().pack_g;
+  if (G != 4 && G != 16) G = 8;
+  int dev = 0, nsm = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+  int W = 32;
+  while (W > 32 / G && (nall + W - 1) / W < nsm * 16) W >>= 1;
   const int wpb = 2;
-  const int nwarp = (nall + 31) / 32;
+  const int nwarp = (nall + W - 1) / W;
   const dim3 grid((nwarp + wpb - 1) / wpb), block(wpb * 32);
-#define CREST_PACK_ARGS nat, nall, d_at, d_xyz, d_sel, nsel, rot_from_mask, L, d_xyz_axis, d_rot, d_aniso, d_X, d_xn
-  switch (tune().pack_g) {
+#define CREST_PACK_ARGS nat, nall, d_at, d_xyz, d_sel, nsel, rot_from_mask, L, d_xyz_axis, d_rot, d_aniso, d_X, d_xn, W
+  switch (G) {
     case 4: pack_axis_kernel<4><<<grid, block, 0, stream>>>(CREST_PACK_ARGS); break;
     case 16: pack_axis_kernel<16><<<grid, block, 0, stream>>>(CREST_PACK_ARGS); break;
     default: pack_axis_kernel<8><<<grid, block, 0, stream>>>(CREST_PACK_ARGS); break;
