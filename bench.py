@@ -368,7 +368,8 @@ def run_ours(args):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dts = [float(x) for x in tt]
         dt = float(np.median(dts))
-        print("e2e step times (ms):", " ".join(f"{x * 1e3:.2f}" for x in dts), file=sys.stderr)
+        if rank == 0:
+            print("e2e step times (ms):", " ".join(f"{x * 1e3:.2f}" for x in dts), file=sys.stderr)
         e2e = {"value": pairs_step / dt, "unit": UNIT,
                "h2d_bytes_per_step": int(xyz.nbytes + world * (er.nbytes + at.nbytes)),
                "d2h_bytes_per_step": int(nall * 4 + nall * 24 + 8), "ms_per_step": dt * 1e3,
