@@ -145,6 +145,7 @@ struct crest_cuda_ctx {
   int* d_tf_items = nullptr;
   size_t cap_tf_items = 0;
   double tf_items_ethr = std::numeric_limits<double>::quiet_NaN();
+  int tf_items_nranks = 0;     // the item size depends on the number of ranks sharing the list
   int last_variant = 0;                // 0 row-tile DMMA, 1 column DMMA, 2 TF32 screen + exact list
 };
 
@@ -239,7 +240,7 @@ void col_items_host(int n, const double* er, double ethr, std::vector<int>& item
 // gated pair by pair (cregen.f90:1275); the rest of the band needs no energies at all.  The list is
 // cut on a fixed grid of `chunk` groups and ordered segment-major so that concurrently running CTAs
 // stream the same j-groups (L2-resident) past different i-tiles.
-void tf_items_host(int n, const double* er, double ethr, std::vector<int>& items) {
+void tf_items_host(int n, const double* er, double ethr, std::vector<int>& items, int nranks = 1) {
   items.clear();
   if (n < 2) return;
   const int ntile = (n + 127) / 128;
@@ -264,7 +265,9 @@ void tf_items_host(int n, const double* er, double ethr, std::vector<int>& items
     gg[I] = (jint + 15) / 16;
     total += ge[I] - gb[I];
   }
-  long long chunk = tune().chunk > 0 ? tune().chunk : total / (148LL * 16);
+  // >= 16 items per CTA and rank: the CTAs of a rank take its items round-robin, so the stage lasts
+  // ceil(items / 148) items (measured on C3: 128-group items cost nothing against 256, 64 cost 1.3 %)
+  long long chunk = tune().chunk > 0 ? tune().chunk : total / (148LL * 16 * (nranks > 0 ? nranks : 1));
   if (chunk < 8) chunk = 8;
   if (chunk > 256 && tune().chunk <= 0) chunk = 256;
   const int ngroup = ntile * 8;
@@ -278,9 +281,10 @@ void tf_items_host(int n, const double* er, double ethr, std::vector<int>& items
   }
 }
 
-int upload_tf_items(crest_cuda_ctx* c, double ethr, cudaStream_t st) {
-  tf_items_host(c->nall, c->h_er.data(), ethr, c->tf_items);
+int upload_tf_items(crest_cuda_ctx* c, double ethr, int nranks, cudaStream_t st) {
+  tf_items_host(c->nall, c->h_er.data(), ethr, c->tf_items, nranks);
   c->tf_items_ethr = ethr;
+  c->tf_items_nranks = nranks;
   const size_t n = c->tf_items.size();
   if (n > c->cap_tf_items) {
     cudaFree(c->d_tf_items); c->d_tf_items = nullptr; c->cap_tf_items = 0;
@@ -717,7 +721,8 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
   if (c->use_tf32 && !want_mask && !d_rmat && a.g.debug != 1 && a.g.debug != 2) {
     // tensor-core screen + exact candidate pass; the FP64 column kernel follows as a conditional
     // launch that only runs if the candidate list overflowed (results are idempotent: atomicMax)
-    if (!(c->tf_items_ethr == thr->ethr) && upload_tf_items(c, thr->ethr, st)) return 1;
+    if (!(c->tf_items_ethr == thr->ethr && c->tf_items_nranks == nranks) &&
+        upload_tf_items(c, thr->ethr, nranks, st)) return 1;
     const long long Ttf = (long long)(c->tf_items.size() / 4);
     long long tb = 0, te = 0;
     crest_cuda_shard_range(Ttf, rank, nranks, &tb, &te);
