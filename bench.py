@@ -401,8 +401,8 @@ def run_ours(args):
         variant = {0: "pair_tile (DMMA row tiles)", 1: "pair_col (DMMA column sweep)",
                    2: "pair_tf32 (tcgen05 TF32 screen) + exact_cand (FP64 list)"}[info["variant"]]
         # dram__bytes_read.sum + dram__bytes_write.sum of pair_tf32_kernel<8>, one launch, from the
-        # committed ncu --set full capture of this command (profiles/r01_v11_pair_tf32_ncu_full_summary.txt)
-        traffic = (232066560 + 7250944 if (info["variant"] == 2 and args.workload == "C3" and
+        # committed ncu --set full capture of this command (profiles/r01_v13_pair_tf32_ncu_full_summary.txt)
+        traffic = (234556416 + 6808320 if (info["variant"] == 2 and args.workload == "C3" and
                                            args.nall is None and world == 1 and args.ethr > 1e8) else None)
         if info["variant"] == 2:
             peak = tf32_peak_tflops(torch, dev)
