@@ -7,10 +7,12 @@ CPU tests pin the oracle restatement against numpy (Kabsch-SVD RMSD, the closed 
 uniqueCore) and the host-only C-ABI walk against the oracle; GPU tests compare the CUDA path with
 the oracle through the C ABI.  Tolerance: RMSD 1e-6 A (north_star); integer outputs identical
 unless a reference RMSD lies within 1e-6 of a threshold (none in the seeded inputs: asserted)."""
+import os
+
 import numpy as np
 import pytest
 
-from conftest import has_gpu
+from conftest import GOLDEN, has_gpu
 from crest_b200 import synth
 
 gpu = pytest.mark.gpu
@@ -165,7 +167,34 @@ def test_compare_no_cpu_fallback(cuda_lib):
         cb.intraconf(x, np.ones(4, np.int32), [1], [2], ["c1"])
 
 
+def test_golden_f2_f3_reproduced_by_oracle(oracle):
+    g = np.load(os.path.join(GOLDEN, "f2_compare.npz"))
+    rmat = oracle.compare_blocks(g["xyz1"], g["b1"], g["e1"], g["xyz2"], g["b2"], g["e2"])
+    assert np.allclose(rmat, g["rmat"], rtol=0, atol=1e-12)
+    left, right = oracle.compare_correlate(g["en1"], g["en2"], g["rmat"], 0.125)
+    assert np.array_equal(left, g["left"]) and np.array_equal(right, g["right"])
+    g = np.load(os.path.join(GOLDEN, "f3_intraconf.npz"))
+    fac, ef = oracle.intraconf(g["xyz"], g["inc"], g["low"], g["nrot"], [str(s) for s in g["sym"]])
+    assert np.array_equal(fac, g["fac"]) and np.array_equal(ef, g["enantiofac"])
+    assert fac.max() > 1 and ef.max() == 2.0          # the fixture exercises both outputs
+
+
 # ------------------------------------------------------------------ GPU: parity through the C ABI
+@gpu
+def test_gpu_golden_f2_f3():
+    import crest_b200 as cb
+    g = np.load(os.path.join(GOLDEN, "f2_compare.npz"))
+    rmat = cb.compare_blocks(g["xyz1"], g["b1"], g["e1"], g["xyz2"], g["b2"], g["e2"])
+    assert np.abs(rmat - g["rmat"]).max() < TOL
+    assert not np.any(np.abs(g["rmat"] - 0.125) < TOL)
+    left, right = cb.compare_correlate(g["en1"], g["en2"], rmat, 0.125)
+    assert np.array_equal(left, g["left"]) and np.array_equal(right, g["right"])
+    g = np.load(os.path.join(GOLDEN, "f3_intraconf.npz"))
+    fac, ef = cb.intraconf(g["xyz"], g["inc"], g["low"], g["nrot"], [str(s) for s in g["sym"]])
+    assert np.array_equal(fac, g["fac"]) and np.array_equal(ef, g["enantiofac"])
+
+
+
 @gpu
 @pytest.mark.parametrize("n,nat,nheavy,seed", [(40, 17, 9, 11), (300, 50, 23, 12), (150, 100, 46, 13),
                                                 (33, 5, 5, 14)])
