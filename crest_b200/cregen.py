@@ -98,15 +98,16 @@ def band_tiles(er, ethr):
     return np.array(ti, np.int64), np.array(tj, np.int64), rowstart, jfirst[:nI]
 
 
-def tf32_items(er, ethr):
+def tf32_items(er, ethr, nranks=1):
     """Host-only: work list of the tensor-core screen kernel, (n,4) int32 rows
-    {I, g_begin, g_end, g_gate_end} (see include/crest_cuda.h)."""
+    {I, g_begin, g_end, g_gate_end} (see include/crest_cuda.h), as `nranks` ranks build it."""
     L = _lib.lib()
     er = np.ascontiguousarray(er, np.float64)
     n = C.c_longlong(0)
-    _lib.check(L.crest_cuda_tf32_items(len(er), _dp(er), float(ethr), None, 0, C.byref(n)))
+    _lib.check(L.crest_cuda_tf32_items_n(len(er), _dp(er), float(ethr), nranks, None, 0, C.byref(n)))
     items = np.zeros((max(n.value, 1), 4), np.int32)
-    _lib.check(L.crest_cuda_tf32_items(len(er), _dp(er), float(ethr), _ip(items), n.value, C.byref(n)))
+    _lib.check(L.crest_cuda_tf32_items_n(len(er), _dp(er), float(ethr), nranks, _ip(items), n.value,
+                                         C.byref(n)))
     return items[: n.value]
 
 

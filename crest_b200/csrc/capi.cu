@@ -368,17 +368,22 @@ int crest_cuda_band_tiles(int nall, const double* er, double ethr, long long* ro
   return 0;
 }
 
-int crest_cuda_tf32_items(int nall, const double* er, double ethr, int* items, long long cap,
-                          long long* nitems) {
-  if (nall < 0 || (!er && nall > 0) || !nitems) { set_error("bad argument"); return 1; }
+int crest_cuda_tf32_items_n(int nall, const double* er, double ethr, int nranks, int* items,
+                            long long cap, long long* nitems) {
+  if (nall < 0 || (!er && nall > 0) || !nitems || nranks < 1) { set_error("bad argument"); return 1; }
   std::vector<int> v;
-  tf_items_host(nall, er, ethr, v);
+  tf_items_host(nall, er, ethr, v, nranks);
   *nitems = (long long)(v.size() / 4);
   if (items) {
     if ((long long)v.size() > cap * 4) { set_error("items buffer too small"); return 1; }
     std::memcpy(items, v.data(), sizeof(int) * v.size());
   }
   return 0;
+}
+
+int crest_cuda_tf32_items(int nall, const double* er, double ethr, int* items, long long cap,
+                          long long* nitems) {
+  return crest_cuda_tf32_items_n(nall, er, ethr, 1, items, cap, nitems);
 }
 
 int crest_cuda_shard_range(long long ntiles, int rank, int nranks, long long* begin,

@@ -235,6 +235,10 @@ int crest_cuda_shard_range(long long ntiles, int rank, int nranks, long long* be
  * capacity of items in quadruples. */
 int crest_cuda_tf32_items(int nall, const double* er, double ethr, int* items, long long cap,
                           long long* nitems);
+/* The same list as `nranks` ranks sharing it build it: items are cut smaller so that every rank still
+ * has >= 16 items per CTA (rank r then takes crest_cuda_shard_range(nitems, r, nranks)). */
+int crest_cuda_tf32_items_n(int nall, const double* er, double ethr, int nranks, int* items,
+                            long long cap, long long* nitems);
 
 /* Developer knobs (same syntax as the CREST_CUDA_TUNE environment variable; NULL = defaults):
  * "notf32" forces the FP64 (DMMA) pair kernels, "tile" the row-tile kernel, "cap=<n>" the candidate

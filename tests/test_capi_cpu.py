@@ -124,6 +124,39 @@ def test_host_tf32_items(cuda_lib):
             assert len(items) >= 1
 
 
+def test_host_tf32_items_rank_sized(cuda_lib):
+    """The list `nranks` ranks build (smaller items, >= 16 per CTA and rank) covers the same pairs,
+    and the rank shards (crest_cuda_shard_range) partition it."""
+    from crest_b200 import cregen as cg
+    rng = np.random.default_rng(4)
+    n = 40000
+    er = np.sort(rng.uniform(0, 6.0, n)) / 627.50947428 - 50.0
+    base = cg.tf32_items(er, 1e9)
+
+    def area(items):
+        i1 = np.minimum(items[:, 0] * 128 + 128, n) - items[:, 0] * 128
+        return (i1.astype(np.int64) * (np.minimum(items[:, 2] * 16, n) - items[:, 1] * 16)).sum()
+
+    for nranks in (2, 3, 8):
+        items = cg.tf32_items(er, 1e9, nranks)
+        assert len(items) > len(base)                      # finer cut
+        assert area(items) == area(base)
+        # per i-tile the j-group ranges tile [g_begin, g_end) of the single-rank list without overlap
+        for I in (0, 7, n // 128 - 1):
+            def spans(lst):
+                r = lst[lst[:, 0] == I][:, 1:3]
+                return r[np.argsort(r[:, 0])]
+            a, b = spans(items), spans(base)
+            assert a[0, 0] == b[0, 0] and a[-1, 1] == b[-1, 1]
+            assert np.all(a[1:, 0] == a[:-1, 1])
+        got = []
+        for r in range(nranks):
+            b0, e0 = cg.shard_range(len(items), r, nranks)
+            got.append((b0, e0))
+        assert got[0][0] == 0 and got[-1][1] == len(items)
+        assert all(got[k][1] == got[k + 1][0] for k in range(nranks - 1))
+
+
 def test_argument_checks(cuda_lib):
     # NULL thresholds / bad sizes are rejected before any device work
     rc = cuda_lib.crest_cuda_cregen_dup(3, 2, None, None, None, None, 0, 1, None, None, None, None,
