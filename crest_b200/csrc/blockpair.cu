@@ -80,7 +80,7 @@ struct BpArgs {
 };
 
 template <int MODE>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)   // <= 128 registers: two CTAs per SM (ncu: 130 registers gave one)
 bp_pair_kernel(const BpArgs p, int ntj) {
   __shared__ __align__(16) double xs[kBK][3][kBT];
   __shared__ __align__(16) double ys[kBK][3][kBT];
