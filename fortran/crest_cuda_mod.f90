@@ -206,7 +206,7 @@ contains
     integer :: c,k
     do c = 1,nconf
       do k = 1,3
-        csym(k,c) = symsym(c) (k:k)
+        csym(k,c) = symsym(c)(k:k)
       end do
     end do
     rc = crest_cuda_intraconf(int(nat,c_int),int(nall,c_int),xyz,int(inc,c_int),int(nconf,c_int), &
