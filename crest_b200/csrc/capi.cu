@@ -146,6 +146,11 @@ struct crest_cuda_ctx {
   size_t cap_tf_items = 0;
   double tf_items_ethr = std::numeric_limits<double>::quiet_NaN();
   int tf_items_nranks = 0;     // the item size depends on the number of ranks sharing the list
+  // d_X padding (atom slots beyond the selection, rows beyond nall) is zeroed once per layout: pack
+  // rewrites every used slot of every live row on each call and nothing else writes d_X
+  bool X_zeroed = false;
+  PackLayout X_zero_L{};
+  int X_zero_nall = -1;
   int last_variant = 0;                // 0 row-tile DMMA, 1 column DMMA, 2 TF32 screen + exact list
 };
 
@@ -606,6 +611,7 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
     cudaFree(c->d_X); c->d_X = nullptr; c->cap_X = 0;
     CREST_CUDA_TRY(cudaMalloc(&c->d_X, sizeof(double) * nX));
     c->cap_X = nX;
+    c->X_zeroed = false;
   }
   if (c->use_tf32) {
     const size_t nx = (size_t)c->ntile * 128 * 3 * c->tf.kslab * c->tf.nslab;    // floats, same for Xa and Xb
@@ -666,7 +672,11 @@ int crest_cuda_ctx_pack(crest_cuda_ctx* c, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   CREST_CUDA_TRY(cudaSetDevice(c->device));
   // padding rows / atoms of X must be zero: they enter the MMA (atoms) or are masked (rows)
-  CREST_CUDA_TRY(cudaMemsetAsync(c->d_X, 0, sizeof(double) * c->L.total_doubles(), st));
+  if (!c->X_zeroed || std::memcmp(&c->L, &c->X_zero_L, sizeof(PackLayout)) != 0 ||
+      c->nall != c->X_zero_nall) {
+    CREST_CUDA_TRY(cudaMemsetAsync(c->d_X, 0, sizeof(double) * c->L.total_doubles(), st));
+    c->X_zeroed = true; c->X_zero_L = c->L; c->X_zero_nall = c->nall;
+  }
   CREST_CUDA_TRY(cudaMemsetAsync(c->d_dup, 0, sizeof(int) * (size_t)(c->nall ? c->nall : 1), st));
   CREST_CUDA_TRY(cudaMemsetAsync(c->d_npairs, 0, sizeof(unsigned long long), st));
   c->launches = 0;
