@@ -35,7 +35,7 @@ def parse():
     p.add_argument("--steps", type=int, default=20)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    p.add_argument("--workload", default="C3", choices=["C1", "C2", "C3", "C4", "C5"])
+    p.add_argument("--workload", default="C3", choices=["C1", "C2", "C3", "C4", "C5", "C3dense", "C3adv", "C4ext"])
     p.add_argument("--nall", type=int, default=None, help="override conformer count (debug)")
     p.add_argument("--ethr", type=float, default=1e9, help="kcal/mol; 1e9 = all pairs")
     p.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU-baseline sample time")
@@ -428,7 +428,8 @@ def run_ours(args):
             "kernels": {"variant": variant, "pair_stage_ms": pair_ms, "grid": info["grid"],
                         "smem": info["smem"], "items_this_rank": info["tiles_shard"],
                         "atoms_padded": info["A_padded"], "launches_per_step": info["launches"],
-                        "exact_candidates": info["candidates"], "overflow": info["overflow"]},
+                        "candidates": info["candidates"], "exact_evaluations": info["exact_evals"],
+                        "dense_items": info["dense_items"], "flags": info["flags"]},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                          "frac": achieved / peak, "traffic": traffic,
                          "fp64_tensor_peak": fp64_peak, "fp64_tensor_equiv": achieved / fp64_peak,

@@ -333,8 +333,8 @@ class CregenContext:
         buf = (C.c_longlong * 16)()
         _lib.check(self._L.crest_cuda_ctx_info(self._h, C.byref(thr), rank, nranks, buf))
         keys = ["tiles_shard", "tiles_total", "A", "A_padded", "grid", "smem", "launches",
-                "variant", "candidates", "overflow", "violations"]
-        return dict(zip(keys, list(buf)[:11]))
+                "variant", "candidates", "dense_items", "violations", "exact_evals", "flags"]
+        return dict(zip(keys, list(buf)[:13]))
 
     def download(self, want_xyz=False, stream=0):
         rot = np.zeros((max(self.nall, 1), 3))

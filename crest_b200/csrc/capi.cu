@@ -61,10 +61,13 @@ static void parse_tune(const char* e, Tune& t) {
   if (std::strstr(e, "nohalf")) t.no_half = 1;
   if (std::strstr(e, "notf32")) t.no_tf32 = 1;
   if (std::strstr(e, "seqgroup")) t.seq_group = 1;
+  if (std::strstr(e, "forcedense")) t.force_dense = 1;
+  if (std::strstr(e, "nodense")) t.no_dense = 1;
+  if (const char* q = std::strstr(e, "densebudget=")) if (std::sscanf(q + 12, "%d", &v) == 1) t.dense_budget = v;
+  if (const char* q = std::strstr(e, "maskmb=")) if (std::sscanf(q + 7, "%d", &v) == 1) t.mask_mb = v;
   if (const char* q = std::strstr(e, "packg=")) if (std::sscanf(q + 6, "%d", &v) == 1) t.pack_g = v;
   if (const char* q = std::strstr(e, "copythr=")) if (std::sscanf(q + 8, "%d", &v) == 1) t.copy_threads = v;
   if (const char* q = std::strstr(e, "groupcap=")) if (std::sscanf(q + 9, "%d", &v) == 1) t.group_cap = v;
-  if (const char* q = std::strstr(e, "cap=")) if (std::sscanf(q + 4, "%d", &v) == 1) t.cand_cap = v;
   if (const char* q = std::strstr(e, "chunk=")) if (std::sscanf(q + 6, "%d", &v) == 1) t.chunk = v;
   if (const char* q = std::strstr(e, "skew=")) if (std::sscanf(q + 5, "%d", &v) == 1) t.skew = v;
 }
@@ -245,9 +248,9 @@ void col_items_host(int n, const double* er, double ethr, std::vector<int>& item
 // gated pair by pair (cregen.f90:1275); the rest of the band needs no energies at all.  The list is
 // cut on a fixed grid of `chunk` groups and ordered segment-major so that concurrently running CTAs
 // stream the same j-groups (L2-resident) past different i-tiles.
-void tf_items_host(int n, const double* er, double ethr, std::vector<int>& items, int nranks = 1) {
+int tf_items_host(int n, const double* er, double ethr, std::vector<int>& items, int nranks = 1) {
   items.clear();
-  if (n < 2) return;
+  if (n < 2) return 8;
   const int ntile = (n + 127) / 128;
   std::vector<int> gb(ntile, 0), ge(ntile, 0), gg(ntile, 0);
   // first j in [0, i] with (er[i]-er[j])*autokcal < ethr; i+1 if none (monotone: er ascends)
@@ -273,8 +276,9 @@ void tf_items_host(int n, const double* er, double ethr, std::vector<int>& items
   // >= 16 items per CTA and rank: the CTAs of a rank take its items round-robin, so the stage lasts
   // ceil(items / 148) items (measured on C3: 128-group items cost nothing against 256, 64 cost 1.3 %)
   long long chunk = tune().chunk > 0 ? tune().chunk : total / (148LL * 16 * (nranks > 0 ? nranks : 1));
+  chunk = chunk / 8 * 8;       // segments are whole 128-column blocks of the candidate bitmask
   if (chunk < 8) chunk = 8;
-  if (chunk > 256 && tune().chunk <= 0) chunk = 256;
+  if (chunk > 256) chunk = 256;
   const int ngroup = ntile * 8;
   const int nseg = (int)((ngroup + chunk - 1) / chunk);
   for (int sg = 0; sg < nseg; ++sg) {
@@ -284,20 +288,40 @@ void tf_items_host(int n, const double* er, double ethr, std::vector<int>& items
       if (b < e) { items.push_back(I); items.push_back(b); items.push_back(e); items.push_back(gg[I]); }
     }
   }
+  return (int)chunk;
 }
 
 int upload_tf_items(crest_cuda_ctx* c, double ethr, int nranks, cudaStream_t st) {
-  tf_items_host(c->nall, c->h_er.data(), ethr, c->tf_items, nranks);
+  c->tf.chunk = tf_items_host(c->nall, c->h_er.data(), ethr, c->tf_items, nranks);
   c->tf_items_ethr = ethr;
   c->tf_items_nranks = nranks;
   const size_t n = c->tf_items.size();
   if (n > c->cap_tf_items) {
     cudaFree(c->d_tf_items); c->d_tf_items = nullptr; c->cap_tf_items = 0;
+    cudaFree(c->tf.item_cnt); c->tf.item_cnt = nullptr;
     CREST_CUDA_TRY(cudaMalloc(&c->d_tf_items, sizeof(int) * n));
+    CREST_CUDA_TRY(cudaMalloc(&c->tf.item_cnt, sizeof(unsigned) * (n / 4)));
+    CREST_CUDA_TRY(cudaMemsetAsync(c->tf.item_cnt, 0, sizeof(unsigned) * (n / 4), st));
     c->cap_tf_items = n;
   }
   if (n) CREST_CUDA_TRY(cudaMemcpyAsync(c->d_tf_items, c->tf_items.data(), sizeof(int) * n,
                                         cudaMemcpyHostToDevice, st));
+  // verdict per (segment, i-tile) and the work list of the FP64 tensor kernel for dense items
+  const size_t nseg = ((size_t)c->ntile * 8 + c->tf.chunk - 1) / c->tf.chunk;
+  const size_t nd = nseg * (size_t)c->ntile;
+  if (nd > c->tf.dense_cap) {
+    cudaFree(c->tf.dense); c->tf.dense = nullptr; c->tf.dense_cap = 0;
+    CREST_CUDA_TRY(cudaMalloc(&c->tf.dense, nd));
+    c->tf.dense_cap = nd;
+  }
+  const size_t per_item = (size_t)(c->tf.chunk / 4 + 1) * (c->use_col ? 8 : 4);
+  size_t want = std::min<size_t>((n / 4) * per_item, (size_t)32 << 20);
+  if (want < 1024) want = 1024;
+  if (want > c->tf.dense_items_cap) {
+    cudaFree(c->tf.dense_items); c->tf.dense_items = nullptr; c->tf.dense_items_cap = 0;
+    CREST_CUDA_TRY(cudaMalloc(&c->tf.dense_items, sizeof(int4) * want));
+    c->tf.dense_items_cap = (unsigned)want;
+  }
   return 0;
 }
 
@@ -436,7 +460,8 @@ void crest_cuda_ctx_destroy(crest_cuda_ctx* c) {
   cudaFree(c->d_er); cudaFree(c->d_rot); cudaFree(c->d_aniso); cudaFree(c->d_X); cudaFree(c->d_xn);
   cudaFree(c->d_dup); cudaFree(c->d_npairs); cudaFree(c->d_rowstart); cudaFree(c->d_jfirst); cudaFree(c->d_items);
   cudaFree(c->d_mask); cudaFree(c->d_rmat);
-  cudaFree(c->tf.Xa); cudaFree(c->tf.Xb); cudaFree(c->tf.hn); cudaFree(c->tf.cand);
+  cudaFree(c->tf.Xa); cudaFree(c->tf.Xb); cudaFree(c->tf.hn); cudaFree(c->tf.cmask); cudaFree(c->tf.fmask);
+  cudaFree(c->tf.item_cnt); cudaFree(c->tf.dense); cudaFree(c->tf.dense_items); cudaFree(c->tf.unfinished);
   cudaFree(c->tf.cand_count); cudaFree(c->d_npairs_scratch); cudaFree(c->d_tf_items);
   delete c;
 }
@@ -628,19 +653,32 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
       c->cap_tf_hn = nh;
     }
     if (!c->tf.cand_count) {
-      CREST_CUDA_TRY(cudaMalloc(&c->tf.cand_count, sizeof(unsigned) * 8));   // [4] = converter's unsafe flag
+      CREST_CUDA_TRY(cudaMalloc(&c->tf.cand_count, sizeof(unsigned) * 8));   // counters, see Tf32Buffers
       CREST_CUDA_TRY(cudaMemset(c->tf.cand_count, 0, sizeof(unsigned) * 8));
       CREST_CUDA_TRY(cudaMalloc(&c->d_npairs_scratch, sizeof(unsigned long long)));
     }
-    // candidate list: duplicates + near-threshold pairs; sized for 64 per conformer (min 1M,
-    // max 32M entries); an overflow re-runs the launch on the FP64 column kernel
-    size_t want = tune().cand_cap > 0 ? (size_t)tune().cand_cap
-                                      : std::min<size_t>(std::max<size_t>((size_t)nall * 64, 1u << 20), 32u << 20);
-    if (want > c->tf.cand_cap || (tune().cand_cap > 0 && want != c->tf.cand_cap)) {
-      cudaFree(c->tf.cand); c->tf.cand = nullptr; c->tf.cand_cap = 0;
-      CREST_CUDA_TRY(cudaMalloc(&c->tf.cand, sizeof(int) * 2 * want));
-      c->tf.cand_cap = (unsigned)want;
+    // candidate bitmask (pair_tf32.cu): one pass over all columns if that fits the budget (default
+    // 2 GB, CREST_CUDA_TUNE maskmb=<MB>), else passes of whole segments; never less than one segment
+    // of 4096 columns.  Zeroed once: cand_scan_kernel clears what the screen sets.
+    {
+      const size_t full = tf32_mask_words(nall, 0, nall);
+      const size_t budget = ((size_t)(tune().mask_mb > 0 ? tune().mask_mb : 2048) << 20) / sizeof(unsigned);
+      const size_t one_seg = (size_t)nall * 128;
+      const size_t want = std::max<size_t>(std::min(full, std::max(budget, one_seg)), 128);
+      if (want > c->tf.cm_words || (tune().mask_mb > 0 && want != c->tf.cm_words)) {
+        cudaFree(c->tf.cmask); cudaFree(c->tf.fmask);
+        c->tf.cmask = c->tf.fmask = nullptr; c->tf.cm_words = 0;
+        CREST_CUDA_TRY(cudaMalloc(&c->tf.cmask, sizeof(unsigned) * want));
+        CREST_CUDA_TRY(cudaMemset(c->tf.cmask, 0, sizeof(unsigned) * want));
+        c->tf.cm_words = want;
+      }
     }
+    if ((size_t)nall > c->tf.unfinished_cap) {
+      cudaFree(c->tf.unfinished); c->tf.unfinished = nullptr; c->tf.unfinished_cap = 0;
+      CREST_CUDA_TRY(cudaMalloc(&c->tf.unfinished, (size_t)nall));
+      c->tf.unfinished_cap = nall;
+    }
+    c->tf.kappa = tf32_kappa(c->tf.kslab * c->tf.nslab);
   }
   CREST_CUDA_TRY(cudaMemcpy(c->d_at, at, sizeof(int) * nat, cudaMemcpyHostToDevice));
   CREST_CUDA_TRY(cudaMemcpy(c->d_sel, sel.data(), sizeof(int) * sel.size(), cudaMemcpyHostToDevice));
@@ -685,8 +723,8 @@ int crest_cuda_ctx_pack(crest_cuda_ctx* c, void* stream) {
     return 1;
   if (c->nall > 0) c->launches += 1;
   if (c->use_tf32) {
-    if (launch_tf32_convert(c->d_X, c->d_xn, c->nall, c->L, c->ntile, c->tf.nslab, c->tf.kslab, c->tf.Xa,
-                            c->tf.Xb, c->tf.hn, c->tf.cand_count + 4, st))
+    if (launch_tf32_convert(c->d_X, c->d_xn, c->nall, c->L, c->ntile, c->tf.nslab, c->tf.kslab, c->tf.kappa,
+                            c->tf.Xa, c->tf.Xb, c->tf.hn, c->tf.cand_count + 4, st))
       return 1;
     c->launches += 1;
   }
@@ -699,6 +737,40 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
   if (nranks < 1 || rank < 0 || rank >= nranks) { set_error("bad shard %d/%d", rank, nranks); return 1; }
   CREST_CUDA_TRY(cudaSetDevice(c->device));
   if (c->nall < 2) return 0;
+  PairArgs a{};
+  a.X = c->d_X; a.xn = c->d_xn; a.er = c->d_er; a.rot = c->d_rot; a.aniso = c->d_aniso;
+  a.nall = c->nall;
+  a.dup = c->d_dup; a.npairs = c->d_npairs;
+  a.mask = nullptr; a.n8 = (c->nall + 7) / 8;
+  a.rmat = d_rmat;
+  a.g = make_gates(*thr, enantio, c->nsel);
+  a.L = c->L;
+  a.dbg = nullptr;
+  a.work_count = nullptr; a.tiles = nullptr;
+  const bool tf32_path = c->use_tf32 && !want_mask && !d_rmat && a.g.debug != 1 && a.g.debug != 2;
+  if (tf32_path) {
+    // tensor-core screen -> per-item verdict -> FP64 tensor kernel on dense items -> top-down exact
+    // scan of the candidate bitmask (pair_tf32.cu), pass by pass over this rank's slice of the list
+    if (!(c->tf_items_ethr == thr->ethr && c->tf_items_nranks == nranks) &&
+        upload_tf_items(c, thr->ethr, nranks, st)) return 1;
+    const long long Ttf = (long long)(c->tf_items.size() / 4);
+    long long tb = 0, te = 0;
+    crest_cuda_shard_range(Ttf, rank, nranks, &tb, &te);
+    CREST_CUDA_TRY(cudaMemsetAsync(c->tf.cand_count, 0, sizeof(unsigned) * 4, st));
+    CREST_CUDA_TRY(cudaMemsetAsync(c->tf.cand_count + 5, 0, sizeof(unsigned) * 3, st));
+    if (a.g.debug == 3 && !c->tf.fmask) {
+      CREST_CUDA_TRY(cudaMalloc(&c->tf.fmask, sizeof(unsigned) * c->tf.cm_words));
+    }
+    PairArgs fb = a;
+    fb.npairs = c->d_npairs_scratch;      // the screen already counted these pairs
+    int nsf = 0;
+    if (!c->use_col) pair_smem_bytes(c->L, &nsf);
+    if (launch_pair_tf32(a, fb, c->tf, c->d_tf_items, c->tf_items.data(), (int)tb, (int)te,
+                         a.g.debug == 3, nsf, st, &c->last_grid, &c->last_smem, &c->launches))
+      return 1;
+    c->last_variant = 2;
+    return 0;
+  }
   if (c->use_col) {
     if (!(c->items_ethr == thr->ethr) && upload_items(c, thr->ethr, st)) return 1;
   } else if (!(c->tiles_ethr == thr->ethr)) {
@@ -706,13 +778,9 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
     if (upload_tiles(c, st)) return 1;
   }
   const long long T = c->use_col ? (long long)(c->items.size() / 4) : c->rowstart.back();
-  PairArgs a{};
-  a.X = c->d_X; a.xn = c->d_xn; a.er = c->d_er; a.rot = c->d_rot; a.aniso = c->d_aniso;
   a.rowstart = c->d_rowstart; a.jfirst = c->d_jfirst;
-  a.nI = (int)c->jfirst.size(); a.nall = c->nall;
+  a.nI = (int)c->jfirst.size();
   crest_cuda_shard_range(T, rank, nranks, &a.tile_begin, &a.tile_end);
-  a.dup = c->d_dup; a.npairs = c->d_npairs;
-  a.mask = nullptr; a.n8 = (c->nall + 7) / 8;
   if (want_mask) {
     const size_t need = (size_t)a.n8 * a.n8;
     if (need > c->cap_mask) {
@@ -723,47 +791,11 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
     CREST_CUDA_TRY(cudaMemsetAsync(c->d_mask, 0, sizeof(unsigned long long) * need, st));
     a.mask = c->d_mask;
   }
-  a.rmat = d_rmat;
-  a.g = make_gates(*thr, enantio, c->nsel);
-  a.L = c->L;
-  a.dbg = nullptr;
   if (a.g.debug == 2) {
     CREST_CUDA_TRY(cudaMalloc(&a.dbg, sizeof(long long) * 32));
     CREST_CUDA_TRY(cudaMemsetAsync(a.dbg, 0, sizeof(long long) * 32, st));
   }
   int ns = 0;
-  a.run_if = nullptr;
-  if (c->use_tf32 && !want_mask && !d_rmat && a.g.debug != 1 && a.g.debug != 2) {
-    // tensor-core screen + exact candidate pass; the FP64 column kernel follows as a conditional
-    // launch that only runs if the candidate list overflowed (results are idempotent: atomicMax)
-    if (!(c->tf_items_ethr == thr->ethr && c->tf_items_nranks == nranks) &&
-        upload_tf_items(c, thr->ethr, nranks, st)) return 1;
-    const long long Ttf = (long long)(c->tf_items.size() / 4);
-    long long tb = 0, te = 0;
-    crest_cuda_shard_range(Ttf, rank, nranks, &tb, &te);
-    CREST_CUDA_TRY(cudaMemsetAsync(c->tf.cand_count, 0, sizeof(unsigned) * 4, st));
-    if (launch_pair_tf32(a, c->tf, c->d_tf_items, (int)tb, (int)te, a.g.debug == 3, st,
-                         &c->last_grid, &c->last_smem))
-      return 1;
-    if (c->last_grid > 0) c->launches += 2;
-    PairArgs fb = a;
-    fb.run_if = c->tf.cand_count + 1;
-    fb.npairs = c->d_npairs_scratch;
-    // the fallback covers the WHOLE triangle on this rank: the tf32 and column work lists shard
-    // the pair space differently, so a per-shard re-run would leave holes in a multi-rank job
-    int g2 = 0, s2 = 0;
-    if (c->use_col) {
-      if (launch_pair_cols(fb, c->d_items, 0, (int)(c->items.size() / 4), st, &g2, &s2)) return 1;
-    } else {
-      int nsf = 0;
-      pair_smem_bytes(c->L, &nsf);
-      fb.tile_begin = 0; fb.tile_end = c->rowstart.back();
-      if (launch_pair_tiles(fb, nsf, st, &g2, &s2)) return 1;
-    }
-    if (g2 > 0) c->launches += 1;
-    c->last_variant = 2;
-    return 0;
-  }
   c->last_variant = c->use_col ? 1 : 0;
   if (c->use_col) {
     if (launch_pair_cols(a, c->d_items, (int)a.tile_begin, (int)a.tile_end, st, &c->last_grid,
@@ -829,7 +861,9 @@ int crest_cuda_ctx_info(crest_cuda_ctx* c, const crest_cuda_thresholds* thr, int
   if (!c || !info) { set_error("NULL argument"); return 1; }
   if (check_thr(thr)) return 1;
   if (nranks < 1 || rank < 0 || rank >= nranks) { set_error("bad shard %d/%d", rank, nranks); return 1; }
-  if (c->nall >= 2 && c->use_col) {
+  if (c->last_variant == 2) {
+    // work list of the tensor-core screen: built by ctx_pairs
+  } else if (c->nall >= 2 && c->use_col) {
     if (!(c->items_ethr == thr->ethr)) {
       CREST_CUDA_TRY(cudaSetDevice(c->device));
       if (upload_items(c, thr->ethr, 0)) return 1;
@@ -847,13 +881,13 @@ int crest_cuda_ctx_info(crest_cuda_ctx* c, const crest_cuda_thresholds* thr, int
   long long tb = 0, te = 0;
   crest_cuda_shard_range(T, rank, nranks, &tb, &te);
   info[7] = c->last_variant;
-  info[8] = info[9] = info[10] = 0;
+  info[8] = info[9] = info[10] = info[11] = info[12] = 0;
   if (c->last_variant == 2 && c->tf.cand_count) {
-    unsigned h[4] = {0, 0, 0, 0};
+    unsigned h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     CREST_CUDA_TRY(cudaSetDevice(c->device));
     CREST_CUDA_TRY(cudaDeviceSynchronize());
     CREST_CUDA_TRY(cudaMemcpy(h, c->tf.cand_count, sizeof(h), cudaMemcpyDeviceToHost));
-    info[8] = h[0]; info[9] = h[1]; info[10] = h[2];
+    info[8] = h[3]; info[9] = h[5]; info[10] = h[2]; info[11] = h[0]; info[12] = h[1] | (h[7] << 1);
   }
   info[0] = te - tb;
   info[1] = T;

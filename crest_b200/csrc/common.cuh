@@ -33,7 +33,7 @@ struct PackLayout {
 
 // Developer knobs (env CREST_CUDA_TUNE="slab=<8-atom blocks per slab>,stages=<n>,dist=<n>,skew=<clk>"),
 // read once; 0 = automatic.  Used to A/B the pipeline shape on the GPU box without rebuilding.
-struct Tune { int slab_blocks = 0, stages = 0, dist = 0, skew = -1, force_tile = 0, no_half = 0, no_tf32 = 0, cand_cap = 0, chunk = 0, seq_group = 0, group_cap = 0, copy_threads = -1, pack_g = 0; };
+struct Tune { int force_dense = 0, no_dense = 0, mask_mb = 0, dense_budget = 0, slab_blocks = 0, stages = 0, dist = 0, skew = -1, force_tile = 0, no_half = 0, no_tf32 = 0, cand_cap = 0, chunk = 0, seq_group = 0, group_cap = 0, copy_threads = -1, pack_g = 0; };
 const Tune& tune();
 void set_tune(const char* spec);   // re-parse the knobs (tests A/B kernel variants in one process)
 
@@ -138,8 +138,11 @@ struct PairArgs {
   int dist;              // producer runs `dist` ring items ahead of warp 0
   int skew_clk;          // start delay of warps 4-7 (half a tile), 0 = none
   long long* dbg;        // CREST_CUDA_DEBUG=2: per-warp cycle counters [8 warps][4 phases]
-  const unsigned* run_if; // column kernel only: if non-NULL the kernel runs only when *run_if != 0
-                          // (FP64 fallback behind the tensor-core screen's candidate-list overflow)
+  // Device-generated work (dense items behind the tensor-core screen, pair_tf32.cu classify_items_kernel):
+  // if non-NULL the kernel takes its item / tile COUNT from *work_count (items start at item_begin /
+  // tile_begin = 0) and, in the row-tile kernel, the tiles themselves from `tiles` {panel, j-tile, -, -}.
+  const unsigned* work_count;
+  const int4* tiles;
 };
 int launch_pair_tiles(const PairArgs& a, int nstage, cudaStream_t stream, int* grid_out,
                       int* smem_out);
@@ -149,25 +152,40 @@ int launch_pair_cols(const PairArgs& a, const void* d_items, int item_begin, int
                      cudaStream_t stream, int* grid_out, int* smem_out);
 int col_smem_bytes(int KS, int* nstage_out);
 // tensor-core screen (pair_tf32.cu): TF32 operand copies, screen norms and the candidate list
-constexpr double kTfKappa = 1.8e-3;   // lam_test = (1-kappa) s/2 - E2/2 (error budget: pair_tf32.cu header)
 struct Tf32Buffers {
   float* Xa = nullptr;        // [tile][comp][chunk][128][4]  A operands (i-tiles of 128 conformers)
   float* Xb = nullptr;        // [group][chunk][48][4]        B operands (j-groups of 16 conformers)
   float* hn = nullptr;        // [ntile*128] rd(0.5*|x|^2*(1-kappa))
-  void* cand = nullptr;       // int2[cand_cap] candidate pairs (i, j)
-  unsigned cand_cap = 0;
-  unsigned* cand_count = nullptr;   // [0] appended, [1] overflow, [2] debug violations, [3] spare
+  unsigned* cmask = nullptr;  // candidate bitmask of one pass (rows x columns of the pass), all-zero between launches
+  unsigned* fmask = nullptr;  // self-check only (CREST_CUDA_DEBUG=3): the screen's "far" verdicts
+  size_t cm_words = 0;        // capacity of cmask (and fmask) in 32-bit words
+  unsigned* item_cnt = nullptr;     // candidates per work item, zero between launches
+  unsigned char* dense = nullptr;   // [segment][i-tile] verdict of classify_items_kernel
+  unsigned char* unfinished = nullptr;  // [row] rows that gave up inside a dense item (cand_scan_kernel)
+  size_t unfinished_cap = 0;
+  size_t dense_cap = 0;
+  int4* dense_items = nullptr;      // work list of the FP64 tensor kernel for dense items
+  unsigned dense_items_cap = 0;
+  unsigned* cand_count = nullptr;   // [0] exact evaluations, [1] unsafe magnitudes, [2] debug violations, [3] candidates, [4] converter flag, [5] dense items, [6] dense list length, [7] dense list overflow
+  int chunk = 0;              // j-groups per segment of the work list (multiple of 8)
+  double kappa = 0.0;         // relative lowering of the screen's test point (error budget of this atom count)
   int nslab = 1;              // TF32 K slabs (1 for A <= 88; slabs of 48 slots for the row-tile layout)
   int kslab = 0;              // atom slots per slab (multiple of 8)
 };
 constexpr int kTfSlabSlots = 48;
 int tf32_smem_bytes(int KU, int* nbstage_out);
 int launch_tf32_convert(const double* d_X, const double* d_xn, int nall, const PackLayout& L,
-                        int ntile, int nslab_t, int kslab, float* d_Xa, float* d_Xb, float* d_hn,
-                        unsigned* d_unsafe, cudaStream_t stream);
+                        int ntile, int nslab_t, int kslab, double kappa, float* d_Xa, float* d_Xb,
+                        float* d_hn, unsigned* d_unsafe, cudaStream_t stream);
+double tf32_kappa(int kslots);
 // items = device array of {I, g_begin, g_end, g_gate_end} int quadruples
-int launch_pair_tf32(const PairArgs& a, const Tf32Buffers& tb, const void* d_items, int item_begin,
-                     int item_end, int all_cand, cudaStream_t stream, int* grid_out, int* smem_out);
+// h_items = host copy of the list (the launcher cuts [item_begin, item_end) into passes of whole
+// segments whose candidate bitmask fits tb.cm_words); fb = arguments of the FP64 tensor kernel that
+// re-does dense items (its own pair counter); launches_out += kernels launched
+int launch_pair_tf32(const PairArgs& a, const PairArgs& fb, const Tf32Buffers& tb, const void* d_items,
+                     const int* h_items, int item_begin, int item_end, int all_cand, int nstage_tile,
+                     cudaStream_t stream, int* grid_out, int* smem_out, long long* launches_out);
+size_t tf32_mask_words(int nall, int col0, int col_end);
 int launch_backtrack(int nall, int* d_dup, cudaStream_t stream);
 int launch_rmsd_pairs(int A, int n, const double* d_packed, long long npairs, const int* d_i,
                       const int* d_j, double* d_rmsd, double* d_rmsd_m, cudaStream_t stream);

@@ -136,7 +136,8 @@ struct ColArgs {
   Gates g;
   int A, KS, nstage;
   long long* dbg;        // make PROF=1 + CREST_CUDA_DEBUG=2: per-warp cycle counters
-  const unsigned* run_if; // non-NULL: run only if *run_if != 0 (fallback behind the TF32 screen)
+  const unsigned* work_count; // non-NULL: items [item_begin, item_begin + *work_count) written by the
+                              // device (dense items behind the tensor-core screen)
 };
 
 // Per-warp constants of the kernel, bundled so the two ping-pong call sites stay short.
@@ -249,7 +250,8 @@ __device__ __forceinline__ void unit_meta(const ColArgs& a, const ColWarp& w, in
 template <int NKB, bool HALF, bool SCREEN>
 __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* smem_raw,
                                               uint64_t* full_bar, uint64_t* empty_bar,
-                                              uint64_t& jfull_bar, uint64_t& jempty_bar) {
+                                              uint64_t& jfull_bar, uint64_t& jempty_bar,
+                                              const int item_end) {
   const int warp = threadIdx.x >> 5;
   const int nstage = a.nstage;
   const int KS = a.KS;
@@ -272,9 +274,9 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
   const bool is_producer = (threadIdx.x == 0);
   int pk = a.item_begin + blockIdx.x, pu = 0, pu_end = 0;
   uint32_t p_it = 0;
-  if (is_producer && pk < a.item_end) { pu = a.items[pk].u_begin; pu_end = a.items[pk].u_end; }
+  if (is_producer && pk < item_end) { pu = a.items[pk].u_begin; pu_end = a.items[pk].u_end; }
   auto produce_one = [&]() {
-    if (pk >= a.item_end) return;
+    if (pk >= item_end) return;
     const int st = p_it % nstage;
     const uint32_t ph = (p_it / nstage) & 1;
     mbar_wait(&empty_bar[st], ph ^ 1);
@@ -284,7 +286,7 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
     ++p_it;
     if (++pu == pu_end) {
       pk += gridDim.x;
-      if (pk < a.item_end) { pu = a.items[pk].u_begin; pu_end = a.items[pk].u_end; }
+      if (pk < item_end) { pu = a.items[pk].u_begin; pu_end = a.items[pk].u_end; }
     }
   };
   if (is_producer)
@@ -303,7 +305,7 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
       if (w.lane == 0) mbar_arrive(&jempty_bar);
     }
     k += gridDim.x;
-    if (k >= a.item_end) return false;
+    if (k >= item_end) return false;
     const ColItem item = a.items[k];
     J = item.J; u = item.u_begin; u_end = item.u_end; item_edge = item.edge;
 #pragma unroll
@@ -410,7 +412,8 @@ pair_col_kernel(const ColArgs a) {
   __shared__ __align__(8) uint64_t full_bar[kColStagesMax];
   __shared__ __align__(8) uint64_t empty_bar[kColStagesMax];
   __shared__ __align__(8) uint64_t jfull_bar, jempty_bar;
-  if (a.run_if && *a.run_if == 0u) return;
+  const int item_end = a.work_count ? a.item_begin + (int)*a.work_count : a.item_end;
+  if (a.item_begin + (int)blockIdx.x >= item_end) return;
   if (threadIdx.x == 0) {
     for (int s = 0; s < a.nstage; ++s) {
       mbar_init(&full_bar[s], 1);
@@ -421,7 +424,7 @@ pair_col_kernel(const ColArgs a) {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  pair_col_body<NKB, HALF, SCREEN>(a, smem_raw, full_bar, empty_bar, jfull_bar, jempty_bar);
+  pair_col_body<NKB, HALF, SCREEN>(a, smem_raw, full_bar, empty_bar, jfull_bar, jempty_bar, item_end);
 }
 
 int col_smem_bytes(int KS, int* nstage_out) {
@@ -455,14 +458,14 @@ static int launch_col_nkb(const ColArgs& a, int half, int grid, int smem, cudaSt
 int launch_pair_cols(const PairArgs& pa, const void* d_items, int item_begin, int item_end,
                      cudaStream_t stream, int* grid_out, int* smem_out) {
   if (grid_out) *grid_out = 0;
-  const int nitems = item_end - item_begin;
+  const int nitems = pa.work_count ? (1 << 30) : item_end - item_begin;
   if (nitems <= 0) return 0;
   ColArgs a{};
   a.X = pa.X; a.xn = pa.xn; a.er = pa.er; a.rot = pa.rot; a.aniso = pa.aniso;
   a.items = static_cast<const ColItem*>(d_items);
   a.item_begin = item_begin; a.item_end = item_end;
   a.nall = pa.nall; a.dup = pa.dup; a.npairs = pa.npairs; a.mask = pa.mask; a.n8 = pa.n8;
-  a.rmat = pa.rmat; a.g = pa.g; a.A = pa.L.A; a.KS = pa.L.KS; a.dbg = pa.dbg; a.run_if = pa.run_if;
+  a.rmat = pa.rmat; a.g = pa.g; a.A = pa.L.A; a.KS = pa.L.KS; a.dbg = pa.dbg; a.work_count = pa.work_count;
   int ns = 0;
   const int smem = col_smem_bytes(a.KS, &ns);
   a.nstage = ns;

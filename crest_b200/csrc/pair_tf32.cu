@@ -38,6 +38,8 @@
 #include "common.cuh"
 #include "qcp.cuh"
 #include "pipe.cuh"
+#include <algorithm>
+#include <cmath>
 
 namespace crest {
 
@@ -148,10 +150,16 @@ struct TfArgs {
   double ethr;
   int enantio;
   int dbg;                // timing experiments (CREST_CUDA_DEBUG=4: no screen arithmetic, 5: no MMAs, 6: neither)
-  int all_cand;           // debug: every pair goes to the exact kernel, bit 31 of j = screen said far
-  int2* cand;             // candidate list
-  unsigned cand_cap;
-  unsigned* cand_count;   // [0] = appended, [1] = overflow flag, [2] = screen violations (debug), [4] = converter: unsafe magnitudes
+  int all_cand;           // debug: every pair is a candidate, fmask bit = screen said far
+  // candidate bitmask of this pass: bit (j - cm_col0) of row (i - cm_row0), row stride
+  // cm_stride 32-bit words; written with red.or, read top-down and cleared by cand_scan_kernel
+  unsigned* cmask;
+  unsigned* fmask;        // debug (all_cand): same geometry, bit set = the screen called the pair far
+  int cm_row0, cm_col0;
+  long long cm_stride;
+  const int* dup;         // current links (1-based parent or 0): candidates below them are never needed
+  unsigned* item_cnt;     // candidates emitted per work item (classify_items_kernel reads + clears)
+  unsigned* cand_count;   // [0] exact evaluations, [1] converter "unsafe magnitudes" seen by the launch, [2] screen violations (debug), [3] candidates emitted, [4] converter flag, [5] dense items
   unsigned long long* npairs;
 };
 
@@ -165,7 +173,8 @@ struct TfArgs {
 template <bool DBG>
 __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v)[9][4], const float* hnp,
                                              int j0, int i, bool iok, f2_t hic2, bool rowfast,
-                                             bool gate, bool slow, unsigned long long& my_pairs) {
+                                             bool gate, bool slow, int dupi,
+                                             unsigned long long& my_pairs, unsigned& my_cand) {
   const float4 h0 = __ldg(reinterpret_cast<const float4*>(hnp));
   const float hj[4] = {h0.x, h0.y, h0.z, h0.w};
   uint32_t sg[4];                        // sign bit set = not proven far
@@ -215,18 +224,14 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
     cand &= ok;
   }
   if (cand) {
-#pragma unroll 1
-    for (int p = 0; p < 4; ++p) {
-      if (!((cand >> p) & 1u)) continue;
-      const unsigned idx = atomicAdd(a.cand_count, 1u);
-      if (idx < a.cand_cap) {
-        int jj = j0 + p;
-        if (DBG && a.all_cand && ((farbits >> p) & 1u)) jj |= (int)0x80000000u;
-        a.cand[idx] = make_int2(i, jj);
-      } else {
-        a.cand_count[1] = 1u;
-      }
-    }
+    // the reference keeps the LARGEST matching j (cregen.f90:1353-1373): nothing at or below the link
+    // this row already has can change it
+    if (!(DBG && a.all_cand) && j0 + 3 < dupi) return;
+    const int rel = j0 - a.cm_col0;
+    const size_t w = (size_t)(i - a.cm_row0) * (size_t)a.cm_stride + (size_t)(rel >> 5);
+    atomicOr(a.cmask + w, cand << (rel & 31));
+    if (DBG && a.all_cand && farbits) atomicOr(a.fmask + w, (farbits & cand) << (rel & 31));
+    my_cand += __popc(cand);
   }
 }
 
@@ -237,8 +242,11 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
 template <int NST, bool DBG>
 __device__ __forceinline__ void epilogue_groups(const TfArgs& a, const TfItem& item, int i, bool iok, int sq, int lane,
                                                 uint32_t lane_base, uint32_t dfull0, uint32_t dempty0,
-                                                uint32_t& t, uint32_t& ph, unsigned long long& my_pairs) {
+                                                uint32_t& t, uint32_t& ph, unsigned long long& my_pairs,
+                                                int item_index) {
   const float hic = __fadd_rd(a.hn[i], a.cE);
+  const int dupi = iok ? a.dup[i] : 0;
+  unsigned my_cand = 0;
   const f2_t hic2 = f2_pack(hic, hic);
   const bool rowfast = iok && hic > 0.0f;
   const float* hnp = a.hn + item.g_begin * 16 + sq * 4;
@@ -257,9 +265,13 @@ __device__ __forceinline__ void epilogue_groups(const TfArgs& a, const TfItem& i
     tc_fence_before();
     __syncwarp();
     if (elect_one()) mbar_arrive_a(dempty0 + 8u * t);    // this warp's 4 pairs are in registers
-    screen_batch<DBG>(a, v, hnp, j0, i, iok, hic2, rowfast, gate, slow, my_pairs);
+    screen_batch<DBG>(a, v, hnp, j0, i, iok, hic2, rowfast, gate, slow, dupi, my_pairs, my_cand);
     if (NST == 2) { ph ^= t; t ^= 1u; }
     else if (++t == (uint32_t)NST) { t = 0; ph ^= 1u; }
+  }
+  if (__any_sync(0xffffffffu, my_cand != 0)) {
+    const unsigned c = __reduce_add_sync(0xffffffffu, my_cand);
+    if (lane == 0) atomicAdd(a.item_cnt + item_index, c);
   }
 }
 
@@ -409,7 +421,7 @@ pair_tf32_kernel(const TfArgs a) {
         __syncwarp();
         if (lane == 0) { mbar_arrive(&at_full); mbar_arrive(&a_empty); }
       }
-      epilogue_groups<kTfDStages, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, my_pairs);
+      epilogue_groups<kTfDStages, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, my_pairs, k);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) my_pairs += __shfl_xor_sync(0xffffffffu, my_pairs, o);
@@ -562,7 +574,7 @@ pair_tf32_slab_kernel(const TfArgs a) {
       const TfItem item = a.items[k];
       const int i = item.I * 128 + q * 32 + lane;
       const bool iok = i < a.nall;
-      epilogue_groups<kSlabBlock, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, my_pairs);
+      epilogue_groups<kSlabBlock, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, my_pairs, k);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) my_pairs += __shfl_xor_sync(0xffffffffu, my_pairs, o);
@@ -625,31 +637,39 @@ tf32_convert_kernel(const XView xv, const double* __restrict__ xn, int nall, int
   reinterpret_cast<float4*>(Xb)[(((size_t)g * nslab_t + sl) * nchunk + c) * 48 + (jj >> 2) * 12 + comp * 4 + (jj & 3)] = o;
 }
 
-// ---- exact pass over the candidate list: FP64 covariance, Newton/Jacobi, gates, atomicMax --------
-// 8 lanes per pair.  Decisions are those of pair_col.cu's unit_exact (same second-level screen,
-// same pair_e_exact, same float32-threshold emulation and rot gate).
-struct ExactArgs {
+// ---- exact pass over the candidate bitmask: top-down per row, FP64 covariance, Newton/Jacobi, gates ----
+// The reference's K4 (src/cregen.f90:1353-1373) keeps, per row i, the LARGEST in-band j that matches
+// (`double(i)=j` without leaving the loop), so a row is decided by its candidates in DESCENDING j: the
+// first exact match ends the row, and nothing at or below the link the row already has (earlier pass,
+// other kernel) is looked at.  One warp per row: the row's words of this pass are read 128 at a time
+// (512 B per warp load), non-zero words are cleared on the way (the mask is all-zero again when the
+// kernel ends - no memset per call) and their set bits evaluated four at a time, 8 lanes per candidate.
+// Decisions are those of pair_col.cu's unit_exact (same second-level screen, same pair_e_exact, same
+// float32-threshold emulation and rot gate).  Words of items the classifier handed to the DMMA kernel
+// (dense != 0) are cleared without evaluation.
+struct ScanArgs {
   XView xv; const double* xn; const double* rot; const double* aniso;
-  const int2* cand; const unsigned* cand_count; unsigned cand_cap;
+  unsigned* cmask; unsigned* fmask;
+  int row0, col0, col_end, nall;      // rows [row0, nall) x columns [col0, col_end) of this pass
+  long long stride;                   // words per row (multiple of 128)
+  const unsigned char* dense;         // [segment][i-tile] != 0: candidate-dense item (classify_items_kernel)
+  unsigned char* unfinished;          // [row] set when a row gives up inside a dense item (-> DMMA re-run)
+  int dense_budget;                   // exact evaluations a row may spend inside dense items (0: none)
+  int segcols, ntile;                 // columns per segment (multiple of 128), i-tiles
   Gates g;
   int* dup;
-  unsigned* violations;   // debug (all_cand): pairs the screen called far whose exact e < E2
+  unsigned* counters;                 // [0] += exact evaluations, [2] += screen violations (debug)
+  int debug_all;                      // self-check: evaluate every candidate, no pruning, count violations
 };
 
-__global__ void __launch_bounds__(256)
-exact_cand_kernel(const ExactArgs a) {
-  const unsigned n = min(a.cand_count[0], a.cand_cap);
-  const int sub = threadIdx.x & 7;
-  const unsigned gmask = 0xFFu << (threadIdx.x & 24);
-  for (unsigned p = blockIdx.x * 32u + (threadIdx.x >> 3); p < ((n + 31u) & ~31u); p += gridDim.x * 32u) {
-    const bool live = p < n;
-    const int2 ij = live ? a.cand[p] : make_int2(0, 0);
-    const int i = ij.x, j = ij.y & 0x7fffffff;
-    const bool screen_far_flag = ij.y < 0;
-    const size_t cs = (size_t)a.xv.rows * a.xv.KS;         // distance between components
-    double r[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-    if (live)
-     for (int sd = 0; sd < a.xv.nslab; ++sd) {
+// exact decision for candidate (i, j) by the 8 lanes of group `grp` (sub = lane & 7); returns on the
+// sub == 0 lane: bit 0 = duplicate link, bit 1 = exact e < E2 (for the self-check)
+__device__ __forceinline__ unsigned exact_pair8(const ScanArgs& a, int i, int j, bool live, int sub,
+                                                unsigned gmask) {
+  const size_t cs = (size_t)a.xv.rows * a.xv.KS;         // distance between components
+  double r[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  if (live)
+    for (int sd = 0; sd < a.xv.nslab; ++sd) {
       const double* xi = a.xv.row(i, 0, sd);
       const double* xj = a.xv.row(j, 0, sd);
       for (int k = sub; k < a.xv.KU; k += 8) {
@@ -659,29 +679,196 @@ exact_cand_kernel(const ExactArgs a) {
         r[3] = fma(x1, y0, r[3]); r[4] = fma(x1, y1, r[4]); r[5] = fma(x1, y2, r[5]);
         r[6] = fma(x2, y0, r[6]); r[7] = fma(x2, y1, r[7]); r[8] = fma(x2, y2, r[8]);
       }
-     }
-#pragma unroll
-    for (int z = 0; z < 9; ++z) {
-      r[z] += __shfl_xor_sync(gmask, r[z], 1);
-      r[z] += __shfl_xor_sync(gmask, r[z], 2);
-      r[z] += __shfl_xor_sync(gmask, r[z], 4);
     }
-    if (live && sub == 0) {
-      const double s = a.xn[i] + a.xn[j];
-      const Quartic q = quartic_of(r);
-      const double c1 = a.g.enantio ? -q.c1abs : -8.0 * q.det;
-      if (!screen_far(q, c1, s, fma(1e-8, s, a.g.E2))) {
-        const double e = pair_e_exact(r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], r[8], s,
-                                      a.g.enantio);
-        if (e < a.g.E2) {
-          if (screen_far_flag && a.violations) atomicAdd(a.violations, 1u);
-          bool dupl = e < a.g.E1;
-          if (!dupl)
-            dupl = equalrotaniso_dev(a.rot + 3 * (size_t)i, a.rot + 3 * (size_t)j, a.aniso[i],
-                                     a.aniso[j], a.g.bthr_half, a.g.bthrmax, a.g.bthrshift);
-          if (dupl) atomicMax(a.dup + i, j + 1);
+#pragma unroll
+  for (int z = 0; z < 9; ++z) {
+    r[z] += __shfl_xor_sync(gmask, r[z], 1);
+    r[z] += __shfl_xor_sync(gmask, r[z], 2);
+    r[z] += __shfl_xor_sync(gmask, r[z], 4);
+  }
+  unsigned res = 0;
+  if (live && sub == 0) {
+    const double s = a.xn[i] + a.xn[j];
+    const Quartic q = quartic_of(r);
+    const double c1 = a.g.enantio ? -q.c1abs : -8.0 * q.det;
+    if (!screen_far(q, c1, s, fma(1e-8, s, a.g.E2))) {
+      const double e = pair_e_exact(r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], r[8], s, a.g.enantio);
+      if (e < a.g.E2) {
+        res = 2u;
+        bool dupl = e < a.g.E1;
+        if (!dupl)
+          dupl = equalrotaniso_dev(a.rot + 3 * (size_t)i, a.rot + 3 * (size_t)j, a.aniso[i], a.aniso[j],
+                                   a.g.bthr_half, a.g.bthrmax, a.g.bthrshift);
+        if (dupl) res |= 1u;
+      }
+    }
+  }
+  return res;
+}
+
+__global__ void __launch_bounds__(256)
+cand_scan_kernel(const ScanArgs a) {
+  const int lane = threadIdx.x & 31, sub = lane & 7, grp = lane >> 3;
+  const unsigned gmask = 0xFFu << (lane & 24);
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  unsigned n_eval = 0, n_viol = 0;
+  // longest rows first (descending i), round-robin over the warps of the grid
+  for (int i = a.nall - 1 - wid; i > a.col0 && i >= a.row0; i -= warps) {
+    const int jend = min(i, a.col_end);                       // columns [col0, jend) hold pairs of row i
+    if (jend <= a.col0) continue;
+    unsigned* const rowp = a.cmask + (size_t)(i - a.row0) * (size_t)a.stride;
+    const unsigned* const frow = a.fmask ? a.fmask + (size_t)(i - a.row0) * (size_t)a.stride : nullptr;
+    const int m0 = a.dup[i];
+    int m = m0;                                               // best link so far (j + 1)
+    bool done = false;                                        // row decided: only clearing remains
+    int budget = a.dense_budget;                              // evaluations left inside dense items
+    bool gave_up = false;
+    const unsigned char* const dense_i = a.dense ? a.dense + (i >> 7) : nullptr;
+    for (int blk = (jend - 1 - a.col0) >> 12; blk >= 0; --blk) {     // 128 words = 4096 columns
+      uint4* const wp = reinterpret_cast<uint4*>(rowp + (size_t)blk * 128) + lane;
+      uint4 w = *wp;
+      const bool nz = (w.x | w.y | w.z | w.w) != 0u;
+      unsigned any = __ballot_sync(0xffffffffu, nz);
+      if (!any) continue;
+      if (nz) *wp = make_uint4(0u, 0u, 0u, 0u);
+      if (done) continue;
+      while (any && !done) {
+        const int src = 31 - __clz(any);
+        any &= ~(1u << src);
+        const unsigned w4[4] = {__shfl_sync(0xffffffffu, w.x, src), __shfl_sync(0xffffffffu, w.y, src),
+                                __shfl_sync(0xffffffffu, w.z, src), __shfl_sync(0xffffffffu, w.w, src)};
+#pragma unroll
+        for (int q = 3; q >= 0 && !done; --q) {
+          unsigned word = w4[q];
+          if (!word) continue;
+          const int widx = blk * 128 + src * 4 + q;
+          const int cbase = a.col0 + widx * 32;
+          if (!a.debug_all && cbase + 32 <= m) { done = true; break; }               // whole word below the link
+          const bool in_dense = dense_i && dense_i[(size_t)(cbase / a.segcols) * a.ntile];
+          if (in_dense && budget <= 0) {       // this row's share of the item goes to the FP64 tensor kernel
+            gave_up = true;
+            continue;
+          }
+          const unsigned fword = frow ? frow[widx] : 0u;
+          while (word && !done) {
+            // the four highest candidates of the word, one per 8-lane group
+            int bsel = -1;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              const int bit = word ? 31 - __clz(word) : -1;
+              if (bit >= 0) word &= ~(1u << bit);
+              if (t == grp) bsel = bit;
+            }
+            const int j = cbase + bsel;
+            // descending order: once a candidate is at or below the current link, so is everything after it
+            const bool valid = bsel >= 0;
+            const bool pruned = valid && !a.debug_all && j + 1 <= m;
+            const bool live = valid && !pruned;
+            const unsigned res = exact_pair8(a, i, live ? j : 0, live, sub, gmask);
+            if (live && sub == 0) {
+              ++n_eval;
+              if (a.debug_all && (res & 2u) && ((fword >> bsel) & 1u)) ++n_viol;
+            }
+            int hit = (live && sub == 0 && (res & 1u)) ? j + 1 : 0;
+            hit = __reduce_max_sync(0xffffffffu, hit);
+            if (hit > m) m = hit;
+            if (in_dense) budget -= 4;
+            // a match ends the row (the reference keeps the largest j), and so does a pruned candidate
+            if (!a.debug_all && (hit > 0 || __any_sync(0xffffffffu, pruned))) done = true;
+          }
         }
       }
+    }
+    if (lane == 0 && m > m0) atomicMax(a.dup + i, m);
+    if (lane == 0 && gave_up && !done) a.unfinished[i] = 1;
+  }
+  n_eval = __reduce_add_sync(0xffffffffu, n_eval);
+  n_viol = __reduce_add_sync(0xffffffffu, n_viol);
+  if (lane == 0) {
+    if (n_eval) atomicAdd(a.counters + 0, n_eval);
+    if (n_viol) atomicAdd(a.counters + 2, n_viol);
+  }
+}
+
+// ---- per-item verdict after the screen, dense leftovers on the FP64 tensor kernel --------------------------
+// An item whose candidates exceed 1/16 of its pairs (a block of near-identical structures, or a molecule so
+// large that the TF32 bound decides little) is flagged DENSE.  Measured (C3dense, C4ext):
+// re-doing every dense item as a DMMA contraction costs more than the top-down scan, because nearly every
+// row of such an item ends at its first exact match.  So the scan gets a small budget of evaluations per
+// row inside dense items; only rows that spend it without a match ("unfinished": many near, non-matching
+// neighbours) send their 16-row unit of the item to pair_col_kernel ({J, u_begin, u_end, edge} items) or
+// their 32-row panel to pair_tile_kernel ({panel, j-tile} tiles) - the worst case is bounded by the FP64
+// tensor kernel over the dense items.  A launch whose converter saw unsafe magnitudes (FP32 screen
+// arithmetic not guaranteed finite) sends every unit of every item there.  Item counters are cleared for
+// the next launch.
+struct ClassifyArgs {
+  const TfItem* items; int item_begin, item_end;
+  unsigned* item_cnt;
+  unsigned char* dense; int chunk, ntile;
+  const unsigned char* unfinished;
+  int col_layout;          // 1: column items for pair_col, 0: (panel, j-tile) tiles for pair_tile
+  int4* out_items; unsigned out_cap;
+  unsigned* counters;      // [3] += candidates, [4] converter flag (read), [5] += dense items, [6] list length, [7] list overflow
+  int nunits;              // 16-row units of the column layout / 32-row panels of the row-tile layout
+  int nall;
+  int force_dense;         // developer knob: 1 every item dense and re-done, -1 none (except unsafe magnitudes)
+};
+
+__global__ void __launch_bounds__(256)
+classify_items_kernel(const ClassifyArgs a) {
+  const int k = a.item_begin + blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= a.item_end) return;
+  const TfItem it = a.items[k];
+  const unsigned c = a.item_cnt[k];
+  if (c) { a.item_cnt[k] = 0u; atomicAdd(a.counters + 3, c); }
+  const unsigned pairs = 128u * 16u * (unsigned)(it.g_end - it.g_begin);
+  const bool all = a.force_dense > 0 || a.counters[4] != 0u;
+  const bool dense = all || (a.force_dense == 0 && c > pairs / 16u);
+  a.dense[(size_t)(it.g_begin / a.chunk) * a.ntile + it.I] = all ? 2 : (dense ? 1 : 0);
+  if (dense) atomicAdd(a.counters + 5, 1u);
+}
+
+// after the scan: one thread per dense item; runs of consecutive units that still need work become one
+// column item per j-tile (the column kernel streams the i-units of an item past a resident j-tile)
+__global__ void __launch_bounds__(256)
+expand_dense_kernel(const ClassifyArgs a) {
+  const int per = a.col_layout ? 8 : 4, rows = a.col_layout ? 16 : 32;
+  const int k = a.item_begin + blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= a.item_end) return;
+  const TfItem it = a.items[k];
+  const unsigned char d = a.dense[(size_t)(it.g_begin / a.chunk) * a.ntile + it.I];
+  if (!d) return;
+  unsigned need = 0;
+  for (int sub = 0; sub < per; ++sub) {
+    const int r = it.I * per + sub;                    // unit / panel index
+    if (r >= a.nunits) break;
+    bool nd = d == 2;
+    if (!nd) {
+      const int i0 = r * rows, i1 = min(i0 + rows, a.nall);
+      for (int i = i0; i < i1 && !nd; ++i) nd = a.unfinished[i] != 0;
+    }
+    if (nd) need |= 1u << sub;
+  }
+  if (!need) return;
+  const int J0 = (it.g_begin * 16) / 64, J1 = (it.g_end * 16 - 1) / 64;
+  const unsigned nJ = (unsigned)(J1 - J0 + 1);
+  unsigned nrun = 0;
+  if (a.col_layout) { for (int sub = 0; sub < per; ++sub) nrun += ((need >> sub) & 1u) && !(sub && ((need >> (sub - 1)) & 1u)); }
+  else nrun = __popc(need);
+  const unsigned n = nrun * nJ;
+  unsigned at = atomicAdd(a.counters + 6, n);
+  if (at + n > a.out_cap) { atomicSub(a.counters + 6, n); a.counters[7] = 1u; return; }
+  for (int sub = 0; sub < per; ++sub) {
+    if (!((need >> sub) & 1u)) continue;
+    const int r0 = it.I * per + sub;
+    if (a.col_layout) {
+      int e = sub;
+      while (e + 1 < per && ((need >> (e + 1)) & 1u)) ++e;
+      for (int J = J0; J <= J1; ++J) a.out_items[at++] = make_int4(J, r0, it.I * per + e + 1, 1);
+      sub = e;
+    } else {
+      for (int J = J0; J <= J1; ++J) a.out_items[at++] = make_int4(r0, J, 0, 0);
     }
   }
 }
@@ -702,15 +889,26 @@ static XView make_xview(const double* d_X, const PackLayout& L) {
   return v;
 }
 
+// Error budget of the screen for a K extent of `kslots` atom slots: operands rounded to
+// TF32 by us (u), products exact in FP32, FP32 accumulation over the chained MMAs budgeted at
+// gamma = max(6e-5, 2 * kslots * 2^-23) (one truncated add per product, twice the truncation ulp);
+// kappa = sqrt(3) * (2u + u^2 + gamma) with 0.2 % slack, never below the 1.8e-3 of the A <= 88 analysis.
+double tf32_kappa(int kslots) {
+  const double u = std::ldexp(1.0, -11) * (1.0 + std::ldexp(1.0, -12));
+  const double gamma = std::max(6.0e-5, 2.0 * (double)kslots * std::ldexp(1.0, -23));
+  const double k = 1.002 * std::sqrt(3.0) * (2.0 * u + u * u + gamma);
+  return k > 1.8e-3 ? k : 1.8e-3;
+}
+
 int launch_tf32_convert(const double* d_X, const double* d_xn, int nall, const PackLayout& L,
-                        int ntile, int nslab_t, int kslab, float* d_Xa, float* d_Xb, float* d_hn,
-                        unsigned* d_unsafe, cudaStream_t stream) {
+                        int ntile, int nslab_t, int kslab, double kappa, float* d_Xa, float* d_Xb,
+                        float* d_hn, unsigned* d_unsafe, cudaStream_t stream) {
   CREST_CUDA_TRY(cudaMemsetAsync(d_unsafe, 0, sizeof(unsigned), stream));
   const long long total = (long long)ntile * 128 * 3 * (kslab / 4) * nslab_t;
   if (total <= 0) return 0;
   const int blocks = (int)((total + 255) / 256);
   tf32_convert_kernel<<<blocks, 256, 0, stream>>>(make_xview(d_X, L), d_xn, nall, ntile, nslab_t, kslab,
-                                                  d_Xa, d_Xb, d_hn, kTfKappa, d_unsafe);
+                                                  d_Xa, d_Xb, d_hn, kappa, d_unsafe);
   CREST_CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -731,15 +929,56 @@ static int launch_tf32_inst(const TfArgs& a, int grid, int smem, cudaStream_t st
   return 0;
 }
 
-int launch_pair_tf32(const PairArgs& pa, const Tf32Buffers& tb, const void* d_items, int item_begin,
-                     int item_end, int all_cand, cudaStream_t stream, int* grid_out, int* smem_out) {
+// words of the candidate bitmask of a pass over columns [col0, col_end): rows [col0, nall), row stride
+// rounded up to 128 words (one warp-wide uint4 load of cand_scan_kernel)
+static long long mask_stride(int col0, int col_end) {
+  const long long w = ((long long)(col_end - col0) + 31) / 32;
+  return (w + 127) / 128 * 128;
+}
+size_t tf32_mask_words(int nall, int col0, int col_end) {
+  return (size_t)(nall - col0 > 0 ? nall - col0 : 0) * (size_t)mask_stride(col0, col_end);
+}
+
+static int launch_tf32_screen(const TfArgs& a, bool slab, int grid, int smem, cudaStream_t stream) {
+  if (slab) {
+    if (a.dbg != 0 || a.all_cand) {
+      CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_slab_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      pair_tf32_slab_kernel<true><<<grid, kTfThreads, smem, stream>>>(a);
+    } else {
+      CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_slab_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      pair_tf32_slab_kernel<false><<<grid, kTfThreads, smem, stream>>>(a);
+    }
+    CREST_CUDA_TRY(cudaGetLastError());
+    return 0;
+  }
+  switch (a.KU / 8) {
+    case 1: return launch_tf32_inst<1>(a, grid, smem, stream);
+    case 2: return launch_tf32_inst<2>(a, grid, smem, stream);
+    case 3: return launch_tf32_inst<3>(a, grid, smem, stream);
+    case 4: return launch_tf32_inst<4>(a, grid, smem, stream);
+    case 5: return launch_tf32_inst<5>(a, grid, smem, stream);
+    case 6: return launch_tf32_inst<6>(a, grid, smem, stream);
+    case 7: return launch_tf32_inst<7>(a, grid, smem, stream);
+    case 8: return launch_tf32_inst<8>(a, grid, smem, stream);
+    case 9: return launch_tf32_inst<9>(a, grid, smem, stream);
+    case 10: return launch_tf32_inst<10>(a, grid, smem, stream);
+    case 11: return launch_tf32_inst<11>(a, grid, smem, stream);
+    default: set_error("tf32 kernel: unsupported K extent %d", a.KU); return 1;
+  }
+}
+
+// Screen + exact decisions of the items [item_begin, item_end) of a segment-major work list.  The list
+// is cut into PASSES of whole segments (all items of a pass share the column range [col0, col_end)),
+// run from the highest columns down so that links found in one pass prune the candidates of the next:
+//   pair_tf32 screen -> classify_items -> FP64 tensor kernel on dense items -> cand_scan (top-down)
+int launch_pair_tf32(const PairArgs& pa, const PairArgs& fb_in, const Tf32Buffers& tb, const void* d_items,
+                     const int* h_items, int item_begin, int item_end, int all_cand, int nstage_tile,
+                     cudaStream_t stream, int* grid_out, int* smem_out, long long* launches_out) {
   if (grid_out) *grid_out = 0;
-  const int nitems = item_end - item_begin;
-  if (nitems <= 0) return 0;
+  if (item_end - item_begin <= 0) return 0;
   TfArgs a{};
   a.Xa = tb.Xa; a.Xb = tb.Xb; a.hn = tb.hn; a.er = pa.er;
   a.items = static_cast<const TfItem*>(d_items);
-  a.item_begin = item_begin; a.item_end = item_end;
   a.nall = pa.nall; a.KU = tb.kslab; a.nslab = tb.nslab;
   const bool slab = tb.nslab > 1 || tb.kslab != pa.L.KU;
   int ns = 0;
@@ -755,48 +994,89 @@ int launch_pair_tf32(const PairArgs& pa, const Tf32Buffers& tb, const void* d_it
   a.nbstage = ns;
   a.cE = -0.5f * pa.g.E2_up;
   a.ethr = pa.g.ethr; a.enantio = pa.g.enantio; a.all_cand = all_cand; a.dbg = pa.g.debug;
-  a.cand = static_cast<int2*>(tb.cand); a.cand_cap = tb.cand_cap; a.cand_count = tb.cand_count;
+  a.cmask = tb.cmask; a.fmask = all_cand ? tb.fmask : nullptr;
+  a.dup = pa.dup; a.item_cnt = tb.item_cnt; a.cand_count = tb.cand_count;
   a.npairs = pa.npairs;
+  if (all_cand && !tb.fmask) { set_error("self-check needs the far-verdict mask"); return 1; }
   int dev = 0, nsm = 148;
   CREST_CUDA_TRY(cudaGetDevice(&dev));
   CREST_CUDA_TRY(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
-  const int grid = nitems < nsm ? nitems : nsm;
-  int rc = 1;
-  if (slab) {
-    if (a.dbg != 0 || a.all_cand) {
-      CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_slab_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      pair_tf32_slab_kernel<true><<<grid, kTfThreads, smem, stream>>>(a);
-    } else {
-      CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tf32_slab_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      pair_tf32_slab_kernel<false><<<grid, kTfThreads, smem, stream>>>(a);
+  const int chunk = tb.chunk, segcols = chunk * 16;
+  const int ntile = (pa.nall + 127) / 128;
+  const bool col_layout = pa.L.rows == kUnit;
+  int grid_max = 0;
+  long long launches = 0;
+  auto seg_of = [&](int k) { return h_items[4 * k + 1] / chunk; };
+  int pe = item_end;
+  while (pe > item_begin) {
+    // grow the pass downwards by whole segments while its bitmask fits
+    const int s_hi = seg_of(pe - 1);
+    const int col_end = std::min((s_hi + 1) * segcols, pa.nall);
+    int pb = pe, s_lo = s_hi;
+    for (;;) {
+      int q = pb;
+      const int s = seg_of(q - 1);
+      while (q > item_begin && seg_of(q - 1) == s) --q;
+      if (tf32_mask_words(pa.nall, s * segcols, col_end) > tb.cm_words) {
+        if (pb == pe) { set_error("candidate bitmask too small for one segment (%zu words)", tb.cm_words); return 1; }
+        break;
+      }
+      pb = q; s_lo = s;
+      if (pb == item_begin) break;
     }
+    const int col0 = s_lo * segcols;
+    a.item_begin = pb; a.item_end = pe;
+    a.cm_row0 = col0; a.cm_col0 = col0; a.cm_stride = mask_stride(col0, col_end);
+    const int nitems = pe - pb;
+    const int grid = nitems < nsm ? nitems : nsm;
+    if (grid > grid_max) grid_max = grid;
+    CREST_CUDA_TRY(cudaMemsetAsync(tb.cand_count + 6, 0, sizeof(unsigned), stream));
+    if (all_cand)
+      CREST_CUDA_TRY(cudaMemsetAsync(tb.fmask, 0, sizeof(unsigned) * tf32_mask_words(pa.nall, col0, col_end), stream));
+    if (launch_tf32_screen(a, slab, grid, smem, stream)) return 1;
+    ClassifyArgs c{};
+    c.items = a.items; c.item_begin = pb; c.item_end = pe; c.item_cnt = tb.item_cnt;
+    c.dense = tb.dense; c.chunk = chunk; c.ntile = ntile; c.col_layout = col_layout ? 1 : 0;
+    c.unfinished = tb.unfinished; c.nall = pa.nall;
+    c.out_items = tb.dense_items; c.out_cap = tb.dense_items_cap; c.counters = tb.cand_count;
+    c.nunits = pa.L.npanel; c.force_dense = tune().force_dense ? 1 : (tune().no_dense ? -1 : 0);
+    classify_items_kernel<<<(nitems + 255) / 256, 256, 0, stream>>>(c);
     CREST_CUDA_TRY(cudaGetLastError());
-    rc = 0;
-  } else
-  switch (a.KU / 8) {
-    case 1: rc = launch_tf32_inst<1>(a, grid, smem, stream); break;
-    case 2: rc = launch_tf32_inst<2>(a, grid, smem, stream); break;
-    case 3: rc = launch_tf32_inst<3>(a, grid, smem, stream); break;
-    case 4: rc = launch_tf32_inst<4>(a, grid, smem, stream); break;
-    case 5: rc = launch_tf32_inst<5>(a, grid, smem, stream); break;
-    case 6: rc = launch_tf32_inst<6>(a, grid, smem, stream); break;
-    case 7: rc = launch_tf32_inst<7>(a, grid, smem, stream); break;
-    case 8: rc = launch_tf32_inst<8>(a, grid, smem, stream); break;
-    case 9: rc = launch_tf32_inst<9>(a, grid, smem, stream); break;
-    case 10: rc = launch_tf32_inst<10>(a, grid, smem, stream); break;
-    case 11: rc = launch_tf32_inst<11>(a, grid, smem, stream); break;
-    default: set_error("tf32 kernel: unsupported K extent %d", a.KU); return 1;
+    CREST_CUDA_TRY(cudaMemsetAsync(tb.unfinished, 0, (size_t)pa.nall, stream));
+    ScanArgs e{};
+    e.xv = make_xview(pa.X, pa.L); e.xn = pa.xn; e.rot = pa.rot; e.aniso = pa.aniso;
+    e.cmask = tb.cmask; e.fmask = a.fmask;
+    e.row0 = col0; e.col0 = col0; e.col_end = col_end; e.nall = pa.nall; e.stride = a.cm_stride;
+    e.dense = all_cand ? nullptr : tb.dense; e.unfinished = tb.unfinished;
+    e.dense_budget = (c.force_dense > 0) ? 0 : (tune().dense_budget > 0 ? tune().dense_budget : 64);
+    e.segcols = segcols; e.ntile = ntile;
+    e.g = pa.g; e.dup = pa.dup; e.counters = tb.cand_count; e.debug_all = all_cand ? 1 : 0;
+    const int rows = pa.nall - col0;
+    int sgrid = (rows + 7) / 8;
+    if (sgrid > nsm * 8) sgrid = nsm * 8;
+    if (sgrid < 1) sgrid = 1;
+    cand_scan_kernel<<<sgrid, 256, 0, stream>>>(e);
+    CREST_CUDA_TRY(cudaGetLastError());
+    // unfinished units of dense items on the FP64 tensor kernel (idle CTAs return at once when the list is empty)
+    if (!all_cand) {
+      expand_dense_kernel<<<(nitems + 255) / 256, 256, 0, stream>>>(c);
+      CREST_CUDA_TRY(cudaGetLastError());
+      PairArgs fb = fb_in;
+      fb.work_count = tb.cand_count + 6;
+      int g2 = 0, s2 = 0;
+      if (col_layout) {
+        if (launch_pair_cols(fb, tb.dense_items, 0, 0, stream, &g2, &s2)) return 1;
+      } else {
+        fb.tiles = tb.dense_items; fb.tile_begin = 0; fb.tile_end = 0;
+        if (launch_pair_tiles(fb, nstage_tile, stream, &g2, &s2)) return 1;
+      }
+    }
+    launches += all_cand ? 3 : 5;
+    pe = pb;
   }
-  if (rc) return rc;
-  ExactArgs e{};
-  e.xv = make_xview(pa.X, pa.L); e.xn = pa.xn; e.rot = pa.rot; e.aniso = pa.aniso;
-  e.cand = a.cand; e.cand_count = tb.cand_count; e.cand_cap = tb.cand_cap;
-  e.g = pa.g; e.dup = pa.dup;
-  e.violations = all_cand ? tb.cand_count + 2 : nullptr;
-  exact_cand_kernel<<<nsm * 4, 256, 0, stream>>>(e);
-  CREST_CUDA_TRY(cudaGetLastError());
-  if (grid_out) *grid_out = grid;
+  if (grid_out) *grid_out = grid_max;
   if (smem_out) *smem_out = smem;
+  if (launches_out) *launches_out += launches;
   return 0;
 }
 

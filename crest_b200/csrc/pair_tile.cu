@@ -35,6 +35,11 @@ struct TileCursor {
   long long row_beg = 0, row_end = 0;   // rowstart[I], rowstart[I+1]
   int jf = 0;
   __device__ __forceinline__ void seek(const PairArgs& a, long long t, int& Iout, int& Jout) {
+    if (a.tiles) {                      // explicit device-generated tile list
+      const int4 tl = a.tiles[t];
+      Iout = tl.x; Jout = tl.y;
+      return;
+    }
     if (I < 0) {
       int lo = 0, hi = a.nI - 1;        // largest I with rowstart[I] <= t
       while (lo < hi) {
@@ -55,7 +60,8 @@ struct TileCursor {
 
 __global__ void __launch_bounds__(kPairThreads, 1)
 pair_tile_kernel(const PairArgs a, const int nstage) {
-  if (a.run_if && *a.run_if == 0u) return;   // fallback behind the tensor-core screen: idle unless it overflowed
+  const long long tile_end = a.work_count ? a.tile_begin + (long long)*a.work_count : a.tile_end;
+  if (a.tile_begin + blockIdx.x >= tile_end) return;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kMaxStages];
   __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
@@ -100,7 +106,7 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
   uint32_t p_it = 0;
   TileCursor p_cur;
   auto produce_one = [&]() {
-    if (p_tile >= a.tile_end) return;
+    if (p_tile >= tile_end) return;
     if (p_slab == 0) p_cur.seek(a, p_tile, p_I, p_J);
     const int st = p_it % nstage;
     const uint32_t ph = (p_it / nstage) & 1;
@@ -138,7 +144,7 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
   constexpr bool prof = false;
 #endif
   TileCursor cur;
-  for (long long t = a.tile_begin + blockIdx.x; t < a.tile_end; t += gridDim.x) {
+  for (long long t = a.tile_begin + blockIdx.x; t < tile_end; t += gridDim.x) {
     int I, J;
     cur.seek(a, t, I, J);
     const int i0 = I * kTileI + wi * 16;       // first i of this warp
@@ -336,7 +342,7 @@ int pair_smem_bytes(const PackLayout& L, int* nstage_out) {
 int launch_pair_tiles(const PairArgs& a_in, int nstage, cudaStream_t stream, int* grid_out,
                       int* smem_out) {
   PairArgs a = a_in;
-  const long long ntiles = a.tile_end - a.tile_begin;
+  const long long ntiles = a.work_count ? (1ll << 40) : a.tile_end - a.tile_begin;
   if (grid_out) *grid_out = 0;
   if (ntiles <= 0) return 0;
   int dev = 0, nsm = 148;

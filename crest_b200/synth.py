@@ -43,8 +43,10 @@ def _random_rotations(rng, n):
     return R
 
 
-def make_molecule(rng, nat, nheavy):
-    """Topology: returns (at[nat], parent[nat] for hydrogens, base dihedrals)."""
+def make_molecule(rng, nat, nheavy, extended=False):
+    """Topology: returns (at[nat], parent[nat] for hydrogens, base dihedrals).  extended: an
+    all-trans backbone (dihedrals pi +- 0.2) instead of a random coil - a large radius of gyration,
+    the unfriendly case for the TF32 screen (its undecided zone grows with Rg)."""
     nheavy = max(3, min(nheavy, nat))
     at = np.ones(nat, dtype=np.int32)
     at[:nheavy] = rng.choice([6, 7, 8], size=nheavy, p=[0.75, 0.10, 0.15])
@@ -53,12 +55,14 @@ def make_molecule(rng, nat, nheavy):
     parent = np.arange(nh) % nheavy
     slot = np.arange(nh) // nheavy
     base_dih = rng.uniform(-np.pi, np.pi, size=nheavy)
+    if extended:
+        base_dih = np.pi + 0.2 * base_dih / np.pi
     return at, parent.astype(np.int64), slot.astype(np.int64), base_dih, nheavy
 
 
-def build_conformers(rng, K, nat, nheavy, n_torsion_changes=4):
+def build_conformers(rng, K, nat, nheavy, n_torsion_changes=4, extended=False):
     """K conformers (K,nat,3) of one molecule differing in a few backbone torsions."""
-    at, parent, slot, base_dih, nheavy = make_molecule(rng, nat, nheavy)
+    at, parent, slot, base_dih, nheavy = make_molecule(rng, nat, nheavy, extended)
     dih = np.tile(base_dih, (K, 1))
     for _ in range(n_torsion_changes):
         which = rng.integers(3, max(4, nheavy), size=K)
@@ -84,14 +88,15 @@ def build_conformers(rng, K, nat, nheavy, n_torsion_changes=4):
 
 
 def make_ensemble(nall, nat, nheavy=None, copies=8, seed=SEED, ewin_kcal=6.0,
-                  frac_mirror=0.10, frac_straddle=0.05, frac_rotamer=0.05, sigma=0.02):
+                  frac_mirror=0.10, frac_straddle=0.05, frac_rotamer=0.05, sigma=0.02,
+                  extended=False, n_torsion_changes=4):
     """Returns dict(at (nat,), xyz (nall,nat,3) C-order == Fortran xyz(3,nat,nall), er (nall,) Eh
     ascending, conf_id (nall,), kind (nall,) 0 dup /1 mirror /2 straddler /3 rotamer)."""
     rng = np.random.default_rng(seed)
     if nheavy is None:
         nheavy = nat
     K = max(1, (nall + copies - 1) // copies)
-    at, conf, parent, slot, nheavy = build_conformers(rng, K, nat, nheavy)
+    at, conf, parent, slot, nheavy = build_conformers(rng, K, nat, nheavy, n_torsion_changes, extended)
     conf_id = rng.integers(0, K, size=nall)
     conf_id[:min(K, nall)] = np.arange(min(K, nall))      # every conformer at least once
     kind = np.zeros(nall, dtype=np.int32)
@@ -135,6 +140,18 @@ CONFIGS = {
     "C3": dict(nall=100000, nat=60, nheavy=60, heavy=False),
     "C4": dict(nall=20000, nat=300, nheavy=138, heavy=False),
     "C5": dict(nall=1000000, nat=40, nheavy=40, heavy=False),
+    # unfriendly ensembles for the tensor-core screen: a COLLAPSED ensemble (1000 copies
+    # per conformer: 100 000 structures -> 100 conformers, the regime after iMTD-GC,
+    # reference src/algos/search_conformers.f90:179-180) and an EXTENDED chain (large Rg, conformers
+    # one small torsion change apart: many near pairs the TF32 bound cannot decide)
+    "C3dense": dict(nall=100000, nat=60, nheavy=60, heavy=False, copies=1000),
+    # adversarial for the screen: ONE conformer with noise sigma = 0.135 A per coordinate: every pair sits
+    # at RMSD ~ 0.33 A - above 2*rthr (no match, nothing prunes) but inside the zone the TF32 bound cannot
+    # decide: all pairs become candidates and the dense items end on the FP64 tensor kernel
+    "C3adv": dict(nall=100000, nat=60, nheavy=60, heavy=False, copies=100000, sigma=0.135,
+                  frac_mirror=0.0, frac_straddle=0.0, frac_rotamer=0.0),
+    "C4ext": dict(nall=20000, nat=300, nheavy=138, heavy=False, extended=True, copies=40,
+                  n_torsion_changes=1),
 }
 
 

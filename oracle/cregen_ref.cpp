@@ -123,6 +123,10 @@ void cregen_cre(int nat, int nall, const int* at, double* xyz, const double* er_
       if (!(de < ethr)) continue;
       const int64_t kl = linr(out.rmap1[i], out.rmap2[i], j);
       const double dr = (double)rmat[(size_t)(kl - 1)];
+      if (p.boundary_tol >= 0.0 &&
+          (std::fabs(dr - rthr) <= p.boundary_tol || std::fabs(dr - 2.0 * rthr) <= p.boundary_tol) &&
+          (out.boundary_rows.empty() || out.boundary_rows.back() != i))
+        out.boundary_rows.push_back(i);
       if (dr < rthr) {
         dbl[i] = j;
       } else if (dr < 2.0 * rthr) {

@@ -123,6 +123,7 @@ struct CreParams {
   const int* include_rmsd = nullptr;  // mask(nat), >0 = atom enters RMSD (substruc only)
   int nosort = 0;
   int keep_rmat = 0;
+  double boundary_tol = -1.0;  // >= 0: record rows with a band RMSD within tol of rthr / 2*rthr
 };
 
 struct CreResult {
@@ -139,6 +140,7 @@ struct CreResult {
   int nallout = 0;              // value returned to the caller
   int nkept = 0;                // nall - #duplicates
   int nfail = 0;                // number of rmsd() calls that returned -1
+  std::vector<int> boundary_rows;  // 1-based rows i with |dr-rthr| or |dr-2rthr| <= boundary_tol (test listing)
 };
 
 // Apply "structure i goes to position pos[i]" to an array of records (what the reference's

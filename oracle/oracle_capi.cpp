@@ -11,6 +11,9 @@
 
 using namespace crest_oracle;
 
+static double g_boundary_tol = -1.0;
+static std::vector<int> g_boundary_rows;
+
 extern "C" {
 
 // out[0]=rmsd out[1]=lambda out[2]=xnorm out[3]=ynorm out[4..12]=R row-major, out[13..16]=q
@@ -99,6 +102,15 @@ void oracle_backtrack(int n, int* arr1 /*n+1, [0] unused*/) {
 // Full cregen_CRE.  Outputs (caller allocated): rot(3,nall), er_out(nall), dup(nall) 1-based
 // parents, orderref(nall) 1-based, group(0:nall), enuc(nall), rmat (klong floats or NULL),
 // info[0]=nallout info[1]=nkept info[2]=klong info[3]=nfail.
+// Test listing: rows whose band holds an RMSD within `tol` of rthr / 2*rthr in the NEXT
+// oracle_cregen_cre call (tol < 0 switches the listing off); read back with oracle_boundary_rows.
+void oracle_set_boundary_tol(double tol) { g_boundary_tol = tol; }
+int oracle_boundary_rows(int* rows, int cap) {
+  const int n = (int)g_boundary_rows.size();
+  if (rows) for (int i = 0; i < n && i < cap; ++i) rows[i] = g_boundary_rows[i];
+  return n;
+}
+
 int oracle_cregen_cre(int nat, int nall, const int* at, double* xyz, const double* er,
                       const int* include_rmsd, int substruc, int heavy, int enantio, int nosort,
                       double ethr, double rthr, double bthr, double bthrmax, double bthrshift,
@@ -108,8 +120,10 @@ int oracle_cregen_cre(int nat, int nall, const int* at, double* xyz, const doubl
   p.ethr = ethr; p.rthr = rthr; p.bthr = bthr; p.bthrmax = bthrmax; p.bthrshift = bthrshift;
   p.enantio = enantio; p.heavy = heavy; p.substruc = substruc; p.include_rmsd = include_rmsd;
   p.nosort = nosort; p.keep_rmat = rmat != nullptr;
+  p.boundary_tol = g_boundary_tol;
   CreResult r;
   cregen_cre(nat, nall, at, xyz, er, p, r);
+  g_boundary_rows = r.boundary_rows;
   for (int i = 0; i < nall; ++i) {
     if (rot) { rot[3 * i] = r.rot[3 * i]; rot[3 * i + 1] = r.rot[3 * i + 1]; rot[3 * i + 2] = r.rot[3 * i + 2]; }
     if (er_out) er_out[i] = r.er[i];

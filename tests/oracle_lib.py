@@ -47,6 +47,10 @@ def lib():
         L.oracle_cregen_cre.argtypes = [C.c_int, C.c_int, c_ip, c_dp, c_dp, c_ip, C.c_int, C.c_int,
                                         C.c_int, C.c_int] + [C.c_double] * 5 + \
             [c_dp, c_dp, c_ip, c_ip, c_ip, c_dp, c_fp, C.c_longlong, c_lp]
+        L.oracle_set_boundary_tol.restype = None
+        L.oracle_set_boundary_tol.argtypes = [C.c_double]
+        L.oracle_boundary_rows.restype = C.c_int
+        L.oracle_boundary_rows.argtypes = [c_ip, C.c_int]
         L.oracle_pair_rows.restype = C.c_longlong
         L.oracle_pair_rows.argtypes = [C.c_int, C.c_int, c_dp, c_dp, C.c_double, C.c_int, C.c_int,
                                        C.c_int, c_fp]
@@ -131,7 +135,8 @@ def esort(energies, ewin=1e9):
 
 
 def cregen_cre(at, xyz, er, *, ethr=0.05, rthr=0.125, bthr=0.01, bthrmax=0.025, bthrshift=0.5,
-               enantio=True, heavy=False, include_rmsd=None, nosort=False, want_rmat=False):
+               enantio=True, heavy=False, include_rmsd=None, nosort=False, want_rmat=False,
+               boundary_tol=None):
     """Run the oracle cregen_CRE.  xyz (nall,nat,3); er ascending (Eh). Returns a dict; xyz is
     returned transformed + permuted like the reference leaves it."""
     xyz = np.array(xyz, np.float64, order="C", copy=True)
@@ -149,6 +154,7 @@ def cregen_cre(at, xyz, er, *, ethr=0.05, rthr=0.125, bthr=0.01, bthrmax=0.025, 
     info = np.zeros(4, np.int64)
     cap = nall * (nall - 1) // 2 if want_rmat else 0
     rmat = np.zeros(max(cap, 1), np.float32) if want_rmat else None
+    lib().oracle_set_boundary_tol(-1.0 if boundary_tol is None else float(boundary_tol))
     rc = lib().oracle_cregen_cre(nat, nall, _ip(at), _dp(xyz), _dp(er), _ip(inc), int(substruc),
                                  int(heavy), int(enantio), int(nosort), ethr, rthr, bthr, bthrmax,
                                  bthrshift, _dp(rot), _dp(er_out), _ip(dup), _ip(orderref),
@@ -161,6 +167,12 @@ def cregen_cre(at, xyz, er, *, ethr=0.05, rthr=0.125, bthr=0.01, bthrmax=0.025, 
                nkept=int(info[1]), klong=int(info[2]), nfail=int(info[3]))
     if want_rmat:
         res["rmat"] = rmat[:int(info[2])]
+    if boundary_tol is not None:
+        nb = lib().oracle_boundary_rows(None, 0)
+        rows = np.zeros(max(nb, 1), np.int32)
+        lib().oracle_boundary_rows(_ip(rows), nb)
+        res["boundary_rows"] = rows[:nb] - 1      # 0-based rows (stage-A numbering)
+        lib().oracle_set_boundary_tol(-1.0)
     return res
 
 

@@ -467,7 +467,7 @@ def test_tf32_equals_fp64_kernels(cb, cfg, nall, ethr):
     l_til, r_til, i_til = _stage_a(cb, ens, env, "notf32,tile")
     # A <= 88: one-slab kernel vs column + row-tile DMMA; A > 88 (C4): K-slab kernel vs row-tile DMMA
     assert (i_tf["variant"], i_col["variant"], i_til["variant"]) == (2, 1 if i_tf["A"] <= 88 else 0, 0)
-    assert i_tf["overflow"] == 0
+    assert i_tf["flags"] == 0
     assert l_tf["npairs"] == l_col["npairs"] == l_til["npairs"]
     assert np.array_equal(l_tf["dup"], l_col["dup"]) and np.array_equal(l_tf["dup"], l_til["dup"])
     assert np.array_equal(r_tf, r_col)
@@ -494,7 +494,6 @@ def test_tf32_screen_selfcheck(cb):
                       env_from_kwargs(cb, gold_kwargs(g), g["xyz"].shape[1])))
     for ens, env in cases:
         n = len(ens["er"])
-        cregen.set_tune(f"cap={n * n}")
         try:
             os.environ["CREST_CUDA_DEBUG"] = "3"
             ctx = cb.CregenContext()
@@ -506,24 +505,87 @@ def test_tf32_screen_selfcheck(cb):
             ctx.close()
         finally:
             os.environ.pop("CREST_CUDA_DEBUG", None)
-            cregen.set_tune(None)
-        assert info["variant"] == 2 and info["overflow"] == 0
+        assert info["variant"] == 2 and info["flags"] == 0
         assert info["candidates"] == links["npairs"]          # every pair was re-checked
+        assert info["exact_evals"] == links["npairs"]
         assert info["violations"] == 0
         ref, _, _ = _stage_a(cb, ens, env, "notf32")
         assert np.array_equal(links["dup"], ref["dup"])
 
 
-def test_tf32_overflow_falls_back_to_fp64(cb):
-    """A candidate list that is too small must not lose pairs: the launch is re-run on the FP64
-    column kernel (conditional launch, no host round trip)."""
-    ens = synth.make_config("C1", nall=1000, seed=5)
-    env = cb.Env(ethr=1e9)
+@pytest.mark.parametrize("cfg,nall,ethr", [("C1", 1000, 1e9), ("C5", 3000, 0.2), ("C4", 700, 1e9)])
+def test_tf32_dense_items_go_to_fp64_tensor_kernel(cb, cfg, nall, ethr):
+    """`forcedense` hands EVERY work item of the screen to the FP64 tensor kernel through the
+    device-built work list (column items for A <= 88, row tiles above): same links, same pair count."""
+    ens = synth.make_config(cfg, nall=nall, seed=5)
+    env = cb.Env(ethr=ethr)
     ref, rref, _ = _stage_a(cb, ens, env, "notf32")
-    got, rgot, info = _stage_a(cb, ens, env, "cap=32")
-    assert info["variant"] == 2 and info["overflow"] == 1
+    got, rgot, info = _stage_a(cb, ens, env, "forcedense")
+    assert info["variant"] == 2 and info["dense_items"] == info["tiles_total"] and info["flags"] == 0
+    assert info["exact_evals"] == 0
     assert np.array_equal(got["dup"], ref["dup"]) and np.array_equal(rgot, rref)
     assert got["npairs"] == ref["npairs"]
+
+
+@pytest.mark.parametrize("nall,nat,copies", [(6000, 40, 300), (4000, 60, 2000), (1500, 300, 500)])
+def test_tf32_collapsed_ensembles(cb, nall, nat, copies):
+    """Collapsed ensembles (hundreds to thousands of copies per conformer: the iMTD-GC regime): nearly
+    every candidate is a match.  The top-down scan decides a row with its first exact match, dense
+    items go to the FP64 tensor kernel; links identical to the FP64-only run."""
+    ens = synth.make_ensemble(nall, nat, nat, copies=copies, seed=17)
+    ens["heavy"] = False
+    env = cb.Env(ethr=1e9)
+    ref, rref, _ = _stage_a(cb, ens, env, "notf32")
+    got, rgot, info = _stage_a(cb, ens, env)
+    assert info["variant"] == 2 and info["flags"] == 0
+    assert np.array_equal(got["dup"], ref["dup"]) and np.array_equal(rgot, rref)
+    assert got["npairs"] == ref["npairs"]
+    assert info["candidates"] > 0.001 * got["npairs"]
+    # without the dense path every candidate block is decided by the scan alone: still identical, and
+    # far fewer exact evaluations than candidates (largest-j-wins pruning)
+    got2, rgot2, info2 = _stage_a(cb, ens, env, "nodense")
+    assert info2["dense_items"] == 0
+    assert np.array_equal(got2["dup"], ref["dup"])
+    assert info2["exact_evals"] < 0.5 * info2["candidates"]
+    # a zero-ish budget inside dense items: rows that need more than 4 evaluations there hand their unit
+    # to the FP64 tensor kernel
+    got3, rgot3, info3 = _stage_a(cb, ens, env, "densebudget=1")
+    assert np.array_equal(got3["dup"], ref["dup"]) and got3["npairs"] == ref["npairs"]
+
+
+def test_tf32_adversarial_near_misses(cb):
+    """One conformer, noise of 0.135 A per coordinate: every pair at RMSD ~ 0.33 A, i.e. no match at all
+    (nothing for the largest-j-wins pruning to use) but inside the zone the TF32 bound cannot decide.
+    Rows spend their evaluation budget inside the dense items and hand their units to the FP64 tensor
+    kernel; the result is the FP64-only one and the scan's work stays bounded."""
+    ens = synth.make_config("C3adv", nall=3000, seed=77)
+    env = cb.Env(ethr=1e9)
+    ref, rref, _ = _stage_a(cb, ens, env, "notf32")
+    got, rgot, info = _stage_a(cb, ens, env)
+    assert info["variant"] == 2 and info["flags"] == 0
+    assert np.array_equal(got["dup"], ref["dup"]) and got["npairs"] == ref["npairs"]
+    assert (got["dup"] != 0).sum() < 30                       # (almost) nothing matches
+    assert info["candidates"] > 0.9 * got["npairs"]           # the screen decides (almost) nothing
+    assert info["dense_items"] > 0
+    assert info["exact_evals"] <= 3000 * (64 + 8)             # budget per row inside dense items
+
+
+@pytest.mark.parametrize("cfg,nall,ethr,maskmb", [("C1", 1000, 1e9, 1), ("C5", 9000, 1e9, 1), ("C5", 9000, 0.3, 1),
+                                                  ("C4", 1200, 1e9, 1)])
+def test_tf32_multi_pass_mask(cb, cfg, nall, ethr, maskmb):
+    """A candidate bitmask budget of 1 MB forces several passes (descending column blocks, links of one
+    pass pruning the next): same links as one pass and as the FP64 kernels."""
+    ens = synth.make_config(cfg, nall=nall, seed=41)
+    env = cb.Env(ethr=ethr)
+    ref, rref, _ = _stage_a(cb, ens, env, "notf32")
+    one, rone, i1 = _stage_a(cb, ens, env)
+    got, rgot, info = _stage_a(cb, ens, env, f"maskmb={maskmb},chunk=8")
+    assert info["variant"] == 2
+    if nall >= 5000:
+        assert info["launches"] > i1["launches"]
+    assert np.array_equal(got["dup"], ref["dup"]) and np.array_equal(one["dup"], ref["dup"])
+    assert np.array_equal(rgot, rref)
+    assert got["npairs"] == ref["npairs"] == one["npairs"]
 
 
 @pytest.mark.parametrize("cfg,nall", [("C1", 700), ("C4", 300)])
@@ -539,13 +601,13 @@ def test_tf32_unsafe_magnitudes_fall_back(cb, cfg, nall):
     env = cb.Env(ethr=1e9)
     ref, rref, _ = _stage_a(cb, ens, env, "notf32")
     got, rgot, info = _stage_a(cb, ens, env)
-    assert info["variant"] == 2 and info["overflow"] == 1
+    assert info["variant"] == 2 and (info["flags"] & 1) == 1 and info["dense_items"] == info["tiles_total"]
     assert np.array_equal(got["dup"], ref["dup"]) and np.array_equal(rgot, rref)
     assert got["npairs"] == ref["npairs"]
     # and the flag is cleared by the next pack of a tame ensemble on a fresh context
     tame = synth.make_config(cfg, nall=nall, seed=9)
     _, _, info2 = _stage_a(cb, tame, env)
-    assert info2["variant"] == 2 and info2["overflow"] == 0
+    assert info2["variant"] == 2 and info2["flags"] == 0
 
 
 @pytest.mark.parametrize("nall", [2, 15, 16, 17, 127, 128, 129, 255, 257, 1025])
@@ -625,7 +687,7 @@ def test_full_size_properties_c5(cb, oracle):
     ctx.pairs(env)
     links = ctx.download(want_xyz=True)
     info = ctx.info(env)
-    assert info["variant"] == 2 and info["overflow"] == 0
+    assert info["variant"] == 2 and info["flags"] == 0
     assert links["npairs"] == n * (n - 1) // 2
     dup = links["dup"]
     assert np.all(dup <= np.arange(n))
