@@ -5,8 +5,11 @@ A step = one pass of the hot path over the whole synthetic ensemble, inputs resi
   kernel (1) pack/axis + TF32 operand conversion  ->  kernels (2)+(3): tensor-core screen + exact
   FP64 pass over this rank's shard of the in-band work list  ->  all-reduce(MAX) of dup[] over
   ranks (NCCL, N>1 only)  ->  kernel (4) backtrack.
-`value` = pairs whose (proper+mirror) RMSD was evaluated by ALL ranks / device time (max over
-ranks).  `e2e` runs the same step from HOST buffers (H2D of xyz/er, D2H of rot/dup) every step.
+`value` = in-band pairs CLASSIFIED by all ranks (the TF32 screen dismisses most of them with a proof,
+the rest get an exact FP64 RMSD: `kernels.candidates`, `kernels.exact_evaluations`) / device time (max
+over ranks).  `e2e` = the one-call C ABI crest_cuda_cregen_dup (what the Fortran shim binds) from
+PAGEABLE host buffers, H2D of xyz/er and D2H of rot/dup inside the timed region; at N > 1 it is the
+single-process engine (crest_cuda_init(N)) driven by rank 0 while the other ranks idle.
 `--impl reference` times the CPU restatement of the reference loops (oracle/, OpenMP, all host
 cores) on a bounded row sample of the same workload; the reference itself is Fortran and cannot be
 built in this image.
@@ -41,6 +44,7 @@ def parse():
     p.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU-baseline sample time")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-fp64", action="store_true", help="skip the FP64-only pass reported in kernels.fp64_path")
     return p.parse_args()
 
 
@@ -135,6 +139,14 @@ class ClockSampler:
         return out
 
 
+def host_cores():
+    """Cores this process may use (torchrun exports OMP_NUM_THREADS=1; the affinity mask is the truth)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def cpu_sample(ens, args, seconds):
     """Time the oracle's reference-shaped pair loop (serial i, OpenMP j, two rmsd() per pair,
     float32 store; oracle/oracle_capi.cpp: oracle_pair_rows <- reference src/cregen.f90:1269-1322)
@@ -145,6 +157,7 @@ def cpu_sample(ens, args, seconds):
     if ens["heavy"]:
         xyz = np.ascontiguousarray(xyz[:, at != 1, :])
     nall = xyz.shape[0]
+    O.set_num_threads(host_cores())          # never inherit OMP_NUM_THREADS=1 from the launcher
     cores = O.num_threads()
     # calibrate on a few rows, then size the sample for ~`seconds`
     r0 = max(1, min(8, nall - 1))
@@ -184,6 +197,7 @@ def run_reference(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_s / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": workload_config(args, ens), "cpu_baseline": cb,
+            "cores": cb["cores"],
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), file=_OUT, flush=True)
@@ -244,11 +258,32 @@ def tf32_peak_tflops(torch, dev):
     return 2.0 * n ** 3 / (best * 1e-3) / 1e12
 
 
+def measured_peaks():
+    """MEASURED_PEAKS.json (driver-written: HBM copy GB/s and dense bf16 TFLOP/s of this pool's B200s)."""
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return None
+
+
+def tracked_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the tracked
+    ncu --set full summary profiles/traffic.json ({workload: {bytes, kernel, commit, source}}); null when
+    no capture of this workload is committed (nothing is pasted into this file)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f).get(workload)
+        return t
+    except (OSError, ValueError):
+        return None
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
     import crest_b200 as cb
-    from crest_b200 import synth
+    from crest_b200 import synth, cregen
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -257,8 +292,10 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    cpu_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+        cpu_group = dist.new_group(backend="gloo")     # host-side barrier: idle ranks must not spin on their GPU
 
     ens = synth.make_config(args.workload, nall=args.nall)
     at, xyz, er = ens["at"], ens["xyz"], ens["er"]
@@ -310,7 +347,7 @@ def run_ours(args):
     clocks = sampler.stop() if sampler else None
     ms_total = t_beg.elapsed_time(t_end)
     pair_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
-    # pairs evaluated in the last step (device counter is zeroed by pack), summed over ranks
+    # pairs classified in the last step (device counter is zeroed by pack), summed over ranks
     if world > 1:
         npl = np_t.clone()
         dist.all_reduce(npl, op=dist.ReduceOp.SUM)
@@ -325,115 +362,138 @@ def run_ours(args):
     res = ctx.download()
     ms_step = ms_total / args.steps
     value = pairs_step / (ms_step * 1e-3)
+    launches_step = int(info["launches"])
 
-    # ---- end to end from host buffers through the context API (H2D + D2H inside the timed region)
+    # ---- the FP64-only formulation of the same step (north_star: "fraction of the FP64 tensor roofline"):
+    # DMMA kernels, every in-band pair gets its exact FP64 covariance.  Skipped above 1e10 pairs (C5: 18 s).
+    fp64_path = None
+    if rank == 0 and pairs_step <= 1.0e10 and not args.no_fp64:
+        cregen.set_tune("notf32")
+        c64 = cb.CregenContext(local)
+        c64.upload(env, at, xyz, er)
+        c64.pack(stream)
+        c64.pairs(env, 0, 1, False, stream)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        c64.pairs(env, 0, 1, False, stream)
+        e1.record()
+        torch.cuda.synchronize()
+        ms64 = e0.elapsed_time(e1)
+        i64 = c64.info(env)
+        same = bool(np.array_equal(c64.download()["dup"] != 0, res["dup"] != 0)) if world == 1 else None
+        c64.close()
+        cregen.set_tune(None)
+        fp64_path = {"pair_stage_ms": ms64, "pairs_per_s": pairs_step / (ms64 * 1e-3),
+                     "variant": {0: "pair_tile (DMMA row tiles)", 1: "pair_col (DMMA column sweep)"}.get(i64["variant"]),
+                     "same_duplicates_as_screen_path": same}
+
+    # ---- end to end: the ONE-CALL C ABI from pageable host buffers (what a Fortran caller has); at N > 1
+    # the single-process engine on N GPUs, driven by rank 0 while the other ranks wait on the host
     e2e = None
-    if not args.no_e2e:
-        xyz_p = torch.from_numpy(xyz).pin_memory().numpy()
-        er_p = torch.from_numpy(er).pin_memory().numpy()
-
-        if world == 1:
-            # the call the Fortran shim binds: one C-ABI call, host buffers in, host buffers out
-            api = "crest_cuda_cregen_dup (one-call C ABI), pinned host buffers in / host buffers out"
-
-            def e2e_step():
-                return cb.cregen_dup(env, nat, nall, at, xyz_p, er_p, want_xyz=False)
-        else:
-            api = ("CregenContext.upload_rows (1/N of xyz per rank over PCIe) + NCCL all_gather + pack + "
-                   "pairs + all_reduce(MAX) + sweep + download (crest_cuda_ctx_*), host buffers")
-
-            rec = 3 * nat
-
-            def e2e_step():
-                chunk, first, count = ctx.upload_rows(env, at, xyz_p, er_p, rank, world)
-                full = torch.as_tensor(_DevArray(ctx.xyz_devptr(), chunk * world * rec, "<f8"), device=dev)
-                dist.all_gather_into_tensor(full, full[rank * chunk * rec:(rank + 1) * chunk * rec])
-                step()
-                return ctx.download()
-        e2e_step()
-        sync_all()
-        # every step is timed on its own (host clock around the synchronous call, barrier on both
-        # sides, max over ranks); the value is quoted on the MEDIAN step because a host-side stall
-        # of tens of ms hits one call in a few on a shared box -- mean and max are reported beside it
-        n_e2e = max(1, min(args.steps, 10))
-        dts = []
-        for _ in range(n_e2e):
-            sync_all()
-            t0 = time.perf_counter()
-            r2 = e2e_step()
-            sync_all()
-            dts.append(time.perf_counter() - t0)
-        if world > 1:
-            tt = torch.tensor(dts, dtype=torch.float64, device=dev)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            dts = [float(x) for x in tt]
-        dt = float(np.median(dts))
-        if rank == 0:
-            print("e2e step times (ms):", " ".join(f"{x * 1e3:.2f}" for x in dts), file=sys.stderr)
-        e2e = {"value": pairs_step / dt, "unit": UNIT,
-               "h2d_bytes_per_step": int(xyz.nbytes + world * (er.nbytes + at.nbytes)),
-               "d2h_bytes_per_step": int(nall * 4 + nall * 24 + 8), "ms_per_step": dt * 1e3,
-               "ms_per_step_mean": float(np.mean(dts)) * 1e3, "ms_per_step_max": float(np.max(dts)) * 1e3,
-               "steps": n_e2e, "statistic": "median of per-step times", "api": api}
-        assert np.array_equal(r2["dup"], res["dup"])
-
-    # ---- whole cregen_CRE (duplicates + partition + enuc + rotamer groups) from host buffers:
-    # the "CREGEN wall time" half of the metric, N = 1 only (stage B is one sequential sweep)
     cregen_wall = None
-    if world == 1 and not args.no_e2e:
-        # the call works in place like the reference's cregen_CRE (xyz, er are permuted), so every
-        # repetition gets its own copy of the inputs, made outside the timed region
-        walls = []
-        for _ in range(6):
-            xyz_io, er_io = xyz.copy(), er.copy()
-            t0 = time.perf_counter()
-            full = cb.cregen_CRE_inplace(env, nat, nall, at, xyz_io, er_io)
-            walls.append(time.perf_counter() - t0)
-        cregen_wall = {"ms": min(walls[1:]) * 1e3, "ms_median": float(np.median(walls[1:])) * 1e3,
-                       "api": "crest_cuda_cregen_cre (one call, pageable host buffers, in place like the "
-                              "reference; best of 5 after one warm-up call, median beside it)", "kept": int(full.nallout),
-                       "groups": int(full.group[0])}
+    if not args.no_e2e:
+        if world > 1:
+            dist.barrier(group=cpu_group)
+        if rank == 0:
+            used = cb.init(world)
+            api = (f"crest_cuda_init({world}) + crest_cuda_cregen_dup (one-call C ABI, one host thread drives "
+                   f"{used} GPU(s)), pageable host buffers in / host buffers out")
+
+            def e2e_step(x=xyz, e=er):
+                return cb.cregen_dup(env, nat, nall, at, x, e, want_xyz=False)
+            r2 = e2e_step()
+            n_e2e = max(1, min(args.steps, 10))
+            dts = []
+            for _ in range(n_e2e):
+                t0 = time.perf_counter()
+                r2 = e2e_step()
+                dts.append(time.perf_counter() - t0)
+            dt = float(np.median(dts))
+            print("e2e step times (ms):", " ".join(f"{x * 1e3:.2f}" for x in dts), file=sys.stderr)
+            assert np.array_equal(r2["dup"], res["dup"]) and r2["npairs"] == pairs_step
+            e2e = {"value": pairs_step / dt, "unit": UNIT,
+                   "h2d_bytes_per_step": int(xyz.nbytes + used * (er.nbytes + at.nbytes)),
+                   "d2h_bytes_per_step": int(nall * 4 + nall * 24 + 8 * used), "ms_per_step": dt * 1e3,
+                   "ms_per_step_mean": float(np.mean(dts)) * 1e3, "ms_per_step_max": float(np.max(dts)) * 1e3,
+                   "steps": n_e2e, "statistic": "median of per-call wall times", "api": api, "gpus_used": used,
+                   "host_memory": "pageable"}
+            # the same call from PINNED caller memory (no staging threads; what a CUDA-aware caller could do)
+            xyz_p = torch.from_numpy(xyz).pin_memory().numpy()
+            er_p = torch.from_numpy(er).pin_memory().numpy()
+            e2e_step(xyz_p, er_p)
+            dtp = []
+            for _ in range(max(1, n_e2e // 2)):
+                t0 = time.perf_counter()
+                e2e_step(xyz_p, er_p)
+                dtp.append(time.perf_counter() - t0)
+            e2e["ms_per_step_pinned"] = float(np.median(dtp)) * 1e3
+            del xyz_p, er_p
+            # whole cregen_CRE (duplicates + partition + enuc + rotamer groups): the "CREGEN wall time" half
+            # of the metric.  The call works in place like the reference (xyz, er are permuted), so every
+            # repetition gets its own copy of the inputs, made outside the timed region
+            walls = []
+            for _ in range(6):
+                xyz_io, er_io = xyz.copy(), er.copy()
+                t0 = time.perf_counter()
+                full = cb.cregen_CRE_inplace(env, nat, nall, at, xyz_io, er_io)
+                walls.append(time.perf_counter() - t0)
+            cregen_wall = {"ms": min(walls[1:]) * 1e3, "ms_median": float(np.median(walls[1:])) * 1e3,
+                           "api": "crest_cuda_cregen_cre (one call, pageable host buffers, in place like the "
+                                  "reference; best of 5 after one warm-up call, median beside it)",
+                           "gpus_used": used, "kept": int(full.nallout), "groups": int(full.group[0])}
+            cb.finalize()
+        if world > 1:
+            dist.barrier(group=cpu_group)
 
     if rank == 0:
         A = info["A"]
         fp64_peak = fp64_peak_tflops(torch, dev)
         achieved = 18.0 * A * my_pairs / (pair_ms * 1e-3) / 1e12
         variant = {0: "pair_tile (DMMA row tiles)", 1: "pair_col (DMMA column sweep)",
-                   2: "pair_tf32 (tcgen05 TF32 screen) + exact_cand (FP64 list)"}[info["variant"]]
-        # dram__bytes_read.sum + dram__bytes_write.sum of pair_tf32_kernel<8>, one launch, from the
-        # committed ncu --set full capture of this command (profiles/r01_v13_pair_tf32_ncu_full_summary.txt)
-        traffic = (234556416 + 6808320 if (info["variant"] == 2 and args.workload == "C3" and
-                                           args.nall is None and world == 1 and args.ethr > 1e8) else None)
+                   2: "pair_tf32 (tcgen05 TF32 screen) + cand_scan (top-down exact FP64) + DMMA on dense leftovers"}[info["variant"]]
+        tr = tracked_traffic(args.workload) if (args.nall is None and world == 1 and args.ethr > 1e8) else None
+        mp = measured_peaks()
         if info["variant"] == 2:
-            peak = tf32_peak_tflops(torch, dev)
-            note = ("tensor roofline of the dominant kernel pair_tf32_kernel (tcgen05.mma kind::tf32): "
-                    "18*A FLOP per pair x pairs of rank 0 / pair-stage time (CUDA events around "
-                    "pair_tf32 + exact_cand + the conditional fallback launch); peak = cuBLAS TF32 GEMM "
-                    "8192^3 measured in this run (MEASURED_PEAKS.json has bf16 only). The kernel is "
-                    "bound by the FP32 screen arithmetic of its epilogue warps, not by the tensor "
-                    "pipe (DESIGN.md 4); fp64_tensor_equiv = the same FLOP against the measured DGEMM "
-                    "peak, i.e. what an FP64-only formulation could reach at most")
+            tf32_cublas = tf32_peak_tflops(torch, dev)
+            if mp and mp.get("bf16_tflops"):
+                peak = 0.5 * float(mp["bf16_tflops"])
+                peak_src = "MEASURED_PEAKS.json bf16_tflops / 2 (TF32 dense is half the bf16 rate; burst figure)"
+            else:
+                peak = tf32_cublas
+                peak_src = "cuBLAS TF32 GEMM 8192^3 measured in this run (MEASURED_PEAKS.json absent)"
+            note = ("tensor roofline of the dominant kernel pair_tf32_kernel (tcgen05.mma kind::tf32): 18*A FLOP "
+                    "per pair x pairs of rank 0 / pair-stage time (CUDA events on the launch stream around "
+                    "pair_tf32 + classify + cand_scan + expand + the DMMA launch for dense leftovers); the "
+                    "kernel is bound by the FP32 screen arithmetic of its epilogue warps, not by the tensor "
+                    "pipe (DESIGN.md 4.3)")
         else:
+            tf32_cublas = None
             peak = fp64_peak
-            note = ("FP64 tensor (DMMA) roofline: 18*A FLOP per pair x pairs of rank 0 / pair kernel "
-                    "time (CUDA events); peak = cuBLAS DGEMM 6144^3 measured in this run "
-                    "(MEASURED_PEAKS.json has no FP64 figure)")
+            peak_src = "cuBLAS DGEMM 6144^3 measured in this run (MEASURED_PEAKS.json has no FP64 figure)"
+            note = "FP64 tensor (DMMA) roofline: 18*A FLOP per pair x pairs of rank 0 / pair kernel time (CUDA events)"
+        if fp64_path:
+            fp64_path["tflops"] = 18.0 * A * fp64_path["pairs_per_s"] / 1e12
+            fp64_path["dgemm_peak_tflops"] = fp64_peak
+            fp64_path["frac_of_fp64_tensor_roofline"] = fp64_path["tflops"] / fp64_peak
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "scaling": "strong", "vs_baseline": None,
+            "dtype": "tf32-screen+f64-exact" if info["variant"] == 2 else "f64", "data": "synthetic",
             "config": workload_config(args, ens),
             "pairs_per_step": pairs_step, "duplicates_found": int((res["dup"] != 0).sum()),
-            "gpu_launches": int(info["launches"] * args.steps),
+            "gpu_launches": launches_step * args.steps,
             "kernels": {"variant": variant, "pair_stage_ms": pair_ms, "grid": info["grid"],
                         "smem": info["smem"], "items_this_rank": info["tiles_shard"],
-                        "atoms_padded": info["A_padded"], "launches_per_step": info["launches"],
-                        "candidates": info["candidates"], "exact_evaluations": info["exact_evals"],
-                        "dense_items": info["dense_items"], "flags": info["flags"]},
+                        "atoms_padded": info["A_padded"], "launches_per_step": launches_step,
+                        "candidates": info["candidates"], "candidate_fraction": info["candidates"] / max(my_pairs, 1),
+                        "exact_evaluations": info["exact_evals"],
+                        "dense_items": info["dense_items"], "flags": info["flags"], "fp64_path": fp64_path},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": achieved / peak, "traffic": traffic,
-                         "fp64_tensor_peak": fp64_peak, "fp64_tensor_equiv": achieved / fp64_peak,
-                         "note": note},
+                         "frac": achieved / peak, "traffic": tr["bytes"] if tr else None,
+                         "traffic_source": tr, "peak_source": peak_src, "cublas_tf32_tflops": tf32_cublas,
+                         "fp64_tensor_peak": fp64_peak, "note": note},
             "clocks": clocks, "e2e": e2e, "cregen_wall": cregen_wall,
         }
         if world == 1 and not args.no_cpu_baseline:
@@ -443,6 +503,7 @@ def run_ours(args):
         print(json.dumps(line), file=_OUT, flush=True)
     ctx.close()
     if world > 1:
+        dist.barrier(group=cpu_group)
         dist.destroy_process_group()
 
 

@@ -30,6 +30,9 @@ class CrestCudaError(RuntimeError):
 # every symbol include/crest_cuda.h declares: (restype, argtypes)
 _THR = C.POINTER(Thresholds)
 SYMBOLS = {
+    "crest_cuda_init": (C.c_int, [C.c_int, c_ip]),
+    "crest_cuda_finalize": (None, []),
+    "crest_cuda_ngpu": (C.c_int, []),
     "crest_cuda_cregen_dup": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp, c_ip, C.c_int, C.c_int,
                                         _THR, c_dp, c_dp, c_ip, c_llp]),
     "crest_cuda_cregen_group": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp, c_dp, _THR, c_ip, c_dp]),

@@ -71,6 +71,24 @@ def __getattr__(name):            # module-level lazy constants
     raise AttributeError(name)
 
 
+def init(ngpu=0):
+    """crest_cuda_init: the engine of 1-8 GPUs behind the one-call entry points (cregen_CRE, cregen_dup,
+    ...), driven by this one host thread like CREST's serial region.  ngpu <= 0: every visible GPU,
+    1: the current device.  Returns the number of GPUs in use."""
+    used = C.c_int(0)
+    _lib.check(_lib.lib().crest_cuda_init(int(ngpu), C.byref(used)))
+    return used.value
+
+
+def finalize():
+    """crest_cuda_finalize: release the engine (device buffers, streams, pinned staging)."""
+    _lib.lib().crest_cuda_finalize()
+
+
+def ngpu():
+    return _lib.lib().crest_cuda_ngpu()
+
+
 def set_tune(spec=None):
     """Developer knobs of the pair kernels (crest_cuda_set_tune); None restores the defaults."""
     _lib.lib().crest_cuda_set_tune(spec.encode() if spec else None)

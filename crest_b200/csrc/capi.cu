@@ -2,8 +2,8 @@
 // copies, the host-side band/tile bookkeeping (reference src/cregen.f90:1240-1256) and the exact
 // float32-threshold emulation (cregen.f90:1286,1359-1367).  No CPU fallback lives here: every
 // compute entry point needs a CUDA device and fails otherwise.
-#include "../../include/crest_cuda.h"
-#include "common.cuh"
+#include "ctx.cuh"
+#include "hostcopy.cuh"
 #include <cmath>
 #include <cstdarg>
 #include <cstdlib>
@@ -63,6 +63,8 @@ static void parse_tune(const char* e, Tune& t) {
   if (std::strstr(e, "seqgroup")) t.seq_group = 1;
   if (std::strstr(e, "forcedense")) t.force_dense = 1;
   if (std::strstr(e, "nodense")) t.no_dense = 1;
+  if (std::strstr(e, "nostage")) t.no_stage = 1;
+  if (const char* q = std::strstr(e, "blocks=")) if (std::sscanf(q + 7, "%d", &v) == 1) t.blocks = v;
   if (const char* q = std::strstr(e, "densebudget=")) if (std::sscanf(q + 12, "%d", &v) == 1) t.dense_budget = v;
   if (const char* q = std::strstr(e, "maskmb=")) if (std::sscanf(q + 7, "%d", &v) == 1) t.mask_mb = v;
   if (const char* q = std::strstr(e, "packg=")) if (std::sscanf(q + 6, "%d", &v) == 1) t.pack_g = v;
@@ -103,59 +105,6 @@ static Gates make_gates(const crest_cuda_thresholds& t, int enantio, int A) {
 }  // namespace crest
 
 using namespace crest;
-
-struct crest_cuda_ctx {
-  int device = 0;
-  int nat = 0, nall = 0, nsel = 0, rot_from_mask = 0;
-  PackLayout L{};
-  std::vector<double> h_er;
-  // device buffers
-  int* d_at = nullptr;
-  int* d_sel = nullptr;
-  double* d_xyz = nullptr;
-  double* d_xyz_axis = nullptr;
-  double* d_er = nullptr;
-  double* d_rot = nullptr;
-  double* d_aniso = nullptr;
-  double* d_X = nullptr;
-  double* d_xn = nullptr;
-  int* d_dup = nullptr;
-  unsigned long long* d_npairs = nullptr;
-  long long* d_rowstart = nullptr;
-  int* d_jfirst = nullptr;
-  unsigned long long* d_mask = nullptr;
-  float* d_rmat = nullptr;
-  size_t cap_xyz = 0, cap_conf = 0, cap_X = 0, cap_at = 0, cap_rows = 0, cap_mask = 0;
-  // tile list (host)
-  std::vector<long long> rowstart;
-  std::vector<int> jfirst;
-  double tiles_ethr = std::numeric_limits<double>::quiet_NaN();
-  // column-sweep kernel work list (pair_col.cu): {J, u_begin, u_end, edge} quadruples
-  bool use_col = false;
-  std::vector<int> items;
-  int* d_items = nullptr;
-  size_t cap_items = 0;
-  double items_ethr = std::numeric_limits<double>::quiet_NaN();
-  long long launches = 0;
-  int last_grid = 0, last_smem = 0;
-  // tensor-core screen (pair_tf32.cu): TF32 operand copies, candidate list, its own work list
-  bool use_tf32 = false;
-  int ntile = 0;                       // i-tiles of 128 conformers
-  Tf32Buffers tf{};
-  size_t cap_tf_x = 0, cap_tf_hn = 0;
-  unsigned long long* d_npairs_scratch = nullptr;   // pair counter of a fallback re-run (discarded)
-  std::vector<int> tf_items;
-  int* d_tf_items = nullptr;
-  size_t cap_tf_items = 0;
-  double tf_items_ethr = std::numeric_limits<double>::quiet_NaN();
-  int tf_items_nranks = 0;     // the item size depends on the number of ranks sharing the list
-  // d_X padding (atom slots beyond the selection, rows beyond nall) is zeroed once per layout: pack
-  // rewrites every used slot of every live row on each call and nothing else writes d_X
-  bool X_zeroed = false;
-  PackLayout X_zero_L{};
-  int X_zero_nall = -1;
-  int last_variant = 0;                // 0 row-tile DMMA, 1 column DMMA, 2 TF32 screen + exact list
-};
 
 namespace {
 
@@ -248,10 +197,12 @@ void col_items_host(int n, const double* er, double ethr, std::vector<int>& item
 // gated pair by pair (cregen.f90:1275); the rest of the band needs no energies at all.  The list is
 // cut on a fixed grid of `chunk` groups and ordered segment-major so that concurrently running CTAs
 // stream the same j-groups (L2-resident) past different i-tiles.
-int tf_items_host(int n, const double* er, double ethr, std::vector<int>& items, int nranks = 1) {
-  items.clear();
+// tile0/tile1: the list of a STAGE, i.e. only the i-tiles [tile0, tile1) (appended to `items`).
+int tf_items_host(int n, const double* er, double ethr, std::vector<int>& items, int nranks = 1,
+                  int tile0 = 0, int tile1 = -1) {
   if (n < 2) return 8;
   const int ntile = (n + 127) / 128;
+  if (tile1 < 0 || tile1 > ntile) tile1 = ntile;
   std::vector<int> gb(ntile, 0), ge(ntile, 0), gg(ntile, 0);
   // first j in [0, i] with (er[i]-er[j])*autokcal < ethr; i+1 if none (monotone: er ascends)
   auto first_in_band = [&](int i) {
@@ -263,7 +214,7 @@ int tf_items_host(int n, const double* er, double ethr, std::vector<int>& items,
     return lo;
   };
   long long total = 0;
-  for (int I = 0; I < ntile; ++I) {
+  for (int I = tile0; I < tile1; ++I) {
     const int i0 = I * 128, ilast = std::min(i0 + 127, n - 1), jhi = ilast - 1;
     if (jhi < 0) continue;
     const int jlo = first_in_band(i0);
@@ -279,11 +230,11 @@ int tf_items_host(int n, const double* er, double ethr, std::vector<int>& items,
   chunk = chunk / 8 * 8;       // segments are whole 128-column blocks of the candidate bitmask
   if (chunk < 8) chunk = 8;
   if (chunk > 256) chunk = 256;
-  const int ngroup = ntile * 8;
+  const int ngroup = tile1 * 8;
   const int nseg = (int)((ngroup + chunk - 1) / chunk);
   for (int sg = 0; sg < nseg; ++sg) {
     const int s0 = (int)(sg * chunk), s1 = (int)std::min<long long>((sg + 1) * chunk, ngroup);
-    for (int I = ntile - 1; I >= 0; --I) {
+    for (int I = tile1 - 1; I >= tile0; --I) {
       const int b = std::max(gb[I], s0), e = std::min(ge[I], s1);
       if (b < e) { items.push_back(I); items.push_back(b); items.push_back(e); items.push_back(gg[I]); }
     }
@@ -291,8 +242,25 @@ int tf_items_host(int n, const double* er, double ethr, std::vector<int>& items,
   return (int)chunk;
 }
 
-int upload_tf_items(crest_cuda_ctx* c, double ethr, int nranks, cudaStream_t st) {
-  c->tf.chunk = tf_items_host(c->nall, c->h_er.data(), ethr, c->tf_items, nranks);
+}  // namespace
+
+namespace crest {
+int plan_stages(crest_cuda_ctx* c, double ethr, int nranks, const std::vector<int>& bounds, cudaStream_t st) {
+  if (c->tf_items_ethr == ethr && c->tf_items_nranks == nranks && c->stage_tile == bounds) return 0;
+  const int nstage = (int)bounds.size() - 1;
+  c->tf_items.clear();
+  c->stage_item.assign(1, 0);
+  c->stage_chunk.clear();
+  size_t nd = 1, per_item_max = 1;
+  for (int s = 0; s < nstage; ++s) {
+    const int chunk = tf_items_host(c->nall, c->h_er.data(), ethr, c->tf_items, nranks, bounds[s], bounds[s + 1]);
+    c->stage_chunk.push_back(chunk);
+    c->stage_item.push_back((int)(c->tf_items.size() / 4));
+    const size_t nseg = ((size_t)bounds[s + 1] * 8 + chunk - 1) / chunk;
+    nd = std::max(nd, nseg * (size_t)c->ntile);
+    per_item_max = std::max(per_item_max, (size_t)(chunk / 4 + 1) * (c->use_col ? 8 : 4));
+  }
+  c->stage_tile = bounds;
   c->tf_items_ethr = ethr;
   c->tf_items_nranks = nranks;
   const size_t n = c->tf_items.size();
@@ -307,15 +275,12 @@ int upload_tf_items(crest_cuda_ctx* c, double ethr, int nranks, cudaStream_t st)
   if (n) CREST_CUDA_TRY(cudaMemcpyAsync(c->d_tf_items, c->tf_items.data(), sizeof(int) * n,
                                         cudaMemcpyHostToDevice, st));
   // verdict per (segment, i-tile) and the work list of the FP64 tensor kernel for dense items
-  const size_t nseg = ((size_t)c->ntile * 8 + c->tf.chunk - 1) / c->tf.chunk;
-  const size_t nd = nseg * (size_t)c->ntile;
   if (nd > c->tf.dense_cap) {
     cudaFree(c->tf.dense); c->tf.dense = nullptr; c->tf.dense_cap = 0;
     CREST_CUDA_TRY(cudaMalloc(&c->tf.dense, nd));
     c->tf.dense_cap = nd;
   }
-  const size_t per_item = (size_t)(c->tf.chunk / 4 + 1) * (c->use_col ? 8 : 4);
-  size_t want = std::min<size_t>((n / 4) * per_item, (size_t)32 << 20);
+  size_t want = std::min<size_t>((n / 4) * per_item_max, (size_t)32 << 20);
   if (want < 1024) want = 1024;
   if (want > c->tf.dense_items_cap) {
     cudaFree(c->tf.dense_items); c->tf.dense_items = nullptr; c->tf.dense_items_cap = 0;
@@ -324,6 +289,9 @@ int upload_tf_items(crest_cuda_ctx* c, double ethr, int nranks, cudaStream_t st)
   }
   return 0;
 }
+}  // namespace crest
+
+namespace {
 
 int upload_items(crest_cuda_ctx* c, double ethr, cudaStream_t st) {
   col_items_host(c->nall, c->h_er.data(), ethr, c->items);
@@ -356,13 +324,15 @@ int upload_tiles(crest_cuda_ctx* c, cudaStream_t st) {
   return 0;
 }
 
+}  // namespace
+
+namespace crest {
 int check_thr(const crest_cuda_thresholds* t) {
   if (!t) { set_error("thresholds pointer is NULL"); return 1; }
   if (!(t->rthr == t->rthr) || !(t->ethr == t->ethr)) { set_error("NaN threshold"); return 1; }
   return 0;
 }
-
-}  // namespace
+}  // namespace crest
 
 extern "C" {
 
@@ -466,115 +436,6 @@ void crest_cuda_ctx_destroy(crest_cuda_ctx* c) {
   delete c;
 }
 
-// ---- large transfers from / to PAGEABLE caller memory (Fortran arrays are never pinned) ---------
-// cudaMemcpy stages pageable memory through one driver thread (measured 11 GB/s H2D, 17 GB/s D2H on
-// the B200 box for the 144 MB of C3).  Here T host threads each own a slice of the transfer, two
-// pinned 4 MB slots and a stream: memcpy into / out of a slot overlaps the DMA of the other slot.
-// Pinned or registered caller memory goes straight to cudaMemcpy.  CREST_CUDA_COPY_THREADS=0 turns
-// the staging off, =n sets T (default 4).  The threads only copy memory; they exist for the
-// duration of the call (no pool that would compete with the caller's OpenMP teams).
-static int copy_threads() {
-  static int env_t = -1;
-  if (env_t < 0) {
-    const char* e = std::getenv("CREST_CUDA_COPY_THREADS");
-    env_t = e ? std::atoi(e) : 4;
-    if (env_t < 0) env_t = 0;
-  }
-  int t = tune().copy_threads >= 0 ? tune().copy_threads : env_t;   // CREST_CUDA_TUNE copythr=<n>
-  const int hw = (int)std::thread::hardware_concurrency();
-  if (hw > 0 && t > hw) t = hw;
-  if (t > 16) t = 16;
-  return t;
-}
-
-struct CopySlots {          // process lifetime: 2 x 4 MB pinned per thread
-  static constexpr size_t kChunk = 4u << 20;
-  void* slot[16][2] = {};
-  int device = -1;
-  bool ensure(int T, int dev) {
-    if (device != dev) {
-      for (auto& s : slot) for (void*& q : s) if (q) { cudaFreeHost(q); q = nullptr; }
-      device = dev;
-    }
-    for (int t = 0; t < T; ++t)
-      for (int k = 0; k < 2; ++k)
-        if (!slot[t][k] && cudaMallocHost(&slot[t][k], kChunk) != cudaSuccess) { cudaGetLastError(); return false; }
-    return true;
-  }
-};
-static CopySlots g_slots;
-
-// dir 0: host -> device, 1: device -> host.  Returns 0 ok, 1 error (text set).
-static int big_copy(void* dst, const void* src, size_t bytes, int dir, int device) {
-  const cudaMemcpyKind kind = dir ? cudaMemcpyDeviceToHost : cudaMemcpyHostToDevice;
-  const void* host = dir ? dst : src;
-  int T = copy_threads();
-  cudaPointerAttributes at{};
-  const bool pageable = cudaPointerGetAttributes(&at, host) != cudaSuccess ||
-                        at.type == cudaMemoryTypeUnregistered;
-  cudaGetLastError();
-  if (bytes < (32u << 20) || T == 0 || !pageable || !g_slots.ensure(T, device)) {
-    CREST_CUDA_TRY(cudaMemcpy(dst, src, bytes, kind));
-    return 0;
-  }
-  const size_t C = CopySlots::kChunk;
-  const size_t nchunk = (bytes + C - 1) / C;
-  std::vector<int> err((size_t)T, 0);
-  auto work = [&](int t) {
-    if (cudaSetDevice(device) != cudaSuccess) { err[t] = 1; return; }
-    cudaStream_t st;
-    cudaEvent_t ev[2];
-    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) { err[t] = 1; return; }
-    cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming);
-    // chunks t, t+T, t+2T, ... (interleaved: all threads stream through neighbouring pages)
-    bool ok = true;
-    if (dir == 0) {
-      int k = 0;
-      for (size_t c = (size_t)t; c < nchunk && ok; c += (size_t)T, k ^= 1) {
-        const size_t off = c * C, len = bytes - off < C ? bytes - off : C;
-        ok = cudaEventSynchronize(ev[k]) == cudaSuccess;          // slot k free again
-        std::memcpy(g_slots.slot[t][k], (const char*)src + off, len);
-        ok = ok && cudaMemcpyAsync((char*)dst + off, g_slots.slot[t][k], len, kind, st) == cudaSuccess;
-        ok = ok && cudaEventRecord(ev[k], st) == cudaSuccess;
-      }
-    } else {
-      // prime one DMA, then: issue the next chunk's DMA, copy the finished one out
-      size_t c = (size_t)t;
-      int k = 0;
-      auto issue = [&](size_t cc, int kk) {
-        const size_t off = cc * C, len = bytes - off < C ? bytes - off : C;
-        return cudaMemcpyAsync(g_slots.slot[t][kk], (const char*)src + off, len, kind, st) == cudaSuccess &&
-               cudaEventRecord(ev[kk], st) == cudaSuccess;
-      };
-      if (c < nchunk) ok = issue(c, k);
-      for (; c < nchunk && ok; c += (size_t)T, k ^= 1) {
-        const size_t nxt = c + (size_t)T;
-        if (nxt < nchunk) ok = issue(nxt, k ^ 1);
-        ok = ok && cudaEventSynchronize(ev[k]) == cudaSuccess;
-        const size_t off = c * C, len = bytes - off < C ? bytes - off : C;
-        std::memcpy((char*)dst + off, g_slots.slot[t][k], len);
-      }
-    }
-    ok = ok && cudaStreamSynchronize(st) == cudaSuccess;
-    cudaEventDestroy(ev[0]); cudaEventDestroy(ev[1]);
-    cudaStreamDestroy(st);
-    if (!ok) err[t] = 1;
-  };
-  CREST_CUDA_TRY(cudaDeviceSynchronize());     // the side streams do not order against the null stream
-  std::vector<std::thread> th;
-  for (int t = 1; t < T; ++t) th.emplace_back(work, t);
-  work(0);
-  for (auto& x : th) x.join();
-  for (int t = 0; t < T; ++t)
-    if (err[t]) {
-      set_error("staged %s copy of %zu bytes failed: %s", dir ? "D2H" : "H2D", bytes,
-                cudaGetErrorString(cudaGetLastError()));
-      return 1;
-    }
-  return 0;
-}
-
 int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, const double* xyz,
                           const double* er, const int* rmsd_mask, int rot_from_mask) {
   if (!c) { set_error("ctx is NULL"); return 1; }
@@ -598,6 +459,8 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
   c->L = c->use_col ? make_col_layout(c->nsel, nall) : make_layout(c->nsel, nall);
   c->items_ethr = std::numeric_limits<double>::quiet_NaN();
   c->tf_items_ethr = std::numeric_limits<double>::quiet_NaN();
+  c->stage_tile.clear();
+  c->dup_target = nullptr;
   c->use_tf32 = !tune().no_tf32 && nall >= 2;
   if (c->use_col) { c->tf.nslab = 1; c->tf.kslab = c->L.KU; }
   else { c->tf.kslab = kTfSlabSlots; c->tf.nslab = (c->L.nslab * c->L.KU + kTfSlabSlots - 1) / kTfSlabSlots; }
@@ -661,7 +524,7 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
     // 2 GB, CREST_CUDA_TUNE maskmb=<MB>), else passes of whole segments; never less than one segment
     // of 4096 columns.  Zeroed once: cand_scan_kernel clears what the screen sets.
     {
-      const size_t full = tf32_mask_words(nall, 0, nall);
+      const size_t full = tf32_mask_words(0, nall, 0, nall);
       const size_t budget = ((size_t)(tune().mask_mb > 0 ? tune().mask_mb : 2048) << 20) / sizeof(unsigned);
       const size_t one_seg = (size_t)nall * 128;
       const size_t want = std::max<size_t>(std::min(full, std::max(budget, one_seg)), 128);
@@ -705,9 +568,10 @@ int crest_cuda_ctx_upload_xyz_rows(crest_cuda_ctx* c, int first, int count, cons
 
 void* crest_cuda_ctx_xyz_devptr(crest_cuda_ctx* c) { return c ? (void*)c->d_xyz : nullptr; }
 
-int crest_cuda_ctx_pack(crest_cuda_ctx* c, void* stream) {
-  if (!c) { set_error("ctx is NULL"); return 1; }
-  cudaStream_t st = (cudaStream_t)stream;
+}  // extern "C"
+
+namespace crest {
+int begin_call(crest_cuda_ctx* c, cudaStream_t st) {
   CREST_CUDA_TRY(cudaSetDevice(c->device));
   // padding rows / atoms of X must be zero: they enter the MMA (atoms) or are masked (rows)
   if (!c->X_zeroed || std::memcmp(&c->L, &c->X_zero_L, sizeof(PackLayout)) != 0 ||
@@ -717,22 +581,54 @@ int crest_cuda_ctx_pack(crest_cuda_ctx* c, void* stream) {
   }
   CREST_CUDA_TRY(cudaMemsetAsync(c->d_dup, 0, sizeof(int) * (size_t)(c->nall ? c->nall : 1), st));
   CREST_CUDA_TRY(cudaMemsetAsync(c->d_npairs, 0, sizeof(unsigned long long), st));
-  c->launches = 0;
-  if (launch_pack_axis(c->nat, c->nall, c->d_at, c->d_xyz, c->d_sel, c->nsel, c->rot_from_mask,
-                       c->L, c->d_xyz_axis, c->d_rot, c->d_aniso, c->d_X, c->d_xn, st))
-    return 1;
-  if (c->nall > 0) c->launches += 1;
   if (c->use_tf32) {
-    if (launch_tf32_convert(c->d_X, c->d_xn, c->nall, c->L, c->ntile, c->tf.nslab, c->tf.kslab, c->tf.kappa,
+    CREST_CUDA_TRY(cudaMemsetAsync(c->tf.cand_count, 0, sizeof(unsigned) * 8, st));
+  }
+  c->launches = 0;
+  return 0;
+}
+
+int pack_rows(crest_cuda_ctx* c, int r0, int r1, cudaStream_t st) {
+  if (r1 <= r0) return 0;
+  if (r0 % 128 != 0) { set_error("pack_rows: row block must start on a 128-row tile"); return 1; }
+  const size_t rec = (size_t)3 * c->nat;
+  const size_t xoff = (size_t)(r0 / c->L.rows) * c->L.nslab * c->L.chunk_doubles();
+  if (launch_pack_axis(c->nat, r1 - r0, c->d_at, c->d_xyz + rec * r0, c->d_sel, c->nsel, c->rot_from_mask,
+                       c->L, c->d_xyz_axis + rec * r0, c->d_rot + (size_t)3 * r0, c->d_aniso + r0,
+                       c->d_X + xoff, c->d_xn + r0, st))
+    return 1;
+  c->launches += 1;
+  if (c->use_tf32) {
+    const int t0 = r0 / 128, t1 = (r1 + 127) / 128;
+    if (launch_tf32_convert(c->d_X, c->d_xn, c->nall, c->L, t0, t1, c->tf.nslab, c->tf.kslab, c->tf.kappa,
                             c->tf.Xa, c->tf.Xb, c->tf.hn, c->tf.cand_count + 4, st))
       return 1;
     c->launches += 1;
   }
   return 0;
 }
+}  // namespace crest
 
-static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_thresholds* thr, int rank,
-                      int nranks, int want_mask, float* d_rmat, cudaStream_t st) {
+extern "C" {
+
+int crest_cuda_ctx_pack(crest_cuda_ctx* c, void* stream) {
+  if (!c) { set_error("ctx is NULL"); return 1; }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (begin_call(c, st)) return 1;
+  return pack_rows(c, 0, c->nall, st);
+}
+
+}  // extern "C"
+
+namespace crest {
+bool tf32_path(const crest_cuda_ctx* c, int want_mask, const float* d_rmat) {
+  const char* dbg = std::getenv("CREST_CUDA_DEBUG");
+  const int debug = dbg ? std::atoi(dbg) : 0;
+  return c->use_tf32 && !want_mask && !d_rmat && debug != 1 && debug != 2;
+}
+
+int pairs_stage(crest_cuda_ctx* c, int enantio, const crest_cuda_thresholds* thr, int rank, int nranks,
+                int stage, int want_mask, float* d_rmat, cudaStream_t st) {
   if (check_thr(thr)) return 1;
   if (nranks < 1 || rank < 0 || rank >= nranks) { set_error("bad shard %d/%d", rank, nranks); return 1; }
   CREST_CUDA_TRY(cudaSetDevice(c->device));
@@ -740,24 +636,25 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
   PairArgs a{};
   a.X = c->d_X; a.xn = c->d_xn; a.er = c->d_er; a.rot = c->d_rot; a.aniso = c->d_aniso;
   a.nall = c->nall;
-  a.dup = c->d_dup; a.npairs = c->d_npairs;
+  a.dup = c->dup_target ? c->dup_target : c->d_dup; a.npairs = c->d_npairs;
   a.mask = nullptr; a.n8 = (c->nall + 7) / 8;
   a.rmat = d_rmat;
   a.g = make_gates(*thr, enantio, c->nsel);
   a.L = c->L;
   a.dbg = nullptr;
   a.work_count = nullptr; a.tiles = nullptr;
-  const bool tf32_path = c->use_tf32 && !want_mask && !d_rmat && a.g.debug != 1 && a.g.debug != 2;
-  if (tf32_path) {
-    // tensor-core screen -> per-item verdict -> FP64 tensor kernel on dense items -> top-down exact
-    // scan of the candidate bitmask (pair_tf32.cu), pass by pass over this rank's slice of the list
-    if (!(c->tf_items_ethr == thr->ethr && c->tf_items_nranks == nranks) &&
-        upload_tf_items(c, thr->ethr, nranks, st)) return 1;
-    const long long Ttf = (long long)(c->tf_items.size() / 4);
+  if (tf32_path(c, want_mask, d_rmat)) {
+    // tensor-core screen -> per-item verdict -> top-down exact scan of the candidate bitmask -> FP64
+    // tensor kernel on what dense items left unfinished (pair_tf32.cu), pass by pass over this rank's
+    // slice of the stage's list
+    if (c->stage_tile.empty() || !(c->tf_items_ethr == thr->ethr && c->tf_items_nranks == nranks)) {
+      const std::vector<int> one{0, c->ntile};
+      if (plan_stages(c, thr->ethr, nranks, one, st)) return 1;
+    }
+    if (stage < 0 || stage + 1 >= (int)c->stage_tile.size()) { set_error("bad stage %d", stage); return 1; }
+    const long long i0 = c->stage_item[stage], i1 = c->stage_item[stage + 1];
     long long tb = 0, te = 0;
-    crest_cuda_shard_range(Ttf, rank, nranks, &tb, &te);
-    CREST_CUDA_TRY(cudaMemsetAsync(c->tf.cand_count, 0, sizeof(unsigned) * 4, st));
-    CREST_CUDA_TRY(cudaMemsetAsync(c->tf.cand_count + 5, 0, sizeof(unsigned) * 3, st));
+    crest_cuda_shard_range(i1 - i0, rank, nranks, &tb, &te);
     if (a.g.debug == 3 && !c->tf.fmask) {
       CREST_CUDA_TRY(cudaMalloc(&c->tf.fmask, sizeof(unsigned) * c->tf.cm_words));
     }
@@ -765,12 +662,16 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
     fb.npairs = c->d_npairs_scratch;      // the screen already counted these pairs
     int nsf = 0;
     if (!c->use_col) pair_smem_bytes(c->L, &nsf);
-    if (launch_pair_tf32(a, fb, c->tf, c->d_tf_items, c->tf_items.data(), (int)tb, (int)te,
-                         a.g.debug == 3, nsf, st, &c->last_grid, &c->last_smem, &c->launches))
+    Tf32Buffers tb_ = c->tf;
+    tb_.chunk = c->stage_chunk[stage];
+    const int row_lo = c->stage_tile[stage] * 128, row_hi = std::min(c->stage_tile[stage + 1] * 128, c->nall);
+    if (launch_pair_tf32(a, fb, tb_, c->d_tf_items, c->tf_items.data(), (int)(i0 + tb), (int)(i0 + te),
+                         row_lo, row_hi, a.g.debug == 3, nsf, st, &c->last_grid, &c->last_smem, &c->launches))
       return 1;
     c->last_variant = 2;
     return 0;
   }
+  if (stage != 0) { set_error("the FP64-only kernels run as one stage"); return 1; }
   if (c->use_col) {
     if (!(c->items_ethr == thr->ethr) && upload_items(c, thr->ethr, st)) return 1;
   } else if (!(c->tiles_ethr == thr->ethr)) {
@@ -818,11 +719,14 @@ static int pairs_impl(crest_cuda_ctx* c, int enantio, const crest_cuda_threshold
   if (c->last_grid > 0) c->launches += 1;
   return 0;
 }
+}  // namespace crest
+
+extern "C" {
 
 int crest_cuda_ctx_pairs(crest_cuda_ctx* c, int enantio, const crest_cuda_thresholds* thr,
                          int rank, int nranks, int want_mask, void* stream) {
   if (!c) { set_error("ctx is NULL"); return 1; }
-  return pairs_impl(c, enantio, thr, rank, nranks, want_mask, nullptr, (cudaStream_t)stream);
+  return pairs_stage(c, enantio, thr, rank, nranks, 0, want_mask, nullptr, (cudaStream_t)stream);
 }
 
 void* crest_cuda_ctx_dup_devptr(crest_cuda_ctx* c) { return c ? (void*)c->d_dup : nullptr; }
@@ -877,7 +781,7 @@ int crest_cuda_ctx_info(crest_cuda_ctx* c, const crest_cuda_thresholds* thr, int
   }
   long long T = c->use_col ? (long long)(c->items.size() / 4)
                            : (c->rowstart.empty() ? 0 : c->rowstart.back());
-  if (c->last_variant == 2) T = (long long)(c->tf_items.size() / 4);
+  if (c->last_variant == 2) T = (long long)(c->tf_items.size() / 4);   // all stages
   long long tb = 0, te = 0;
   crest_cuda_shard_range(T, rank, nranks, &tb, &te);
   info[7] = c->last_variant;
@@ -907,235 +811,6 @@ int crest_cuda_ctx_download_mask(crest_cuda_ctx* c, unsigned long long* mask, vo
                                  cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   CREST_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
   return 0;
-}
-
-// ------------------------------------------------------------------------------------------
-// One-call entry points on a process-global context (device buffers are reused across the
-// 5-20 CREGEN calls of one conformer search).
-// ------------------------------------------------------------------------------------------
-static crest_cuda_ctx* g_ctx = nullptr;
-static int global_ctx(crest_cuda_ctx** out) {
-  if (!g_ctx && crest_cuda_ctx_create(&g_ctx, -1)) return 1;
-  *out = g_ctx;
-  return 0;
-}
-
-int crest_cuda_cregen_dup(int nat, int nall, const int* at, const double* xyz, const double* er,
-                          const int* rmsd_mask, int rot_from_mask, int enantio,
-                          const crest_cuda_thresholds* thr, double* rot, double* xyz_axis,
-                          int* dup, long long* npairs) {
-  crest_cuda_ctx* c;
-  if (check_thr(thr)) return 1;
-  if (global_ctx(&c)) return 1;
-  if (crest_cuda_ctx_upload(c, nat, nall, at, xyz, er, rmsd_mask, rot_from_mask)) return 1;
-  if (crest_cuda_ctx_pack(c, nullptr)) return 1;
-  if (crest_cuda_ctx_pairs(c, enantio, thr, 0, 1, 0, nullptr)) return 1;
-  if (crest_cuda_ctx_sweep(c, nullptr)) return 1;
-  return crest_cuda_ctx_download(c, rot, xyz_axis, dup, npairs, nullptr);
-}
-
-int crest_cuda_cregen_group(int nat, int nkept, const int* at, const double* xyz,
-                            const double* er, const double* rot,
-                            const crest_cuda_thresholds* thr, int* group, double* enuc) {
-  if (check_thr(thr)) return 1;
-  if (nat <= 0 || nkept < 0 || !at || !group) { set_error("bad argument"); return 1; }
-  crest_cuda_ctx* c;
-  if (global_ctx(&c)) return 1;
-  CREST_CUDA_TRY(cudaSetDevice(c->device));
-  if (nkept == 0) { group[0] = 0; return 0; }
-  if (!xyz || !er || !rot) { set_error("NULL input array"); return 1; }
-  int* d_at = nullptr; double *d_xyz = nullptr, *d_er = nullptr, *d_rot = nullptr, *d_enuc = nullptr;
-  int* d_group = nullptr;
-  const size_t n = nkept;
-  int rc = 1;
-  do {
-    if (cudaMalloc(&d_at, sizeof(int) * nat) != cudaSuccess) break;
-    if (cudaMalloc(&d_xyz, sizeof(double) * 3 * nat * n) != cudaSuccess) break;
-    if (cudaMalloc(&d_er, sizeof(double) * n) != cudaSuccess) break;
-    if (cudaMalloc(&d_rot, sizeof(double) * 3 * n) != cudaSuccess) break;
-    if (cudaMalloc(&d_enuc, sizeof(double) * n) != cudaSuccess) break;
-    if (cudaMalloc(&d_group, sizeof(int) * (n + 1)) != cudaSuccess) break;
-    if (cudaMemcpy(d_at, at, sizeof(int) * nat, cudaMemcpyHostToDevice) != cudaSuccess) break;
-    if (cudaMemcpy(d_xyz, xyz, sizeof(double) * 3 * nat * n, cudaMemcpyHostToDevice) != cudaSuccess) break;
-    if (cudaMemcpy(d_er, er, sizeof(double) * n, cudaMemcpyHostToDevice) != cudaSuccess) break;
-    if (cudaMemcpy(d_rot, rot, sizeof(double) * 3 * n, cudaMemcpyHostToDevice) != cudaSuccess) break;
-    if (launch_enuc(nat, nkept, d_at, d_xyz, d_enuc, 0)) { rc = 2; break; }
-    if (launch_group(nkept, d_er, d_rot, d_enuc, thr->ethr, thr->bthr, thr->bthrmax,
-                     thr->bthrshift, d_group, 0)) { rc = 2; break; }
-    if (cudaMemcpy(group, d_group, sizeof(int) * (n + 1), cudaMemcpyDeviceToHost) != cudaSuccess) break;
-    if (enuc && cudaMemcpy(enuc, d_enuc, sizeof(double) * n, cudaMemcpyDeviceToHost) != cudaSuccess) break;
-    rc = 0;
-  } while (0);
-  if (rc == 1) set_error("CUDA error in cregen_group: %s", cudaGetErrorString(cudaGetLastError()));
-  cudaFree(d_at); cudaFree(d_xyz); cudaFree(d_er); cudaFree(d_rot); cudaFree(d_enuc); cudaFree(d_group);
-  return rc;
-}
-
-int crest_cuda_cregen_cre(int nat, int nall, const int* at, double* xyz, double* er,
-                          const int* rmsd_mask, int rot_from_mask, int enantio, int nosort,
-                          const crest_cuda_thresholds* thr, double* rot, int* order, int* group,
-                          int* nallout, long long* npairs) {
-  if (!rot || !order || !group || !nallout) { set_error("NULL output array"); return 1; }
-  if (check_thr(thr)) return 1;
-  crest_cuda_ctx* c;
-  if (global_ctx(&c)) return 1;
-  // CREST_CUDA_TIMING=1: phase wall times of this call on stderr (developer aid; adds syncs)
-  static const bool timing = getenv("CREST_CUDA_TIMING") && atoi(getenv("CREST_CUDA_TIMING")) > 0;
-  auto t_last = std::chrono::steady_clock::now();
-  auto lap = [&](const char* what) {
-    if (!timing) return;
-    cudaDeviceSynchronize();
-    const auto now = std::chrono::steady_clock::now();
-    fprintf(stderr, "[cregen_cre] %-28s %8.3f ms\n", what,
-            std::chrono::duration<double, std::milli>(now - t_last).count());
-    t_last = now;
-  };
-  // stage A on the device; only the link array (4 B per structure) comes back for the partition
-  if (crest_cuda_ctx_upload(c, nat, nall, at, xyz, er, rmsd_mask, rot_from_mask)) return 1;
-  lap("upload (H2D xyz)");
-  if (crest_cuda_ctx_pack(c, nullptr)) return 1;
-  lap("pack_axis + tf32_convert");
-  if (crest_cuda_ctx_pairs(c, enantio, thr, 0, 1, 0, nullptr)) return 1;
-  lap("pair stage");
-  if (crest_cuda_ctx_sweep(c, nullptr)) return 1;
-  std::vector<int> dup((size_t)(nall > 0 ? nall : 1));
-  if (crest_cuda_ctx_download(c, nullptr, nullptr, dup.data(), npairs, nullptr)) return 1;
-  lap("backtrack + D2H dup");
-  for (int i = 0; i <= nall; ++i) group[i] = 0;
-  if (nall == 0) { *nallout = 0; return 0; }
-  // kept-first partition, duplicates appended in reverse encounter order (cregen.f90:1397-1419)
-  int ndup = 0;
-  for (int i = 0; i < nall; ++i) ndup += dup[i] != 0;
-  int nout = nall - ndup;
-  std::vector<int> src((size_t)nall);
-  if (nosort) {
-    nout = nall;
-    for (int i = 0; i < nall; ++i) { order[i] = i + 1; src[i] = i; }
-  } else {
-    int j = 0, l = nall + 1;
-    for (int i = 0; i < nall; ++i) {
-      order[i] = (dup[i] == 0) ? ++j : --l;
-      src[order[i] - 1] = i;
-    }
-  }
-  // permutation, K5 and K6 on the device; geometry crosses PCIe once per direction
-  const size_t n = (size_t)nall;
-  int *d_src = nullptr, *d_group = nullptr;
-  double *d_er2 = nullptr, *d_rot2 = nullptr, *d_enuc = nullptr;
-  int rc = 1;
-  do {
-    if (cudaMalloc(&d_src, sizeof(int) * n) != cudaSuccess) break;
-    if (cudaMalloc(&d_group, sizeof(int) * (n + 1)) != cudaSuccess) break;
-    if (cudaMalloc(&d_er2, sizeof(double) * n) != cudaSuccess) break;
-    if (cudaMalloc(&d_rot2, sizeof(double) * 3 * n) != cudaSuccess) break;
-    if (cudaMalloc(&d_enuc, sizeof(double) * n) != cudaSuccess) break;
-    if (cudaMemcpy(d_src, src.data(), sizeof(int) * n, cudaMemcpyHostToDevice) != cudaSuccess) break;
-    // d_xyz (the input copy) is free now: it receives the permuted principal-axis geometries
-    lap("partition (host) + alloc");
-    if (launch_permute(nat, nall, d_src, c->d_xyz_axis, c->d_er, c->d_rot, c->d_xyz, d_er2, d_rot2, 0)) { rc = 2; break; }
-    lap("permute");
-    if (cudaMemset(d_group, 0, sizeof(int) * (n + 1)) != cudaSuccess) break;
-    if (launch_enuc(nat, nout, c->d_at, c->d_xyz, d_enuc, 0)) { rc = 2; break; }
-    lap("enuc");
-    if (launch_group(nout, d_er2, d_rot2, d_enuc, thr->ethr, thr->bthr, thr->bthrmax, thr->bthrshift,
-                     d_group, 0)) { rc = 2; break; }
-    lap("group");
-    if (big_copy(xyz, c->d_xyz, sizeof(double) * 3 * nat * n, 1, c->device)) { rc = 2; break; }
-    lap("D2H xyz");
-    if (cudaMemcpy(er, d_er2, sizeof(double) * n, cudaMemcpyDeviceToHost) != cudaSuccess) break;
-    if (cudaMemcpy(rot, d_rot2, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost) != cudaSuccess) break;
-    if (cudaMemcpy(group, d_group, sizeof(int) * ((size_t)nout + 1), cudaMemcpyDeviceToHost) != cudaSuccess) break;
-    rc = 0;
-  } while (0);
-  if (rc == 1) set_error("CUDA error in cregen_cre: %s", cudaGetErrorString(cudaGetLastError()));
-  cudaFree(d_src); cudaFree(d_group); cudaFree(d_er2); cudaFree(d_rot2); cudaFree(d_enuc);
-  if (rc) return rc;
-  c->launches += 3;
-  if (nosort) nout = group[0];
-  *nallout = nout;
-  return 0;
-}
-
-int crest_cuda_rotconst(int nat, int n, const int* at, const double* xyz, double* rot) {
-  if (nat <= 0 || n < 0 || !at || !rot || (!xyz && n)) { set_error("bad argument"); return 1; }
-  crest_cuda_ctx* c;
-  if (global_ctx(&c)) return 1;
-  CREST_CUDA_TRY(cudaSetDevice(c->device));
-  if (n == 0) return 0;
-  int* d_at = nullptr; double *d_xyz = nullptr, *d_rot = nullptr;
-  CREST_CUDA_TRY(cudaMalloc(&d_at, sizeof(int) * nat));
-  CREST_CUDA_TRY(cudaMalloc(&d_xyz, sizeof(double) * 3 * nat * (size_t)n));
-  CREST_CUDA_TRY(cudaMalloc(&d_rot, sizeof(double) * 3 * (size_t)n));
-  CREST_CUDA_TRY(cudaMemcpy(d_at, at, sizeof(int) * nat, cudaMemcpyHostToDevice));
-  CREST_CUDA_TRY(cudaMemcpy(d_xyz, xyz, sizeof(double) * 3 * nat * (size_t)n, cudaMemcpyHostToDevice));
-  int rc = launch_rotconst(nat, n, d_at, d_xyz, d_rot, 0);
-  if (!rc && cudaMemcpy(rot, d_rot, sizeof(double) * 3 * (size_t)n, cudaMemcpyDeviceToHost) != cudaSuccess) {
-    set_error("D2H failed: %s", cudaGetErrorString(cudaGetLastError()));
-    rc = 1;
-  }
-  cudaFree(d_at); cudaFree(d_xyz); cudaFree(d_rot);
-  return rc;
-}
-
-int crest_cuda_rmsd_pairs(int A, int n, const double* packed, long long npairs, const int* i_idx,
-                          const int* j_idx, double* rmsd, double* rmsd_mirror) {
-  if (A <= 0 || n <= 0 || npairs < 0 || !packed || !rmsd || !rmsd_mirror) {
-    set_error("bad argument"); return 1;
-  }
-  crest_cuda_ctx* c;
-  if (global_ctx(&c)) return 1;
-  CREST_CUDA_TRY(cudaSetDevice(c->device));
-  if (npairs == 0) return 0;
-  for (long long p = 0; p < npairs; ++p)
-    if (i_idx[p] < 0 || i_idx[p] >= n || j_idx[p] < 0 || j_idx[p] >= n) {
-      set_error("pair %lld index out of range", p); return 1;
-    }
-  double *d_p = nullptr, *d_r = nullptr, *d_m = nullptr; int *d_i = nullptr, *d_j = nullptr;
-  CREST_CUDA_TRY(cudaMalloc(&d_p, sizeof(double) * 3 * A * (size_t)n));
-  CREST_CUDA_TRY(cudaMalloc(&d_r, sizeof(double) * npairs));
-  CREST_CUDA_TRY(cudaMalloc(&d_m, sizeof(double) * npairs));
-  CREST_CUDA_TRY(cudaMalloc(&d_i, sizeof(int) * npairs));
-  CREST_CUDA_TRY(cudaMalloc(&d_j, sizeof(int) * npairs));
-  CREST_CUDA_TRY(cudaMemcpy(d_p, packed, sizeof(double) * 3 * A * (size_t)n, cudaMemcpyHostToDevice));
-  CREST_CUDA_TRY(cudaMemcpy(d_i, i_idx, sizeof(int) * npairs, cudaMemcpyHostToDevice));
-  CREST_CUDA_TRY(cudaMemcpy(d_j, j_idx, sizeof(int) * npairs, cudaMemcpyHostToDevice));
-  int rc = launch_rmsd_pairs(A, n, d_p, npairs, d_i, d_j, d_r, d_m, 0);
-  if (!rc) {
-    if (cudaMemcpy(rmsd, d_r, sizeof(double) * npairs, cudaMemcpyDeviceToHost) != cudaSuccess ||
-        cudaMemcpy(rmsd_mirror, d_m, sizeof(double) * npairs, cudaMemcpyDeviceToHost) != cudaSuccess) {
-      set_error("D2H failed: %s", cudaGetErrorString(cudaGetLastError()));
-      rc = 1;
-    }
-  }
-  cudaFree(d_p); cudaFree(d_r); cudaFree(d_m); cudaFree(d_i); cudaFree(d_j);
-  return rc;
-}
-
-int crest_cuda_rmsdalign(int nat, int nall, const int* at, double* xyz) {
-  if (nat <= 0 || nall < 0 || !at || (!xyz && nall)) { set_error("bad argument"); return 1; }
-  crest_cuda_ctx* c;
-  if (global_ctx(&c)) return 1;
-  CREST_CUDA_TRY(cudaSetDevice(c->device));
-  if (nall <= 1) return 0;
-  int* d_at = nullptr; double* d_xyz = nullptr;
-  const size_t bytes = sizeof(double) * 3 * nat * (size_t)nall;
-  CREST_CUDA_TRY(cudaMalloc(&d_at, sizeof(int) * nat));
-  if (cudaMalloc(&d_xyz, bytes) != cudaSuccess) {
-    cudaFree(d_at);
-    set_error("cudaMalloc failed: %s", cudaGetErrorString(cudaGetLastError()));
-    return 1;
-  }
-  int rc = 1;
-  do {
-    if (cudaMemcpy(d_at, at, sizeof(int) * nat, cudaMemcpyHostToDevice) != cudaSuccess) break;
-    if (cudaMemcpy(d_xyz, xyz, bytes, cudaMemcpyHostToDevice) != cudaSuccess) break;
-    if (launch_rmsdalign(nat, nall, d_at, d_xyz, 0)) { rc = 2; break; }
-    if (cudaMemcpy(xyz, d_xyz, bytes, cudaMemcpyDeviceToHost) != cudaSuccess) break;
-    rc = 0;
-  } while (0);
-  if (rc == 1) set_error("CUDA error in rmsdalign: %s", cudaGetErrorString(cudaGetLastError()));
-  cudaFree(d_at); cudaFree(d_xyz);
-  return rc;
 }
 
 // Host-side: the reference's energy sort is an UNSTABLE Hoare quicksort with middle pivot
@@ -1194,28 +869,6 @@ int crest_cuda_cregen_esort(int nat, int nall, double* xyz, double* energies, do
   }
   *nallout = nout;
   return 0;
-}
-
-int crest_cuda_rmat_allpairs(int nat, int nall, const int* at, const double* xyz,
-                             const int* rmsd_mask, int enantio, float* rmat) {
-  if (!rmat) { set_error("rmat is NULL"); return 1; }
-  crest_cuda_ctx* c;
-  if (global_ctx(&c)) return 1;
-  std::vector<double> er((size_t)(nall > 0 ? nall : 1), 0.0);
-  if (crest_cuda_ctx_upload(c, nat, nall, at, xyz, er.data(), rmsd_mask, 0)) return 1;
-  if (crest_cuda_ctx_pack(c, nullptr)) return 1;
-  const size_t np = (size_t)nall * (nall > 0 ? nall - 1 : 0) / 2;
-  if (np == 0) return 0;
-  float* d_rmat = nullptr;
-  CREST_CUDA_TRY(cudaMalloc(&d_rmat, sizeof(float) * np));
-  crest_cuda_thresholds t{1e300, 0.0, 0.0, 0.0, 0.0};
-  int rc = pairs_impl(c, enantio, &t, 0, 1, 0, d_rmat, nullptr);
-  if (!rc && cudaMemcpy(rmat, d_rmat, sizeof(float) * np, cudaMemcpyDeviceToHost) != cudaSuccess) {
-    set_error("D2H failed: %s", cudaGetErrorString(cudaGetLastError()));
-    rc = 1;
-  }
-  cudaFree(d_rmat);
-  return rc;
 }
 
 }  // extern "C"

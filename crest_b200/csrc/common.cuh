@@ -33,7 +33,7 @@ struct PackLayout {
 
 // Developer knobs (env CREST_CUDA_TUNE="slab=<8-atom blocks per slab>,stages=<n>,dist=<n>,skew=<clk>"),
 // read once; 0 = automatic.  Used to A/B the pipeline shape on the GPU box without rebuilding.
-struct Tune { int force_dense = 0, no_dense = 0, mask_mb = 0, dense_budget = 0, slab_blocks = 0, stages = 0, dist = 0, skew = -1, force_tile = 0, no_half = 0, no_tf32 = 0, cand_cap = 0, chunk = 0, seq_group = 0, group_cap = 0, copy_threads = -1, pack_g = 0; };
+struct Tune { int blocks = 0, no_stage = 0, force_dense = 0, no_dense = 0, mask_mb = 0, dense_budget = 0, slab_blocks = 0, stages = 0, dist = 0, skew = -1, force_tile = 0, no_half = 0, no_tf32 = 0, cand_cap = 0, chunk = 0, seq_group = 0, group_cap = 0, copy_threads = -1, pack_g = 0; };
 const Tune& tune();
 void set_tune(const char* spec);   // re-parse the knobs (tests A/B kernel variants in one process)
 
@@ -174,18 +174,21 @@ struct Tf32Buffers {
 };
 constexpr int kTfSlabSlots = 48;
 int tf32_smem_bytes(int KU, int* nbstage_out);
+// i-tiles [tile0, tile1); *d_unsafe is only ever set (the caller zeroes it once per call)
 int launch_tf32_convert(const double* d_X, const double* d_xn, int nall, const PackLayout& L,
-                        int ntile, int nslab_t, int kslab, double kappa, float* d_Xa, float* d_Xb,
-                        float* d_hn, unsigned* d_unsafe, cudaStream_t stream);
+                        int tile0, int tile1, int nslab_t, int kslab, double kappa, float* d_Xa,
+                        float* d_Xb, float* d_hn, unsigned* d_unsafe, cudaStream_t stream);
 double tf32_kappa(int kslots);
 // items = device array of {I, g_begin, g_end, g_gate_end} int quadruples
 // h_items = host copy of the list (the launcher cuts [item_begin, item_end) into passes of whole
 // segments whose candidate bitmask fits tb.cm_words); fb = arguments of the FP64 tensor kernel that
 // re-does dense items (its own pair counter); launches_out += kernels launched
+// rows [row_lo, row_hi) = the i-tiles the items belong to (a stage; 0, nall for the whole ensemble)
 int launch_pair_tf32(const PairArgs& a, const PairArgs& fb, const Tf32Buffers& tb, const void* d_items,
-                     const int* h_items, int item_begin, int item_end, int all_cand, int nstage_tile,
-                     cudaStream_t stream, int* grid_out, int* smem_out, long long* launches_out);
-size_t tf32_mask_words(int nall, int col0, int col_end);
+                     const int* h_items, int item_begin, int item_end, int row_lo, int row_hi,
+                     int all_cand, int nstage_tile, cudaStream_t stream, int* grid_out, int* smem_out,
+                     long long* launches_out);
+size_t tf32_mask_words(int row_lo, int row_hi, int col0, int col_end);
 int launch_backtrack(int nall, int* d_dup, cudaStream_t stream);
 int launch_rmsd_pairs(int A, int n, const double* d_packed, long long npairs, const int* d_i,
                       const int* d_j, double* d_rmsd, double* d_rmsd_m, cudaStream_t stream);

@@ -185,7 +185,7 @@ __device__ __forceinline__ void unit_exact(const ColArgs& a, const ColWarp& w,
             if (!dupl)
               dupl = equalrotaniso_dev(a.rot + 3 * (size_t)i, a.rot + 3 * (size_t)j, a.aniso[i],
                                        a.aniso[j], a.g.bthr_half, a.g.bthrmax, a.g.bthrshift);
-            if (dupl) atomicMax(a.dup + i, j + 1);
+            if (dupl) atomicMax_system(a.dup + i, j + 1);
           }
         }
       }

@@ -601,14 +601,14 @@ struct XView {
 // One thread per (conformer, TF32 slab, comp, 4-slot chunk).  TF32 slot t = FP64 slot t (slabs of the
 // FP64 layout concatenated); kslab slots per TF32 slab, zero beyond the FP64 extent.
 __global__ void __launch_bounds__(256)
-tf32_convert_kernel(const XView xv, const double* __restrict__ xn, int nall, int ntile, int nslab_t,
+tf32_convert_kernel(const XView xv, const double* __restrict__ xn, int nall, int tile0, int ntile, int nslab_t,
                     int kslab, float* __restrict__ Xa, float* __restrict__ Xb,
                     float* __restrict__ hn, double kappa, unsigned* __restrict__ unsafe) {
   const int nchunk = kslab >> 2;
   const long long total = (long long)ntile * 128 * 3 * nchunk * nslab_t;
   const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid < (long long)ntile * 128) {
-    const int i = (int)tid;
+    const int i = tile0 * 128 + (int)tid;
     const float h = i < nall ? __double2float_rd(0.5 * xn[i] * (1.0 - kappa)) : 0.0f;
     hn[i] = h;
     // the screen's sign tests assume finite FP32 arithmetic: lam = hn_i + hn_j + cE < 1e9 keeps every
@@ -622,7 +622,7 @@ tf32_convert_kernel(const XView xv, const double* __restrict__ xn, int nall, int
   const int c = (int)(rest % nchunk); rest /= nchunk;
   const int comp = (int)(rest % 3); rest /= 3;
   const int sl = (int)(rest % nslab_t);
-  const int I = (int)(rest / nslab_t);
+  const int I = tile0 + (int)(rest / nslab_t);
   const int i = I * 128 + r;
   float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
   const int t = sl * kslab + 4 * c;                   // first of 4 consecutive slots (same FP64 slab)
@@ -780,7 +780,7 @@ cand_scan_kernel(const ScanArgs a) {
         }
       }
     }
-    if (lane == 0 && m > m0) atomicMax(a.dup + i, m);
+    if (lane == 0 && m > m0) atomicMax_system(a.dup + i, m);
     if (lane == 0 && gave_up && !done) a.unfinished[i] = 1;
   }
   n_eval = __reduce_add_sync(0xffffffffu, n_eval);
@@ -901,13 +901,13 @@ double tf32_kappa(int kslots) {
 }
 
 int launch_tf32_convert(const double* d_X, const double* d_xn, int nall, const PackLayout& L,
-                        int ntile, int nslab_t, int kslab, double kappa, float* d_Xa, float* d_Xb,
-                        float* d_hn, unsigned* d_unsafe, cudaStream_t stream) {
-  CREST_CUDA_TRY(cudaMemsetAsync(d_unsafe, 0, sizeof(unsigned), stream));
+                        int tile0, int tile1, int nslab_t, int kslab, double kappa, float* d_Xa,
+                        float* d_Xb, float* d_hn, unsigned* d_unsafe, cudaStream_t stream) {
+  const int ntile = tile1 - tile0;
   const long long total = (long long)ntile * 128 * 3 * (kslab / 4) * nslab_t;
   if (total <= 0) return 0;
   const int blocks = (int)((total + 255) / 256);
-  tf32_convert_kernel<<<blocks, 256, 0, stream>>>(make_xview(d_X, L), d_xn, nall, ntile, nslab_t, kslab,
+  tf32_convert_kernel<<<blocks, 256, 0, stream>>>(make_xview(d_X, L), d_xn, nall, tile0, ntile, nslab_t, kslab,
                                                   d_Xa, d_Xb, d_hn, kappa, d_unsafe);
   CREST_CUDA_TRY(cudaGetLastError());
   return 0;
@@ -935,8 +935,9 @@ static long long mask_stride(int col0, int col_end) {
   const long long w = ((long long)(col_end - col0) + 31) / 32;
   return (w + 127) / 128 * 128;
 }
-size_t tf32_mask_words(int nall, int col0, int col_end) {
-  return (size_t)(nall - col0 > 0 ? nall - col0 : 0) * (size_t)mask_stride(col0, col_end);
+size_t tf32_mask_words(int row_lo, int row_hi, int col0, int col_end) {
+  const int r0 = row_lo > col0 ? row_lo : col0;
+  return (size_t)(row_hi > r0 ? row_hi - r0 : 0) * (size_t)mask_stride(col0, col_end);
 }
 
 static int launch_tf32_screen(const TfArgs& a, bool slab, int grid, int smem, cudaStream_t stream) {
@@ -972,8 +973,9 @@ static int launch_tf32_screen(const TfArgs& a, bool slab, int grid, int smem, cu
 // run from the highest columns down so that links found in one pass prune the candidates of the next:
 //   pair_tf32 screen -> classify_items -> FP64 tensor kernel on dense items -> cand_scan (top-down)
 int launch_pair_tf32(const PairArgs& pa, const PairArgs& fb_in, const Tf32Buffers& tb, const void* d_items,
-                     const int* h_items, int item_begin, int item_end, int all_cand, int nstage_tile,
-                     cudaStream_t stream, int* grid_out, int* smem_out, long long* launches_out) {
+                     const int* h_items, int item_begin, int item_end, int row_lo, int row_hi,
+                     int all_cand, int nstage_tile, cudaStream_t stream, int* grid_out, int* smem_out,
+                     long long* launches_out) {
   if (grid_out) *grid_out = 0;
   if (item_end - item_begin <= 0) return 0;
   TfArgs a{};
@@ -1011,13 +1013,13 @@ int launch_pair_tf32(const PairArgs& pa, const PairArgs& fb_in, const Tf32Buffer
   while (pe > item_begin) {
     // grow the pass downwards by whole segments while its bitmask fits
     const int s_hi = seg_of(pe - 1);
-    const int col_end = std::min((s_hi + 1) * segcols, pa.nall);
+    const int col_end = std::min((s_hi + 1) * segcols, row_hi);
     int pb = pe, s_lo = s_hi;
     for (;;) {
       int q = pb;
       const int s = seg_of(q - 1);
       while (q > item_begin && seg_of(q - 1) == s) --q;
-      if (tf32_mask_words(pa.nall, s * segcols, col_end) > tb.cm_words) {
+      if (tf32_mask_words(row_lo, row_hi, s * segcols, col_end) > tb.cm_words) {
         if (pb == pe) { set_error("candidate bitmask too small for one segment (%zu words)", tb.cm_words); return 1; }
         break;
       }
@@ -1026,13 +1028,14 @@ int launch_pair_tf32(const PairArgs& pa, const PairArgs& fb_in, const Tf32Buffer
     }
     const int col0 = s_lo * segcols;
     a.item_begin = pb; a.item_end = pe;
-    a.cm_row0 = col0; a.cm_col0 = col0; a.cm_stride = mask_stride(col0, col_end);
+    const int row0 = std::max(row_lo, col0);
+    a.cm_row0 = row0; a.cm_col0 = col0; a.cm_stride = mask_stride(col0, col_end);
     const int nitems = pe - pb;
     const int grid = nitems < nsm ? nitems : nsm;
     if (grid > grid_max) grid_max = grid;
     CREST_CUDA_TRY(cudaMemsetAsync(tb.cand_count + 6, 0, sizeof(unsigned), stream));
     if (all_cand)
-      CREST_CUDA_TRY(cudaMemsetAsync(tb.fmask, 0, sizeof(unsigned) * tf32_mask_words(pa.nall, col0, col_end), stream));
+      CREST_CUDA_TRY(cudaMemsetAsync(tb.fmask, 0, sizeof(unsigned) * tf32_mask_words(row_lo, row_hi, col0, col_end), stream));
     if (launch_tf32_screen(a, slab, grid, smem, stream)) return 1;
     ClassifyArgs c{};
     c.items = a.items; c.item_begin = pb; c.item_end = pe; c.item_cnt = tb.item_cnt;
@@ -1042,16 +1045,16 @@ int launch_pair_tf32(const PairArgs& pa, const PairArgs& fb_in, const Tf32Buffer
     c.nunits = pa.L.npanel; c.force_dense = tune().force_dense ? 1 : (tune().no_dense ? -1 : 0);
     classify_items_kernel<<<(nitems + 255) / 256, 256, 0, stream>>>(c);
     CREST_CUDA_TRY(cudaGetLastError());
-    CREST_CUDA_TRY(cudaMemsetAsync(tb.unfinished, 0, (size_t)pa.nall, stream));
+    CREST_CUDA_TRY(cudaMemsetAsync(tb.unfinished + row_lo, 0, (size_t)(row_hi - row_lo), stream));
     ScanArgs e{};
     e.xv = make_xview(pa.X, pa.L); e.xn = pa.xn; e.rot = pa.rot; e.aniso = pa.aniso;
     e.cmask = tb.cmask; e.fmask = a.fmask;
-    e.row0 = col0; e.col0 = col0; e.col_end = col_end; e.nall = pa.nall; e.stride = a.cm_stride;
+    e.row0 = row0; e.col0 = col0; e.col_end = col_end; e.nall = row_hi; e.stride = a.cm_stride;
     e.dense = all_cand ? nullptr : tb.dense; e.unfinished = tb.unfinished;
     e.dense_budget = (c.force_dense > 0) ? 0 : (tune().dense_budget > 0 ? tune().dense_budget : 64);
     e.segcols = segcols; e.ntile = ntile;
     e.g = pa.g; e.dup = pa.dup; e.counters = tb.cand_count; e.debug_all = all_cand ? 1 : 0;
-    const int rows = pa.nall - col0;
+    const int rows = row_hi - row0;
     int sgrid = (rows + 7) / 8;
     if (sgrid > nsm * 8) sgrid = nsm * 8;
     if (sgrid < 1) sgrid = 1;

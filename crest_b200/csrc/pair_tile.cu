@@ -292,7 +292,7 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
                   dupl = equalrotaniso_dev(a.rot + 3 * (size_t)i, a.rot + 3 * (size_t)j,
                                            a.aniso[i], a.aniso[j], a.g.bthr_half, a.g.bthrmax,
                                            a.g.bthrshift);
-                if (dupl) atomicMax(a.dup + i, j + 1);
+                if (dupl) atomicMax_system(a.dup + i, j + 1);
               }
             }
           }

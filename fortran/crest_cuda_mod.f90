@@ -14,6 +14,7 @@ module crest_cuda
   implicit none
   private
   public :: crest_cuda_thresholds
+  public :: crest_cuda_start, crest_cuda_stop
   public :: cregen_dup_cuda, cregen_group_cuda
   public :: compare_blocks_cuda, intraconf_cuda
 
@@ -27,6 +28,18 @@ module crest_cuda
   end type crest_cuda_thresholds
 
   interface
+    !> engine of 1-8 GPUs driven by this (single) host thread; ngpu_requested <= 0: all visible GPUs
+    function crest_cuda_init(ngpu_requested,ngpu_used) result(rc) bind(C,name="crest_cuda_init")
+      import
+      integer(c_int),intent(in),value :: ngpu_requested
+      integer(c_int),intent(out) :: ngpu_used
+      integer(c_int) :: rc
+    end function crest_cuda_init
+
+    !> releases every device buffer, stream and pinned staging buffer of the engine
+    subroutine crest_cuda_finalize() bind(C,name="crest_cuda_finalize")
+    end subroutine crest_cuda_finalize
+
     !> replaces cregen.f90:1222-1376 (axis + rot, pair RMSD incl. mirror, duplicate sweep)
     function crest_cuda_cregen_dup(nat,nall,at,xyz,er,rmsd_mask,rot_from_mask,enantio, &
         &                          thr,rot,xyz_axis,dup,npairs) result(rc) &
@@ -92,6 +105,22 @@ module crest_cuda
   end interface
 
 contains
+
+  !> call once (e.g. beside new_ompautoset in cregen_setthreads, cregen.f90:2314-2336):
+  !> ngpu = 0 takes every visible GPU; returns the number in use
+  subroutine crest_cuda_start(ngpu,nused)
+    integer,intent(in) :: ngpu
+    integer,intent(out) :: nused
+    integer(c_int) :: rc,nu
+    rc = crest_cuda_init(int(ngpu,c_int),nu)
+    if (rc /= 0) error stop 'crest_cuda_init failed (no CUDA device; there is no CPU fallback)'
+    nused = int(nu)
+  end subroutine crest_cuda_start
+
+  !> call at program end (or never: the driver reclaims everything at exit)
+  subroutine crest_cuda_stop()
+    call crest_cuda_finalize()
+  end subroutine crest_cuda_stop
 
   !> abort like the reference does on fatal errors (`error stop`); there is no CPU fallback
   subroutine cuda_fail(where)

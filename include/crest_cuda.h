@@ -34,7 +34,23 @@ typedef struct crest_cuda_thresholds {
 } crest_cuda_thresholds;
 
 /* ------------------------------------------------------------------------------------------
- * One-call entry points (what the Fortran shim binds; 1 GPU = the current device)
+ * Engine: the process-global set of GPUs the one-call entry points use.  CREST is one
+ * process with OpenMP and no MPI (newcregen, cregen.f90:221-235, calls from the serial region), so ONE
+ * host thread drives 1-8 GPUs: per-device contexts and streams, xyz split over the GPUs' PCIe links and
+ * exchanged over NVLink peer copies, each GPU running its shard of the pair work, links combined by
+ * system-scope atomicMax into GPU 0's dup[] over peer memory (no collective afterwards).
+ *   ngpu_requested <= 0: every visible GPU; 1: the CURRENT device; n > 1: devices 0..n-1 (needs all-to-all
+ *   peer access, else the engine stays on one GPU).  *ngpu_used receives the count in use.
+ * Optional: without it the first one-call entry point initialises CREST_CUDA_NGPU GPUs (default 1).
+ * crest_cuda_finalize releases every device buffer, stream and pinned staging buffer of the engine;
+ * calling an entry point afterwards re-initialises it.
+ * ------------------------------------------------------------------------------------------ */
+int crest_cuda_init(int ngpu_requested, int* ngpu_used);
+void crest_cuda_finalize(void);
+int crest_cuda_ngpu(void);   /* GPUs of the engine, 0 before init / after finalize */
+
+/* ------------------------------------------------------------------------------------------
+ * One-call entry points (what the Fortran shim binds), on the engine's GPUs
  * ------------------------------------------------------------------------------------------ */
 
 /* Replaces cregen.f90:1222-1376 (K0 axis + rot, K1-K3 pair RMSD incl. mirror, K4 sweep+backtrack).
@@ -202,10 +218,12 @@ int crest_cuda_ctx_download(crest_cuda_ctx* ctx, double* rot, double* xyz_axis, 
  * info[0]=tiles in shard, [1]=tiles total, [2]=atoms in RMSD (A), [3]=padded atoms used by MMA,
  * [4]=grid, [5]=dynamic smem bytes, [6]=kernels launched by the last ctx_* call sequence,
  * [7]=pair-kernel variant of the last ctx_pairs (0 row-tile DMMA, 1 column DMMA, 2 tensor-core
- * TF32 screen + exact FP64 candidate pass), [8]=candidate pairs the screen passed to the exact
- * kernel, [9]=1 if the candidate list overflowed (launch re-run on the FP64 column kernel),
- * [10]=screen violations counted in the CREST_CUDA_DEBUG=3 self-check (must be 0).
- * info must hold 16 entries; reading [8..10] synchronises the device. */
+ * TF32 screen + exact FP64 candidate scan), [8]=candidate pairs the screen could not prove far,
+ * [9]=work items the classifier found candidate-dense, [10]=screen violations counted in the
+ * CREST_CUDA_DEBUG=3 self-check (must be 0), [11]=exact FP64 evaluations the top-down scan spent
+ * (<= [8]: a row ends at its first match), [12]=flags: 1 unsafe magnitudes (every item re-done in FP64),
+ * 2 dense work list overflowed (items left to the scan).  Counters accumulate since the last ctx_pack.
+ * info must hold 16 entries; reading [8..12] synchronises the device. */
 int crest_cuda_ctx_info(crest_cuda_ctx* ctx, const crest_cuda_thresholds* thr, int rank,
                         int nranks, long long* info);
 
@@ -241,8 +259,10 @@ int crest_cuda_tf32_items_n(int nall, const double* er, double ethr, int nranks,
                             long long cap, long long* nitems);
 
 /* Developer knobs (same syntax as the CREST_CUDA_TUNE environment variable; NULL = defaults):
- * "notf32" forces the FP64 (DMMA) pair kernels, "tile" the row-tile kernel, "cap=<n>" the candidate
- * list capacity, "chunk=<n>" j-groups per work item.  Takes effect at the next ctx_upload. */
+ * "notf32" forces the FP64 (DMMA) pair kernels, "tile" the row-tile kernel, "chunk=<n>" j-groups per
+ * work item, "maskmb=<MB>" the candidate-bitmask budget, "forcedense"/"nodense"/"densebudget=<n>" the
+ * dense-item policy, "blocks=<n>" row blocks of the upload pipeline, "nostage" no pinned staging of the
+ * whole-CREGEN geometry.  Takes effect at the next ctx_upload. */
 void crest_cuda_set_tune(const char* spec);
 
 const char* crest_cuda_last_error(void);

@@ -321,6 +321,10 @@ void oracle_intraconf(int nat, int nall, const double* xyz, const int* inc, int 
   }
 }
 
+// Under torch.distributed.run OMP_NUM_THREADS is 1 in the environment: the timed CPU arm sets its thread
+// count explicitly (bench.py).
+void oracle_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+
 int oracle_num_threads(void) { return omp_get_max_threads(); }
 
 }  // extern "C"

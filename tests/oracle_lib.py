@@ -55,6 +55,8 @@ def lib():
         L.oracle_pair_rows.argtypes = [C.c_int, C.c_int, c_dp, c_dp, C.c_double, C.c_int, C.c_int,
                                        C.c_int, c_fp]
         L.oracle_num_threads.restype = C.c_int
+        L.oracle_set_num_threads.restype = None
+        L.oracle_set_num_threads.argtypes = [C.c_int]
         L.oracle_compare_blocks.restype = None
         L.oracle_compare_blocks.argtypes = [C.c_int, c_dp, C.c_int, c_ip, c_ip, c_dp, C.c_int, c_ip,
                                             c_ip, c_dp]
@@ -191,6 +193,11 @@ def pair_rows(xyz_packed, er, i0, i1, *, ethr=1e9, enantio=True, want=True):
 
 def num_threads():
     return lib().oracle_num_threads()
+
+
+def set_num_threads(n):
+    """OpenMP threads of the oracle's loops (torchrun exports OMP_NUM_THREADS=1: bench.py overrides it)."""
+    lib().oracle_set_num_threads(int(n))
 
 
 def compare_blocks(xyz1, b1, e1, xyz2, b2, e2):

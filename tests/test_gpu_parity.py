@@ -567,7 +567,7 @@ def test_tf32_adversarial_near_misses(cb):
     assert (got["dup"] != 0).sum() < 30                       # (almost) nothing matches
     assert info["candidates"] > 0.9 * got["npairs"]           # the screen decides (almost) nothing
     assert info["dense_items"] > 0
-    assert info["exact_evals"] <= 3000 * (64 + 8)             # budget per row inside dense items
+    assert info["exact_evals"] <= 3000 * 100                  # ~ the budget of 64 per row inside dense items
 
 
 @pytest.mark.parametrize("cfg,nall,ethr,maskmb", [("C1", 1000, 1e9, 1), ("C5", 9000, 1e9, 1), ("C5", 9000, 0.3, 1),
@@ -726,3 +726,79 @@ def test_rmsdalign_entry(cb, oracle):
     assert np.array_equal(cb.rmsdalign(at, xyz), xyz)
     # nall = 0 / 1
     assert cb.rmsdalign(np.array([6, 8], np.int32), np.zeros((1, 2, 3))).shape == (1, 2, 3)
+
+
+# ------------------------------------------------------------------------------------------------
+# Engine of the one-call entry points (driver.cu): row-block upload pipeline, single-process multi-GPU
+# ------------------------------------------------------------------------------------------------
+def _one_call(cb, ens, env, want_xyz=True):
+    at, xyz, er = ens["at"], ens["xyz"], ens["er"]
+    nall, nat, _ = xyz.shape
+    return cb.cregen_dup(env, nat, nall, at, xyz, er, want_xyz=want_xyz)
+
+
+@pytest.mark.parametrize("cfg,nall,ethr", [("C3", 30000, 1e9), ("C5", 40000, 0.3), ("C4", 6000, 1e9)])
+def test_engine_upload_pipeline_blocks(cb, cfg, nall, ethr):
+    """The one-call ABI streams xyz in row blocks and starts the pair kernels of block k while block
+    k+1 is on the bus: any number of blocks gives the links of the resident single-stage run."""
+    from crest_b200 import cregen
+    ens = synth.make_config(cfg, nall=nall, seed=12)
+    env = cb.Env(ethr=ethr)
+    ref, rref, _ = _stage_a(cb, ens, env)                   # context API: everything resident, one stage
+    try:
+        outs = []
+        for tune in ("blocks=1", "blocks=3", "blocks=7", None):
+            cregen.set_tune(tune)
+            outs.append(_one_call(cb, ens, env))
+    finally:
+        cregen.set_tune(None)
+    for o in outs:
+        assert np.array_equal(o["dup"], rref)
+        assert o["npairs"] == ref["npairs"]
+        assert np.array_equal(o["rot"], outs[0]["rot"])
+        assert np.array_equal(o["xyz_axis"], outs[0]["xyz_axis"])
+
+
+def test_engine_finalize_and_reinit(cb):
+    ens = synth.make_config("C1", nall=500, seed=2)
+    env = cb.Env(ethr=1e9)
+    a = _one_call(cb, ens, env)
+    cb.finalize()
+    assert cb.ngpu() == 0
+    cb.finalize()                                            # idempotent
+    b = _one_call(cb, ens, env)                              # lazily re-initialised
+    assert cb.ngpu() == 1
+    assert np.array_equal(a["dup"], b["dup"]) and np.array_equal(a["rot"], b["rot"])
+
+
+@pytest.mark.parametrize("ngpu", [2, 4, 8])
+def test_engine_single_process_multi_gpu(cb, cuda_lib, ngpu):
+    """crest_cuda_init(ngpu) + the ONE-CALL ABI (what the Fortran shim binds) on 2/4/8 GPUs driven by
+    one host thread: xyz split over the PCIe links, NVLink peer exchange, sharded pair work, links
+    combined by atomicMax_system into GPU 0's dup[].  Identical to one GPU, for stage A alone and for
+    the whole cregen_CRE."""
+    if cuda_lib.crest_cuda_device_count() < ngpu:
+        pytest.skip(f"needs {ngpu} GPUs")
+    cases = [(synth.make_config("C3", nall=40000, seed=4), cb.Env(ethr=1e9)),
+             (synth.make_config("C5", nall=30000, seed=4), cb.Env(ethr=0.2)),
+             (synth.make_config("C4", nall=5000, seed=4), cb.Env(ethr=1e9)),
+             (synth.make_ensemble(20000, 60, 60, copies=2000, seed=4), cb.Env(ethr=1e9)),
+             (synth.make_config("C1", nall=300, seed=4), cb.Env(ethr=1e9))]
+    try:
+        for ens, env in cases:
+            ens.setdefault("heavy", False)
+            at, xyz, er = ens["at"], ens["xyz"], ens["er"]
+            nall, nat, _ = xyz.shape
+            assert cb.init(1) == 1
+            one = _one_call(cb, ens, env)
+            full1 = cb.cregen_CRE(env, nat, nall, at, xyz, er)
+            assert cb.init(ngpu) == ngpu
+            many = _one_call(cb, ens, env)
+            fulln = cb.cregen_CRE(env, nat, nall, at, xyz, er)
+            assert np.array_equal(one["dup"], many["dup"])
+            assert one["npairs"] == many["npairs"]
+            assert np.array_equal(one["rot"], many["rot"]) and np.array_equal(one["xyz_axis"], many["xyz_axis"])
+            assert full1.nallout == fulln.nallout and np.array_equal(full1.order, fulln.order)
+            assert np.array_equal(full1.group, fulln.group) and np.array_equal(full1.xyz, fulln.xyz)
+    finally:
+        cb.finalize()
