@@ -6,5 +6,5 @@ from .cregen import (Env, CregenContext, cregen_CRE, cregen_dup, cregen_group, r
                      rotconst, rmat_allpairs, cregen_esort, rmsdalign, cregen_CRE_inplace,
                      CrestCudaError, init, finalize, ngpu)
 from ._lib import Thresholds  # noqa: F401
-from .compare import compare_blocks, compare_correlate, intraconf  # noqa: F401
+from .compare import compare_blocks, compare_correlate, intraconf, crossing_dedup  # noqa: F401
 from .ensemble_io import rdensembleparam, rdensemble, wrensemble, grepenergy, e2i  # noqa: F401

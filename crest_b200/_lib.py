@@ -55,6 +55,8 @@ SYMBOLS = {
     "crest_cuda_compare_correlate": (C.c_int, [C.c_int, C.c_int, c_dp, c_dp, c_dp, C.c_double, c_ip, c_ip]),
     "crest_cuda_intraconf": (C.c_int, [C.c_int, C.c_int, c_dp, c_ip, C.c_int, c_ip, c_ip, C.c_char_p,
                                        c_dp, c_dp]),
+    "crest_cuda_crossing_dedup": (C.c_int, [C.c_int, C.c_int, c_dp, c_dp, C.c_double, C.c_int, C.c_int, c_ip, c_dp,
+                                            c_ip, c_llp, c_dp]),
     "crest_cuda_ctx_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
     "crest_cuda_ctx_destroy": (None, [C.c_void_p]),
     "crest_cuda_ctx_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_int, c_ip, c_dp, c_dp, c_ip, C.c_int]),
@@ -67,6 +69,7 @@ SYMBOLS = {
     "crest_cuda_ctx_sweep": (C.c_int, [C.c_void_p, C.c_void_p]),
     "crest_cuda_ctx_download": (C.c_int, [C.c_void_p, c_dp, c_dp, c_ip, c_llp, C.c_void_p]),
     "crest_cuda_ctx_info": (C.c_int, [C.c_void_p, _THR, C.c_int, C.c_int, c_llp]),
+    "crest_cuda_ctx_tf32_accum": (C.c_int, [C.c_void_p, c_dp, c_llp, c_dp, c_dp]),
     "crest_cuda_ctx_download_mask": (C.c_int, [C.c_void_p, c_ullp, C.c_void_p]),
     "crest_cuda_e_threshold": (C.c_double, [C.c_double, C.c_int]),
     "crest_cuda_tile_shape": (None, [c_ip, c_ip]),

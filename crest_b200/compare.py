@@ -3,6 +3,8 @@
 compare_blocks / compare_correlate: compare_ensembles, /root/reference/src/ensemblecomp.f90:213-300
 intraconf:                          intraconfRMSD, /root/reference/src/entropy/entropic.f90:938-1097
 Arrays are (nall, nat, 3) C-order = xyz(3,nat,nall) column-major as Fortran passes them."""
+import ctypes as C
+
 import numpy as np
 
 from . import _lib
@@ -54,3 +56,25 @@ def intraconf(xyz, inc, low, nrot, symsym, enantiofac=None):
     _lib.check(L.crest_cuda_intraconf(xyz.shape[1], xyz.shape[0], _dp(xyz), _ip(inc), nconf, _ip(low),
                                       _ip(nrot), sym, _dp(fac), _dp(ef)))
     return fac[:nconf], ef[:nconf]
+
+
+def crossing_dedup(cand, xyzref, rthr, maxgen2, huge_number=False):
+    """De-duplication of the genetic crossing (crossing.f90:227-338, single-thread order) on generated
+    structures cand (ncand,nat,3) against the reference structure xyzref (nat,3); rthr in the unit of the
+    coordinates.  Returns dict(taken (1-based candidate per accepted slot), rms, ntaken, ierr, ident,
+    rcount, processed, rmsdsum)."""
+    L = _lib.lib()
+    cand = np.ascontiguousarray(cand, np.float64)
+    ref = np.ascontiguousarray(xyzref, np.float64)
+    ncand, nat = cand.shape[0], ref.shape[0]
+    taken = np.zeros(maxgen2, np.int32)
+    rms = np.zeros(maxgen2)
+    nt = C.c_int(0)
+    cnt = np.zeros(4, np.int64)
+    rsum = C.c_double(0)
+    _lib.check(L.crest_cuda_crossing_dedup(nat, ncand, cand.ctypes.data_as(_lib.c_dp), ref.ctypes.data_as(_lib.c_dp),
+                                           float(rthr), int(maxgen2), 1 if huge_number else 0,
+                                           taken.ctypes.data_as(_lib.c_ip), rms.ctypes.data_as(_lib.c_dp),
+                                           C.byref(nt), cnt.ctypes.data_as(_lib.c_llp), C.byref(rsum)))
+    return dict(taken=taken, rms=rms, ntaken=nt.value, ierr=int(cnt[0]), ident=int(cnt[1]), rcount=int(cnt[2]),
+                processed=int(cnt[3]), rmsdsum=rsum.value)

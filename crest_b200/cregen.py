@@ -363,6 +363,14 @@ class CregenContext:
                                                    C.byref(npairs), C.c_void_p(stream)))
         return dict(rot=rot[: self.nall], dup=dup[: self.nall], xyz_axis=xa, npairs=npairs.value)
 
+    def tf32_accum(self):
+        """Probe of the tensor core's FP32 accumulation on the packed ensemble (crest_cuda_ctx_tf32_accum):
+        dict(max_rel_err, ndots, gamma_budget, kappa)."""
+        e, g, k = C.c_double(0), C.c_double(0), C.c_double(0)
+        n = C.c_longlong(0)
+        _lib.check(self._L.crest_cuda_ctx_tf32_accum(self._h, C.byref(e), C.byref(n), C.byref(g), C.byref(k)))
+        return dict(max_rel_err=e.value, ndots=n.value, gamma_budget=g.value, kappa=k.value)
+
     def download_mask(self, stream=0):
         n8 = (self.nall + 7) // 8
         m = np.zeros((n8, n8), np.uint64)

@@ -803,6 +803,41 @@ int crest_cuda_ctx_info(crest_cuda_ctx* c, const crest_cuda_thresholds* thr, int
   return 0;
 }
 
+// Probe of the tensor core's FP32 accumulation: runs the screen over all pairs of the packed ensemble with
+// the raw TMEM covariances dumped, recomputes every dot product of the same TF32-rounded operands in FP64
+// and returns the largest |R~_ab - R_ab| / (|x_a||y_b|) - the quantity the screen's gamma budgets.
+int crest_cuda_ctx_tf32_accum(crest_cuda_ctx* c, double* max_rel_err, long long* ndots, double* gamma_budget,
+                              double* kappa) {
+  if (!c || !max_rel_err || !ndots) { set_error("NULL argument"); return 1; }
+  if (!c->use_tf32 || c->nall < 2) { set_error("the probe needs the tensor-core path and >= 2 structures"); return 1; }
+  CREST_CUDA_TRY(cudaSetDevice(c->device));
+  const size_t n = c->nall;
+  float* d_dump = nullptr;
+  unsigned long long* d_out = nullptr;
+  CREST_CUDA_TRY(cudaMalloc(&d_dump, sizeof(float) * 9 * n * n));
+  if (cudaMalloc(&d_out, 16) != cudaSuccess) { cudaFree(d_dump); set_error("cudaMalloc failed"); return 1; }
+  cudaMemset(d_dump, 0, sizeof(float) * 9 * n * n);
+  cudaMemset(d_out, 0, 16);
+  crest_cuda_thresholds t{1e300, 0.125, 0.01, 0.025, 0.5};
+  c->tf.dump = d_dump;
+  int rc = pairs_stage(c, 1, &t, 0, 1, 0, 0, nullptr, nullptr);
+  c->tf.dump = nullptr;
+  if (!rc) rc = launch_tf32_accum_check(c->tf, c->nall, d_dump, d_out, nullptr);
+  unsigned long long h[2] = {0, 0};
+  if (!rc && cudaMemcpy(h, d_out, 16, cudaMemcpyDeviceToHost) != cudaSuccess) {
+    set_error("probe failed: %s", cudaGetErrorString(cudaGetLastError()));
+    rc = 1;
+  }
+  cudaFree(d_dump); cudaFree(d_out);
+  if (rc) return rc;
+  std::memcpy(max_rel_err, &h[0], 8);
+  *ndots = (long long)h[1];
+  const int K = c->tf.kslab * c->tf.nslab;
+  if (gamma_budget) *gamma_budget = std::max(6.0e-5, 2.0 * K * std::ldexp(1.0, -23));
+  if (kappa) *kappa = c->tf.kappa;
+  return 0;
+}
+
 // Copy of the device bitmask (tests): mask[n8*n8] 64-bit words, bit r*8+col of word (ti,tj).
 int crest_cuda_ctx_download_mask(crest_cuda_ctx* c, unsigned long long* mask, void* stream) {
   if (!c || !c->d_mask || !mask) { set_error("no bitmask was requested"); return 1; }

@@ -167,6 +167,7 @@ struct Tf32Buffers {
   int4* dense_items = nullptr;      // work list of the FP64 tensor kernel for dense items
   unsigned dense_items_cap = 0;
   unsigned* cand_count = nullptr;   // [0] exact evaluations, [1] unsafe magnitudes, [2] debug violations, [3] candidates, [4] converter flag, [5] dense items, [6] dense list length, [7] dense list overflow
+  float* dump = nullptr;      // accumulate-error probe only: raw covariances [nall][nall][9] (crest_cuda_ctx_tf32_accum)
   int chunk = 0;              // j-groups per segment of the work list (multiple of 8)
   double kappa = 0.0;         // relative lowering of the screen's test point (error budget of this atom count)
   int nslab = 1;              // TF32 K slabs (1 for A <= 88; slabs of 48 slots for the row-tile layout)
@@ -179,6 +180,8 @@ int launch_tf32_convert(const double* d_X, const double* d_xn, int nall, const P
                         int tile0, int tile1, int nslab_t, int kslab, double kappa, float* d_Xa,
                         float* d_Xb, float* d_hn, unsigned* d_unsafe, cudaStream_t stream);
 double tf32_kappa(int kslots);
+int launch_tf32_accum_check(const Tf32Buffers& tb, int nall, const float* d_dump, unsigned long long* d_out,
+                            cudaStream_t stream);
 // items = device array of {I, g_begin, g_end, g_gate_end} int quadruples
 // h_items = host copy of the list (the launcher cuts [item_begin, item_end) into passes of whole
 // segments whose candidate bitmask fits tb.cm_words); fb = arguments of the FP64 tensor kernel that

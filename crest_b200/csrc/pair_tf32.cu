@@ -157,6 +157,8 @@ struct TfArgs {
   unsigned* fmask;        // debug (all_cand): same geometry, bit set = the screen called the pair far
   int cm_row0, cm_col0;
   long long cm_stride;
+  float* dump;            // accumulate-error probe (debug 7): raw TMEM covariances, [i][j][9], row stride dump_n
+  int dump_n;
   const int* dup;         // current links (1-based parent or 0): candidates below them are never needed
   unsigned* item_cnt;     // candidates emitted per work item (classify_items_kernel reads + clears)
   unsigned* cand_count;   // [0] exact evaluations, [1] converter "unsafe magnitudes" seen by the launch, [2] screen violations (debug), [3] candidates emitted, [4] converter flag, [5] dense items
@@ -175,6 +177,15 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
                                              int j0, int i, bool iok, f2_t hic2, bool rowfast,
                                              bool gate, bool slow, int dupi,
                                              unsigned long long& my_pairs, unsigned& my_cand) {
+  if (DBG && a.dump) {     // probe of the tensor core's FP32 accumulation (tf32_accum_check_kernel)
+    if (iok)
+#pragma unroll
+      for (int p = 0; p < 4; ++p)
+        if (j0 + p < i)
+#pragma unroll
+          for (int z = 0; z < 9; ++z)
+            a.dump[((size_t)i * a.dump_n + (j0 + p)) * 9 + z] = __uint_as_float(v[z][p]);
+  }
   const float4 h0 = __ldg(reinterpret_cast<const float4*>(hnp));
   const float hj[4] = {h0.x, h0.y, h0.z, h0.w};
   uint32_t sg[4];                        // sign bit set = not proven far
@@ -873,6 +884,72 @@ expand_dense_kernel(const ClassifyArgs a) {
   }
 }
 
+// ---- probe of the tensor core's FP32 accumulation (tools/gpu_tf32_accum.py) ----------
+// The screen's bound budgets gamma for what tcgen05.mma kind::tf32 loses while it accumulates K products
+// in FP32 - a property of the hardware that is not architecturally specified.  This kernel measures it:
+// for every pair (i > j) and every one of the nine components it recomputes the dot product of the SAME
+// TF32-rounded operands (read back from the A operand copy) exactly (products of two TF32 numbers fit
+// FP64 with room to spare) and reports the largest |R~_ab - R_ab| / (|x_a| |y_b|), the quantity gamma
+// bounds.  One thread per pair.
+struct AccumArgs {
+  const float* Xa; int nslab, kslab; int n;
+  const float* dump; int dump_n;
+  unsigned long long* out;   // [0] max rel error (bits of a double), [1] dot products checked
+};
+__device__ __forceinline__ float xa_at(const AccumArgs& a, int i, int comp, int t) {
+  const int I = i >> 7, r = i & 127, sl = t / a.kslab, tt = t % a.kslab, nchunk = a.kslab >> 2;
+  return a.Xa[(((((size_t)I * a.nslab + sl) * 3 + comp) * nchunk + (tt >> 2)) * 128 + r) * 4 + (tt & 3)];
+}
+__global__ void __launch_bounds__(256)
+tf32_accum_check_kernel(const AccumArgs a) {
+  const long long total = (long long)a.n * a.n;
+  double worst = 0.0;
+  unsigned long long cnt = 0;
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long long)gridDim.x * blockDim.x) {
+    const int i = (int)(p / a.n), j = (int)(p % a.n);
+    if (j >= i) continue;
+    const int K = a.nslab * a.kslab;
+    double r[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, nx[3] = {0, 0, 0}, ny[3] = {0, 0, 0};
+    for (int t = 0; t < K; ++t) {
+      double x[3], y[3];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) { x[c] = (double)xa_at(a, i, c, t); y[c] = (double)xa_at(a, j, c, t); }
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        nx[c] = fma(x[c], x[c], nx[c]); ny[c] = fma(y[c], y[c], ny[c]);
+#pragma unroll
+        for (int d = 0; d < 3; ++d) r[3 * c + d] = fma(x[c], y[d], r[3 * c + d]);
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        const double got = (double)a.dump[((size_t)i * a.dump_n + j) * 9 + 3 * c + d];
+        const double den = sqrt(nx[c] * ny[d]);
+        if (den > 0.0) worst = fmax(worst, fabs(got - r[3 * c + d]) / den);
+        ++cnt;
+      }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    worst = fmax(worst, __shfl_xor_sync(0xffffffffu, worst, o));
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMax(a.out, (unsigned long long)__double_as_longlong(worst));     // non-negative doubles order as integers
+    atomicAdd(a.out + 1, cnt);
+  }
+}
+
+int launch_tf32_accum_check(const Tf32Buffers& tb, int nall, const float* d_dump, unsigned long long* d_out,
+                            cudaStream_t stream) {
+  AccumArgs a{};
+  a.Xa = tb.Xa; a.nslab = tb.nslab; a.kslab = tb.kslab; a.n = nall; a.dump = d_dump; a.dump_n = nall; a.out = d_out;
+  tf32_accum_check_kernel<<<148 * 16, 256, 0, stream>>>(a);
+  CREST_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 // ---- host side -------------------------------------------------------------------------------
 int tf32_smem_bytes(int KU, int* nbstage_out) {
   const size_t a_bytes = (size_t)3 * (KU / 4) * 2048, b_bytes = (size_t)(KU / 4) * 768;
@@ -999,6 +1076,8 @@ int launch_pair_tf32(const PairArgs& pa, const PairArgs& fb_in, const Tf32Buffer
   a.cmask = tb.cmask; a.fmask = all_cand ? tb.fmask : nullptr;
   a.dup = pa.dup; a.item_cnt = tb.item_cnt; a.cand_count = tb.cand_count;
   a.npairs = pa.npairs;
+  a.dump = tb.dump; a.dump_n = pa.nall;
+  if (tb.dump && a.dbg == 0) a.dbg = 3;       // the probe lives in the debug instantiation (3: no timing switch)
   if (all_cand && !tb.fmask) { set_error("self-check needs the far-verdict mask"); return 1; }
   int dev = 0, nsm = 148;
   CREST_CUDA_TRY(cudaGetDevice(&dev));

@@ -168,6 +168,24 @@ int crest_cuda_intraconf(int nat, int nall, const double* xyz, const int* inc, i
                          const int* low, const int* nrot, const char* symsym, double* fac,
                          double* enantiofac);
 
+/* De-duplication inside the genetic structure crossing (src/algos/crossing.f90:227-338,
+ * the part between GMETRY / the CN clash check and the output): cand(3,nat,ncand) are the generated
+ * structures in the reference's single-thread loop order (i, then j < i), xyzref(3,nat) the lowest
+ * conformer, rthr in the unit of the coordinates (the reference works in Bohr).  Per structure:
+ * rval = rmsd(cand, xyzref) (263); rval <= rthr discards it; otherwise it is compared with the accepted
+ * structures whose own rval lies within rthr/100 (284) and rejected if any RMSD is < rthr (287-291), else
+ * appended, or - with the maxgen2 slots full - ends the search (huge_number != 0, 303-304) or replaces the
+ * slot sdselect picks (306-310, 401-432).  The GPU evaluates rval and every gated pair RMSD; the ordered
+ * replay of the critical section is host code.
+ *   taken(maxgen2)  out: 1-based index into cand of the structure in accepted slot k, 0 = empty
+ *   rms(maxgen2)    out: its rval;   ntaken out: slots in use
+ *   counters(4)     out: [0] discarded by rval <= rthr, [1] ident (duplicates of accepted structures),
+ *                   [2] rcount, [3] structures looked at before the search stopped
+ *   rmsdsum         out: sum of rval over the rcount structures (rmsdavg before the division, 340) */
+int crest_cuda_crossing_dedup(int nat, int ncand, const double* cand, const double* xyzref, double rthr,
+                              int maxgen2, int huge_number, int* taken, double* rms, int* ntaken,
+                              long long* counters, double* rmsdsum);
+
 /* All-pairs float32 RMSD band exactly as the reference's rmat (cregen.f90:1260-1349): row i holds
  * j = 0..i-1 at offset i*(i-1)/2 (ethr = infinity layout).  For tests on small ensembles. */
 int crest_cuda_rmat_allpairs(int nat, int nall, const int* at, const double* xyz,
@@ -226,6 +244,14 @@ int crest_cuda_ctx_download(crest_cuda_ctx* ctx, double* rot, double* xyz_axis, 
  * info must hold 16 entries; reading [8..12] synchronises the device. */
 int crest_cuda_ctx_info(crest_cuda_ctx* ctx, const crest_cuda_thresholds* thr, int rank,
                         int nranks, long long* info);
+
+/* Evidence for the screen's error budget: after ctx_upload + ctx_pack, runs the tensor-core
+ * screen over ALL pairs with the raw TMEM covariances dumped (9*nall^2 floats of device memory) and
+ * recomputes every dot product of the same TF32-rounded operands exactly: max_rel_err = the largest
+ * |R~_ab - R_ab| / (|x_a||y_b|) the tcgen05 FP32 accumulation produced, ndots = dot products checked,
+ * gamma_budget = what the bound allows for this K extent, kappa = the resulting test-point lowering. */
+int crest_cuda_ctx_tf32_accum(crest_cuda_ctx* ctx, double* max_rel_err, long long* ndots,
+                              double* gamma_budget, double* kappa);
 
 /* Copy of the device duplicate bitmask written by ctx_pairs(want_mask=1): n8*n8 64-bit words with
  * n8 = ceil(nall/8); bit r*8+c of word (ti,tj) = pair (i=8*ti+r, j=8*tj+c) is a duplicate link. */

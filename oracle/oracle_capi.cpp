@@ -1,6 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see ls_rmsd_ref.hpp header).  PARITY UNPINNED.
 // Plain-C entry points so tests/ and bench.py's cpu_baseline leg can drive the restatement
 // through ctypes.  Nothing in crest_b200/ links or loads this library.
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -319,6 +320,88 @@ void oracle_intraconf(int nat, int nall, const double* xyz, const int* inc, int 
     const int k = symmap_ref(symref, symsym + 3 * (size_t)co);
     enantiofac[co] = symenantio[k - 1];
   }
+}
+
+// GC crossing de-duplication, /root/reference/src/algos/crossing.f90:227-338 with ONE thread (loop order
+// i, then j < i = the order of `cand`): rval against the reference structure (263-273), the accepted-list
+// check inside the critical section (275-321) and sdselect (401-432), statement by statement.  `cand`
+// holds the structures that survived GMETRY and the CN clash check (not on the RMSD path).
+// counters: [0] discarded by rval <= rthr, [1] ident, [2] rcount, [3] candidates looked at before
+// stop_crossing.  taken[k] = 1-based candidate index in accepted slot k (0 = empty).
+static int sdselect_ref(int n, const double* rms, double rval) {
+  int pos = 0;
+  double avg = 0.0;
+  for (int i = 0; i < n; ++i) avg = avg + rms[i];
+  const double sum = avg;
+  avg = avg / (double)(float)n;
+  double sdref = 0.0;
+  for (int i = 0; i < n; ++i) sdref = sdref + (rms[i] - avg) * (rms[i] - avg);
+  sdref = std::sqrt(sdref / (double)(float)n);
+  for (int i = 0; i < n; ++i) {
+    avg = sum - rms[i] + rval;
+    avg = avg / (double)(float)n;
+    double sdtmp = 0.0;
+    for (int k = 0; k < n; ++k) sdtmp = sdtmp + (rms[k] - avg) * (rms[k] - avg);
+    sdtmp = sdtmp - (rms[i] - avg) * (rms[i] - avg);
+    sdtmp = sdtmp + (rval - avg) * (rval - avg);
+    sdtmp = std::sqrt(sdtmp / (double)(float)n);
+    if (sdtmp > sdref) { sdref = sdtmp; pos = i + 1; }
+  }
+  return pos;
+}
+
+void oracle_crossing_dedup(int nat, int ncand, const double* cand, const double* xyzref, double rthr,
+                           int maxgen2, int huge_number, int* taken, double* rms, int* ntaken_out,
+                           long long* counters, double* rmsdsum, double* rval_out) {
+  const size_t rec = (size_t)3 * nat;
+  std::vector<double> wx(rec), wy(rec), xyzgen((size_t)maxgen2 * rec);
+  const double rthr100 = rthr / 100.0;
+  int ntaken = 0;
+  long long ierr = 0, ident = 0, rcount = 0, processed = 0;
+  double rmsdavg = 0.0;
+  bool stop_crossing = false;
+  for (int k = 0; k < maxgen2; ++k) { taken[k] = 0; rms[k] = 0.0; }
+  for (int c = 0; c < ncand; ++c) {
+    if (stop_crossing) continue;
+    processed++;
+    const double* cdum = cand + rec * c;
+    const double rval = rmsd(nat, cdum, xyzref, wx.data(), wy.data());
+    if (rval_out) rval_out[c] = rval;
+    if (rval <= rthr) { ierr = ierr + 1; continue; }
+    rcount = rcount + 1;
+    rmsdavg = rmsdavg + rval;
+    if (ntaken < 1) {
+      ntaken = ntaken + 1;
+      std::memcpy(&xyzgen[(size_t)(ntaken - 1) * rec], cdum, rec * sizeof(double));
+      rms[ntaken - 1] = rval; taken[ntaken - 1] = c + 1;
+    } else {
+      bool fail = false;
+      for (int m = 1; m <= ntaken; ++m) {
+        if (std::fabs(rms[m - 1] - rval) < rthr100) {
+          const double rval2 = rmsd(nat, cdum, &xyzgen[(size_t)(m - 1) * rec], wx.data(), wy.data());
+          if (rval2 < rthr) { ident = ident + 1; fail = true; break; }
+        }
+      }
+      if (!fail) {
+        if (ntaken < maxgen2) {
+          ntaken = ntaken + 1;
+          std::memcpy(&xyzgen[(size_t)(ntaken - 1) * rec], cdum, rec * sizeof(double));
+          rms[ntaken - 1] = rval; taken[ntaken - 1] = c + 1;
+        } else if (huge_number) {
+          stop_crossing = true;
+        } else {
+          const int k = sdselect_ref(ntaken, rms, rval);
+          if (k > 0) {
+            std::memcpy(&xyzgen[(size_t)(k - 1) * rec], cdum, rec * sizeof(double));
+            rms[k - 1] = rval; taken[k - 1] = c + 1;
+          }
+        }
+      }
+    }
+  }
+  *ntaken_out = ntaken;
+  *rmsdsum = rmsdavg;
+  counters[0] = ierr; counters[1] = ident; counters[2] = rcount; counters[3] = processed;
 }
 
 // Under torch.distributed.run OMP_NUM_THREADS is 1 in the environment: the timed CPU arm sets its thread

@@ -54,6 +54,9 @@ def lib():
         L.oracle_pair_rows.restype = C.c_longlong
         L.oracle_pair_rows.argtypes = [C.c_int, C.c_int, c_dp, c_dp, C.c_double, C.c_int, C.c_int,
                                        C.c_int, c_fp]
+        L.oracle_crossing_dedup.restype = None
+        L.oracle_crossing_dedup.argtypes = [C.c_int, C.c_int, c_dp, c_dp, C.c_double, C.c_int, C.c_int, c_ip, c_dp,
+                                            c_ip, c_lp, c_dp, c_dp]
         L.oracle_num_threads.restype = C.c_int
         L.oracle_set_num_threads.restype = None
         L.oracle_set_num_threads.argtypes = [C.c_int]
@@ -240,3 +243,20 @@ def intraconf(xyz, inc, low, nrot, symsym, enantiofac=None, rmat_conf=-1):
     if rm is not None:
         return fac[:nconf], ef[:nconf], rm
     return fac[:nconf], ef[:nconf]
+
+
+def crossing_dedup(cand, xyzref, rthr, maxgen2, huge_number=False):
+    """crossing.f90:227-338 with one thread on generated structures cand (ncand,nat,3); returns a dict."""
+    cand = np.ascontiguousarray(cand, np.float64)
+    ref = np.ascontiguousarray(xyzref, np.float64)
+    ncand, nat, _ = cand.shape
+    taken = np.zeros(maxgen2, np.int32)
+    rms = np.zeros(maxgen2)
+    nt = C.c_int(0)
+    cnt = np.zeros(4, np.int64)
+    rsum = C.c_double(0)
+    rval = np.zeros(max(ncand, 1))
+    lib().oracle_crossing_dedup(nat, ncand, _dp(cand), _dp(ref), float(rthr), int(maxgen2), int(huge_number),
+                                _ip(taken), _dp(rms), C.byref(nt), cnt.ctypes.data_as(c_lp), C.byref(rsum), _dp(rval))
+    return dict(taken=taken, rms=rms, ntaken=nt.value, ierr=int(cnt[0]), ident=int(cnt[1]), rcount=int(cnt[2]),
+                processed=int(cnt[3]), rmsdsum=rsum.value, rval=rval[:ncand])

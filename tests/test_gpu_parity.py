@@ -488,6 +488,9 @@ def test_tf32_screen_selfcheck(cb):
     ens["heavy"] = False
     cases.append((ens, cb.Env(ethr=1e9)))
     cases.append((synth.make_config("C4", nall=500, seed=6), cb.Env(ethr=1e9)))     # K-slab kernel
+    big = synth.make_ensemble(260, 520, 520, copies=6, seed=9, frac_straddle=0.3)      # 11 slabs: the
+    big["heavy"] = False                                                               # atom-count dependent budget
+    cases.append((big, cb.Env(ethr=1e9)))
     for name in ("adv_chiral", "adv_linear", "adv_planar"):
         g = np.load(os.path.join(GOLDEN, name + ".npz"))
         cases.append((dict(at=g["at"], xyz=g["xyz"], er=g["er"], heavy=False),
@@ -511,6 +514,23 @@ def test_tf32_screen_selfcheck(cb):
         assert info["violations"] == 0
         ref, _, _ = _stage_a(cb, ens, env, "notf32")
         assert np.array_equal(links["dup"], ref["dup"])
+
+
+@pytest.mark.parametrize("nall,nat", [(700, 60), (400, 300), (200, 1000)])
+def test_tf32_accumulation_error_within_budget(cb, nall, nat):
+    """The bound's gamma budgets the FP32 accumulation error of tcgen05.mma kind::tf32, which is not
+    architecturally specified: measure it (every dot product of the TF32-rounded operands recomputed in
+    FP64) and require it inside the budget of this atom count (profiles/r02_tf32_accum.txt: 3.4e9 dot
+    products, worst 3.4 % of the budget)."""
+    ens = synth.make_ensemble(nall, nat, nat, copies=5, seed=21)
+    ctx = cb.CregenContext()
+    ctx.upload(cb.Env(ethr=1e9), ens["at"], ens["xyz"], ens["er"])
+    ctx.pack()
+    r = ctx.tf32_accum()
+    ctx.close()
+    assert r["ndots"] == 9 * nall * (nall - 1) // 2
+    assert 0.0 < r["max_rel_err"] < 0.25 * r["gamma_budget"]
+    assert r["kappa"] >= 1.8e-3
 
 
 @pytest.mark.parametrize("cfg,nall,ethr", [("C1", 1000, 1e9), ("C5", 3000, 0.2), ("C4", 700, 1e9)])
