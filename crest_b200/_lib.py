@@ -75,6 +75,7 @@ SYMBOLS = {
     "crest_cuda_tile_shape": (None, [c_ip, c_ip]),
     "crest_cuda_band_tiles": (C.c_int, [C.c_int, c_dp, C.c_double, c_llp, c_ip, c_llp]),
     "crest_cuda_tf32_items": (C.c_int, [C.c_int, c_dp, C.c_double, c_ip, C.c_longlong, c_llp]),
+    "crest_cuda_tf32_items_rank": (C.c_int, [C.c_int, c_dp, C.c_double, C.c_int, C.c_int, c_ip, C.c_longlong, c_llp]),
     "crest_cuda_tf32_items_n": (C.c_int, [C.c_int, c_dp, C.c_double, C.c_int, c_ip, C.c_longlong, c_llp]),
     "crest_cuda_shard_range": (C.c_int, [C.c_longlong, C.c_int, C.c_int, c_llp, c_llp]),
     "crest_cuda_set_tune": (None, [C.c_char_p]),

@@ -129,6 +129,18 @@ def tf32_items(er, ethr, nranks=1):
     return items[: n.value]
 
 
+def tf32_items_rank(er, ethr, nranks, rank):
+    """Host-only: the screen's work list of ONE rank (its rows: i-tiles I with I % nranks == rank)."""
+    L = _lib.lib()
+    er = np.ascontiguousarray(er, np.float64)
+    n = C.c_longlong(0)
+    _lib.check(L.crest_cuda_tf32_items_rank(len(er), _dp(er), float(ethr), nranks, rank, None, 0, C.byref(n)))
+    items = np.zeros((max(n.value, 1), 4), np.int32)
+    _lib.check(L.crest_cuda_tf32_items_rank(len(er), _dp(er), float(ethr), nranks, rank, _ip(items), n.value,
+                                            C.byref(n)))
+    return items[: n.value]
+
+
 def shard_range(ntiles, rank, nranks):
     """Host-only: [begin, end) of the tile list owned by `rank` of `nranks`."""
     b, e = C.c_longlong(0), C.c_longlong(0)

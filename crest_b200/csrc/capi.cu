@@ -198,8 +198,12 @@ void col_items_host(int n, const double* er, double ethr, std::vector<int>& item
 // cut on a fixed grid of `chunk` groups and ordered segment-major so that concurrently running CTAs
 // stream the same j-groups (L2-resident) past different i-tiles.
 // tile0/tile1: the list of a STAGE, i.e. only the i-tiles [tile0, tile1) (appended to `items`).
+// rank (0..nranks-1): only the tiles I with I % nranks == rank - ranks share the pair space by ROWS, so the
+// per-row "largest j" needs no exchange beyond combining disjoint rows, and a rank sees all columns of its
+// rows: links found in its high columns prune its low ones (pair_tf32.cu).  Rows interleave, so the
+// triangle's growing row length is spread evenly.  rank < 0: all tiles.
 int tf_items_host(int n, const double* er, double ethr, std::vector<int>& items, int nranks = 1,
-                  int tile0 = 0, int tile1 = -1) {
+                  int tile0 = 0, int tile1 = -1, int rank = -1) {
   if (n < 2) return 8;
   const int ntile = (n + 127) / 128;
   if (tile1 < 0 || tile1 > ntile) tile1 = ntile;
@@ -213,8 +217,11 @@ int tf_items_host(int n, const double* er, double ethr, std::vector<int>& items,
     }
     return lo;
   };
+  const int nr = nranks > 0 ? nranks : 1;
+  auto mine = [&](int I) { return rank < 0 || I % nr == rank; };
   long long total = 0;
   for (int I = tile0; I < tile1; ++I) {
+    if (!mine(I)) continue;
     const int i0 = I * 128, ilast = std::min(i0 + 127, n - 1), jhi = ilast - 1;
     if (jhi < 0) continue;
     const int jlo = first_in_band(i0);
@@ -226,7 +233,8 @@ int tf_items_host(int n, const double* er, double ethr, std::vector<int>& items,
   }
   // >= 16 items per CTA and rank: the CTAs of a rank take its items round-robin, so the stage lasts
   // ceil(items / 148) items (measured on C3: 128-group items cost nothing against 256, 64 cost 1.3 %)
-  long long chunk = tune().chunk > 0 ? tune().chunk : total / (148LL * 16 * (nranks > 0 ? nranks : 1));
+  // `total` already is this rank's share when a rank is given
+  long long chunk = tune().chunk > 0 ? tune().chunk : total / (148LL * 16 * (rank < 0 ? nr : 1));
   chunk = chunk / 8 * 8;       // segments are whole 128-column blocks of the candidate bitmask
   if (chunk < 8) chunk = 8;
   if (chunk > 256) chunk = 256;
@@ -235,6 +243,7 @@ int tf_items_host(int n, const double* er, double ethr, std::vector<int>& items,
   for (int sg = 0; sg < nseg; ++sg) {
     const int s0 = (int)(sg * chunk), s1 = (int)std::min<long long>((sg + 1) * chunk, ngroup);
     for (int I = tile1 - 1; I >= tile0; --I) {
+      if (!mine(I)) continue;
       const int b = std::max(gb[I], s0), e = std::min(ge[I], s1);
       if (b < e) { items.push_back(I); items.push_back(b); items.push_back(e); items.push_back(gg[I]); }
     }
@@ -245,15 +254,16 @@ int tf_items_host(int n, const double* er, double ethr, std::vector<int>& items,
 }  // namespace
 
 namespace crest {
-int plan_stages(crest_cuda_ctx* c, double ethr, int nranks, const std::vector<int>& bounds, cudaStream_t st) {
-  if (c->tf_items_ethr == ethr && c->tf_items_nranks == nranks && c->stage_tile == bounds) return 0;
+int plan_stages(crest_cuda_ctx* c, double ethr, int nranks, int rank, const std::vector<int>& bounds, cudaStream_t st) {
+  if (c->tf_items_ethr == ethr && c->tf_items_nranks == nranks && c->tf_items_rank == rank && c->stage_tile == bounds) return 0;
   const int nstage = (int)bounds.size() - 1;
   c->tf_items.clear();
   c->stage_item.assign(1, 0);
   c->stage_chunk.clear();
   size_t nd = 1, per_item_max = 1;
   for (int s = 0; s < nstage; ++s) {
-    const int chunk = tf_items_host(c->nall, c->h_er.data(), ethr, c->tf_items, nranks, bounds[s], bounds[s + 1]);
+    const int chunk = tf_items_host(c->nall, c->h_er.data(), ethr, c->tf_items, nranks, bounds[s], bounds[s + 1],
+                                    nranks > 1 ? rank : -1);
     c->stage_chunk.push_back(chunk);
     c->stage_item.push_back((int)(c->tf_items.size() / 4));
     const size_t nseg = ((size_t)bounds[s + 1] * 8 + chunk - 1) / chunk;
@@ -263,6 +273,7 @@ int plan_stages(crest_cuda_ctx* c, double ethr, int nranks, const std::vector<in
   c->stage_tile = bounds;
   c->tf_items_ethr = ethr;
   c->tf_items_nranks = nranks;
+  c->tf_items_rank = rank;
   const size_t n = c->tf_items.size();
   if (n > c->cap_tf_items) {
     cudaFree(c->d_tf_items); c->d_tf_items = nullptr; c->cap_tf_items = 0;
@@ -371,7 +382,24 @@ int crest_cuda_tf32_items_n(int nall, const double* er, double ethr, int nranks,
                             long long cap, long long* nitems) {
   if (nall < 0 || (!er && nall > 0) || !nitems || nranks < 1) { set_error("bad argument"); return 1; }
   std::vector<int> v;
-  tf_items_host(nall, er, ethr, v, nranks);
+  if (nranks == 1) tf_items_host(nall, er, ethr, v, 1);
+  else for (int r = 0; r < nranks; ++r) tf_items_host(nall, er, ethr, v, nranks, 0, -1, r);   // rank lists, concatenated
+  *nitems = (long long)(v.size() / 4);
+  if (items) {
+    if ((long long)v.size() > cap * 4) { set_error("items buffer too small"); return 1; }
+    std::memcpy(items, v.data(), sizeof(int) * v.size());
+  }
+  return 0;
+}
+
+int crest_cuda_tf32_items_rank(int nall, const double* er, double ethr, int nranks, int rank, int* items,
+                               long long cap, long long* nitems) {
+  if (nall < 0 || (!er && nall > 0) || !nitems || nranks < 1 || rank < 0 || rank >= nranks) {
+    set_error("bad argument");
+    return 1;
+  }
+  std::vector<int> v;
+  tf_items_host(nall, er, ethr, v, nranks, 0, -1, nranks > 1 ? rank : -1);
   *nitems = (long long)(v.size() / 4);
   if (items) {
     if ((long long)v.size() > cap * 4) { set_error("items buffer too small"); return 1; }
@@ -647,14 +675,15 @@ int pairs_stage(crest_cuda_ctx* c, int enantio, const crest_cuda_thresholds* thr
     // tensor-core screen -> per-item verdict -> top-down exact scan of the candidate bitmask -> FP64
     // tensor kernel on what dense items left unfinished (pair_tf32.cu), pass by pass over this rank's
     // slice of the stage's list
-    if (c->stage_tile.empty() || !(c->tf_items_ethr == thr->ethr && c->tf_items_nranks == nranks)) {
+    if (c->stage_tile.empty() || !(c->tf_items_ethr == thr->ethr && c->tf_items_nranks == nranks &&
+                                   c->tf_items_rank == rank)) {
       const std::vector<int> one{0, c->ntile};
-      if (plan_stages(c, thr->ethr, nranks, one, st)) return 1;
+      if (plan_stages(c, thr->ethr, nranks, rank, one, st)) return 1;
     }
     if (stage < 0 || stage + 1 >= (int)c->stage_tile.size()) { set_error("bad stage %d", stage); return 1; }
+    // the list already holds this rank's rows only
     const long long i0 = c->stage_item[stage], i1 = c->stage_item[stage + 1];
-    long long tb = 0, te = 0;
-    crest_cuda_shard_range(i1 - i0, rank, nranks, &tb, &te);
+    const long long tb = 0, te = i1 - i0;
     if (a.g.debug == 3 && !c->tf.fmask) {
       CREST_CUDA_TRY(cudaMalloc(&c->tf.fmask, sizeof(unsigned) * c->tf.cm_words));
     }
@@ -781,9 +810,10 @@ int crest_cuda_ctx_info(crest_cuda_ctx* c, const crest_cuda_thresholds* thr, int
   }
   long long T = c->use_col ? (long long)(c->items.size() / 4)
                            : (c->rowstart.empty() ? 0 : c->rowstart.back());
-  if (c->last_variant == 2) T = (long long)(c->tf_items.size() / 4);   // all stages
+  if (c->last_variant == 2) T = (long long)(c->tf_items.size() / 4);   // this rank's list, all stages
   long long tb = 0, te = 0;
   crest_cuda_shard_range(T, rank, nranks, &tb, &te);
+  if (c->last_variant == 2) { tb = 0; te = T; }
   info[7] = c->last_variant;
   info[8] = info[9] = info[10] = info[11] = info[12] = 0;
   if (c->last_variant == 2 && c->tf.cand_count) {

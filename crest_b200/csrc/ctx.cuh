@@ -56,6 +56,7 @@ struct crest_cuda_ctx {
   size_t cap_tf_items = 0;
   double tf_items_ethr = std::numeric_limits<double>::quiet_NaN();
   int tf_items_nranks = 0;     // the item size depends on the number of ranks sharing the list
+  int tf_items_rank = -1;      // the rank whose rows the list holds
   // links of this context's pairs go here: its own d_dup, or the d_dup of device 0 over NVLink peer
   // memory in a single-process multi-GPU call (driver.cu)
   int* dup_target = nullptr;
@@ -79,7 +80,7 @@ int pairs_stage(crest_cuda_ctx* c, int enantio, const crest_cuda_thresholds* thr
                 int stage, int want_mask, float* d_rmat, cudaStream_t st);
 // (re)build the per-stage work lists of the screen for tile boundaries `bounds` (nstage+1 entries, first 0,
 // last ntile) and upload them; cached on (ethr, nranks, bounds)
-int plan_stages(crest_cuda_ctx* c, double ethr, int nranks, const std::vector<int>& bounds, cudaStream_t st);
+int plan_stages(crest_cuda_ctx* c, double ethr, int nranks, int rank, const std::vector<int>& bounds, cudaStream_t st);
 bool tf32_path(const crest_cuda_ctx* c, int want_mask, const float* d_rmat);
 // K0 on the rows [r0, r1) (r0 a multiple of 128): pack_axis + TF32 operand conversion
 int pack_rows(crest_cuda_ctx* c, int r0, int r1, cudaStream_t st);

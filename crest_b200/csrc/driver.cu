@@ -23,7 +23,9 @@
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <mutex>
+#include <string>
 #include <thread>
 
 using namespace crest;
@@ -160,11 +162,14 @@ struct Phase {   // CREST_CUDA_TIMING=1: phase wall times on stderr (developer a
 // Measured on C3 (144 MB, pageable, profiles/r02_timeline_c3.txt): 1 block 16.1 ms, 4 blocks 14.6 ms,
 // 6 blocks 14.9, 8 blocks 15.3 - the pair work available after a fraction f of the rows is f^2, so the
 // GPU starves until ~1/4 of the upload whatever the cut, and every extra stage costs ~0.1 ms of tails.
-std::vector<int> plan_blocks(const crest_cuda_ctx* c, bool staged) {
+std::vector<int> plan_blocks(const crest_cuda_ctx* c, bool staged, int ngpu) {
   std::vector<int> b{0, c->ntile};
   const size_t bytes = (size_t)24 * c->nat * c->nall;
   int nb = 1;
-  if (staged && bytes >= ((size_t)24 << 20)) nb = (int)std::min<size_t>(8, std::max<size_t>(2, bytes / ((size_t)36 << 20)));
+  // per GPU the pair work shrinks with the GPU count while the upload (host memcpy bound) does not:
+  // fewer, larger blocks then
+  if (staged && bytes >= ((size_t)24 << 20))
+    nb = (int)std::min<size_t>(8, std::max<size_t>(2, bytes / (((size_t)36 << 20) * (size_t)std::max(1, ngpu / 2))));
   if (tune().blocks > 0) nb = tune().blocks;
   if (nb > c->ntile) nb = c->ntile;
   if (nb <= 1) return b;
@@ -185,14 +190,36 @@ int stage_a(Engine& E, int nat, int nall, const int* at, const double* xyz, cons
   const bool tl = std::getenv("CREST_CUDA_TIMING") && std::atoi(std::getenv("CREST_CUDA_TIMING")) == 2;
   const auto t_host0 = std::chrono::steady_clock::now();
   auto hms = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_host0).count(); };
-  for (int d = 0; d < n; ++d)
-    if (crest_cuda_ctx_upload(E.c[d], nat, nall, at, nullptr, er, rmsd_mask, rot_from_mask)) return 1;
-  const double t_reserve = hms();
+  // One worker thread per GPU beyond the first issues that GPU's copies and launches: a single host
+  // thread spends ~5 us per launch, and 8 GPUs x (7 peer copies + pack + 5 pair-stage launches) per block
+  // made the HOST the bottleneck of an 8-GPU call (profiles/r02_a_timeline_n8.txt: 6 ms of set-up and
+  // 0.6-0.9 ms of enqueueing per block for 0.1-0.5 ms of GPU work).  Errors travel back as text.
+  std::vector<std::string> werr((size_t)n);
+  auto run_parallel = [&](const std::function<int(int)>& f) -> int {
+    std::vector<std::thread> th;
+    std::vector<int> rcs((size_t)n, 0);
+    for (int d = 1; d < n; ++d)
+      th.emplace_back([&, d] { rcs[d] = f(d); if (rcs[d]) werr[d] = crest_cuda_last_error(); });
+    rcs[0] = f(0);
+    for (auto& t : th) t.join();
+    for (int d = 0; d < n; ++d)
+      if (rcs[d]) { if (d > 0) set_error("GPU %d: %s", E.c[d]->device, werr[d].c_str()); return 1; }
+    return 0;
+  };
   crest_cuda_ctx* c0 = E.c[0];
   if (npairs) *npairs = 0;
+  // phase 1 (per GPU): reserve buffers, small uploads, zero the accumulators, this GPU's work lists
+  std::vector<int> tb;
+  bool staged = false;
+  (void)tune();                                              // parse the knobs before any worker starts
+  if (run_parallel([&](int d) -> int {
+        if (crest_cuda_ctx_upload(E.c[d], nat, nall, at, nullptr, er, rmsd_mask, rot_from_mask)) return 1;
+        return 0;
+      })) return 1;
+  const double t_reserve = hms();
   if (nall == 0) return 0;
-  const bool staged = tf32_path(c0, 0, nullptr) && nall >= 2;
-  const std::vector<int> tb = plan_blocks(c0, staged);
+  staged = tf32_path(c0, 0, nullptr) && nall >= 2;
+  tb = plan_blocks(c0, staged, n);
   const int nb = (int)tb.size() - 1;
   const size_t rec = (size_t)24 * nat;                       // bytes per structure
 
@@ -207,19 +234,19 @@ int stage_a(Engine& E, int nat, int nall, const int* at, const double* xyz, cons
       if (o1 > o0) segs.push_back({E.c[d]->device, (char*)E.c[d]->d_xyz + o0, (char*)const_cast<double*>(xyz) + o0, o1 - o0, k});
     }
   }
-  for (int d = 0; d < n; ++d) {
-    CREST_CUDA_TRY(cudaSetDevice(E.c[d]->device));
-    CREST_CUDA_TRY(cudaDeviceSynchronize());                 // the staging streams do not order against earlier work
-    E.c[d]->dup_target = c0->d_dup;
-    if (begin_call(E.c[d], E.c[d]->stream)) return 1;
-    if (staged && plan_stages(E.c[d], thr->ethr, n, tb, E.c[d]->stream)) return 1;
-  }
-  CREST_CUDA_TRY(cudaSetDevice(c0->device));
-  CREST_CUDA_TRY(cudaEventRecord(E.ev_zero, c0->stream));
-  // CREST_CUDA_TIMING=2: host time stamps (no extra syncs) and device events per block on GPU 0
+  if (run_parallel([&](int d) -> int {
+        crest_cuda_ctx* c = E.c[d];
+        CREST_CUDA_TRY(cudaSetDevice(c->device));
+        CREST_CUDA_TRY(cudaDeviceSynchronize());             // the staging streams do not order against earlier work
+        c->dup_target = c0->d_dup;
+        if (begin_call(c, c->stream)) return 1;
+        if (staged && plan_stages(c, thr->ethr, n, d, tb, c->stream)) return 1;
+        if (d == 0) CREST_CUDA_TRY(cudaEventRecord(E.ev_zero, c->stream));
+        return 0;
+      })) return 1;
   const double t_plan = hms();
   std::vector<cudaEvent_t> tev;
-  std::vector<double> t_gate, t_enq;
+  std::vector<double> t_gate((size_t)nb, 0.0), t_enq((size_t)nb, 0.0);
   if (tl) {
     cudaSetDevice(c0->device);
     tev.resize(2 * (size_t)nb + 1);
@@ -229,56 +256,50 @@ int stage_a(Engine& E, int nat, int nall, const int* at, const double* xyz, cons
   BlockGate gate;
   gate.reset(nb, 1 << 30);                                   // armed before the copier starts
   int copy_rc = 0;
-  int T = copy_threads();
+  const int T = copy_threads();
   std::thread copier([&] { copy_rc = staged_copy(segs, 0, T, nb, &gate); });
-  int rc = 0;
-  for (int k = 0; k < nb && !rc; ++k) {
-    if (!gate.wait(k)) { rc = 1; break; }
-    if (tl) t_gate.push_back(hms());
-    const int r0 = tb[k] * 128, r1 = std::min(tb[k + 1] * 128, nall);
-    for (int d = 0; d < n && !rc; ++d) {
-      crest_cuda_ctx* c = E.c[d];
-      if (cudaSetDevice(c->device) != cudaSuccess) { rc = 1; break; }
-      // the other GPUs' shares of the block over NVLink
-      for (int s = 0; s < n && !rc; ++s) {
+  // phase 2 (per GPU): as block k lands, pull the other GPUs' shares, pack, run this GPU's rows of it
+  const int rc = run_parallel([&](int d) -> int {
+    crest_cuda_ctx* c = E.c[d];
+    for (int k = 0; k < nb; ++k) {
+      if (!gate.wait(k)) { set_error("upload failed"); return 1; }
+      if (tl && d == 0) t_gate[k] = hms();
+      const int r0 = tb[k] * 128, r1 = std::min(tb[k + 1] * 128, nall);
+      CREST_CUDA_TRY(cudaSetDevice(c->device));
+      for (int s = 0; s < n; ++s) {                          // the other GPUs' shares of the block over NVLink
         if (s == d) continue;
         const size_t o0 = share_off[(size_t)k * (n + 1) + s], o1 = share_off[(size_t)k * (n + 1) + s + 1];
-        if (o1 > o0 && cudaMemcpyPeerAsync((char*)c->d_xyz + o0, c->device, (char*)E.c[s]->d_xyz + o0,
-                                           E.c[s]->device, o1 - o0, c->stream) != cudaSuccess) {
-          set_error("peer copy %d -> %d failed: %s", s, d, cudaGetErrorString(cudaGetLastError()));
-          rc = 1;
-        }
+        if (o1 > o0)
+          CREST_CUDA_TRY(cudaMemcpyPeerAsync((char*)c->d_xyz + o0, c->device, (char*)E.c[s]->d_xyz + o0,
+                                             E.c[s]->device, o1 - o0, c->stream));
       }
-      if (!rc) rc = pack_rows(c, r0, r1, c->stream);
-      if (!rc && k == nb - 1) {
-        rc = cudaEventRecord(E.ev_packed[d], c->stream) != cudaSuccess;
-        if (!rc && stage_xyz) {
+      if (pack_rows(c, r0, r1, c->stream)) return 1;
+      if (k == nb - 1) {
+        CREST_CUDA_TRY(cudaEventRecord(E.ev_packed[d], c->stream));
+        if (stage_xyz) {
           // this GPU's slice of the finished xyz_axis -> pinned staging, under the pair kernels
           const size_t o0 = (size_t)nall * d / n * rec, o1 = (size_t)nall * (d + 1) / n * rec;
-          rc = cudaStreamWaitEvent(E.copy_st[d], E.ev_packed[d], 0) != cudaSuccess ||
-               (o1 > o0 && cudaMemcpyAsync((char*)stage_xyz + o0, (char*)c->d_xyz_axis + o0, o1 - o0,
-                                           cudaMemcpyDeviceToHost, E.copy_st[d]) != cudaSuccess);
+          CREST_CUDA_TRY(cudaStreamWaitEvent(E.copy_st[d], E.ev_packed[d], 0));
+          if (o1 > o0)
+            CREST_CUDA_TRY(cudaMemcpyAsync((char*)stage_xyz + o0, (char*)c->d_xyz_axis + o0, o1 - o0,
+                                           cudaMemcpyDeviceToHost, E.copy_st[d]));
         }
       }
-      if (!rc && d > 0 && k == 0) rc = cudaStreamWaitEvent(c->stream, E.ev_zero, 0) != cudaSuccess;
+      if (d > 0 && k == 0) CREST_CUDA_TRY(cudaStreamWaitEvent(c->stream, E.ev_zero, 0));
       if (tl && d == 0) cudaEventRecord(tev[2 * (size_t)k + 1], c->stream);
-      if (!rc) rc = pairs_stage(c, enantio, thr, d, n, staged ? k : 0, 0, nullptr, c->stream);
-      if (tl && d == 0) cudaEventRecord(tev[2 * (size_t)k + 2], c->stream);
+      if (pairs_stage(c, enantio, thr, d, n, staged ? k : 0, 0, nullptr, c->stream)) return 1;
+      if (tl && d == 0) { cudaEventRecord(tev[2 * (size_t)k + 2], c->stream); t_enq[k] = hms(); }
     }
-    if (tl) t_enq.push_back(hms());
-  }
+    if (d > 0) CREST_CUDA_TRY(cudaEventRecord(E.ev_done[d], c->stream));
+    return 0;
+  });
   if (rc) gate.fail();
   copier.join();
   if (rc || copy_rc) {
-    if (rc && !copy_rc && !*crest_cuda_last_error()) set_error("stage A failed: %s", cudaGetErrorString(cudaGetLastError()));
     for (int d = 0; d < n; ++d) { cudaSetDevice(E.c[d]->device); cudaDeviceSynchronize(); }
     return 1;
   }
   // GPU 0 chases the roots once every GPU's links have arrived
-  for (int d = 1; d < n; ++d) {
-    CREST_CUDA_TRY(cudaSetDevice(E.c[d]->device));
-    CREST_CUDA_TRY(cudaEventRecord(E.ev_done[d], E.c[d]->stream));
-  }
   CREST_CUDA_TRY(cudaSetDevice(c0->device));
   for (int d = 1; d < n; ++d) CREST_CUDA_TRY(cudaStreamWaitEvent(c0->stream, E.ev_done[d], 0));
   if (crest_cuda_ctx_sweep(c0, c0->stream)) return 1;

@@ -792,7 +792,9 @@ cand_scan_kernel(const ScanArgs a) {
       }
     }
     if (lane == 0 && m > m0) atomicMax_system(a.dup + i, m);
-    if (lane == 0 && gave_up && !done) a.unfinished[i] = 1;
+    // a row that skipped candidates inside a dense item needs the FP64 tensor kernel for them even if it
+    // found a match further down: the skipped ones sit at HIGHER j
+    if (lane == 0 && gave_up) a.unfinished[i] = 1;
   }
   n_eval = __reduce_add_sync(0xffffffffu, n_eval);
   n_viol = __reduce_add_sync(0xffffffffu, n_viol);

@@ -233,7 +233,7 @@ int crest_cuda_ctx_download(crest_cuda_ctx* ctx, double* rot, double* xyz_axis, 
                             long long* npairs, void* stream);
 
 /* Geometry of the launch that ctx_pairs would do (for bench/roofline bookkeeping):
- * info[0]=tiles in shard, [1]=tiles total, [2]=atoms in RMSD (A), [3]=padded atoms used by MMA,
+ * info[0]=work items of this rank, [1]=work items total (FP64-only kernels; = [0] on the screen path), [2]=atoms in RMSD (A), [3]=padded atoms used by MMA,
  * [4]=grid, [5]=dynamic smem bytes, [6]=kernels launched by the last ctx_* call sequence,
  * [7]=pair-kernel variant of the last ctx_pairs (0 row-tile DMMA, 1 column DMMA, 2 tensor-core
  * TF32 screen + exact FP64 candidate scan), [8]=candidate pairs the screen could not prove far,
@@ -279,8 +279,12 @@ int crest_cuda_shard_range(long long ntiles, int rank, int nranks, long long* be
  * capacity of items in quadruples. */
 int crest_cuda_tf32_items(int nall, const double* er, double ethr, int* items, long long cap,
                           long long* nitems);
-/* The same list as `nranks` ranks sharing it build it: items are cut smaller so that every rank still
- * has >= 16 items per CTA (rank r then takes crest_cuda_shard_range(nitems, r, nranks)). */
+/* Multi-rank: the pair space is shared by ROWS - rank r owns the i-tiles I with I % nranks == r and all
+ * their columns (the per-row "largest j" then needs no exchange beyond combining disjoint rows, and links
+ * found in a row's high columns prune its low ones on the same rank).  tf32_items_rank = the list of one
+ * rank (items cut so that it still has >= 16 per CTA); tf32_items_n = all rank lists concatenated. */
+int crest_cuda_tf32_items_rank(int nall, const double* er, double ethr, int nranks, int rank, int* items,
+                               long long cap, long long* nitems);
 int crest_cuda_tf32_items_n(int nall, const double* er, double ethr, int nranks, int* items,
                             long long cap, long long* nitems);
 

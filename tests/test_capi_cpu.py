@@ -125,8 +125,8 @@ def test_host_tf32_items(cuda_lib):
 
 
 def test_host_tf32_items_rank_sized(cuda_lib):
-    """The list `nranks` ranks build (smaller items, >= 16 per CTA and rank) covers the same pairs,
-    and the rank shards (crest_cuda_shard_range) partition it."""
+    """The lists `nranks` ranks build (smaller items, >= 16 per CTA and rank) cover the same pairs, and
+    every rank owns whole rows (interleaved i-tiles)."""
     from crest_b200 import cregen as cg
     rng = np.random.default_rng(4)
     n = 40000
@@ -149,12 +149,16 @@ def test_host_tf32_items_rank_sized(cuda_lib):
             a, b = spans(items), spans(base)
             assert a[0, 0] == b[0, 0] and a[-1, 1] == b[-1, 1]
             assert np.all(a[1:, 0] == a[:-1, 1])
-        got = []
+        # ranks share the pair space by rows: rank r owns the i-tiles I % nranks == r, all their columns
+        off = 0
         for r in range(nranks):
-            b0, e0 = cg.shard_range(len(items), r, nranks)
-            got.append((b0, e0))
-        assert got[0][0] == 0 and got[-1][1] == len(items)
-        assert all(got[k][1] == got[k + 1][0] for k in range(nranks - 1))
+            mine = cg.tf32_items_rank(er, 1e9, nranks, r)
+            assert np.all(mine[:, 0] % nranks == r)
+            assert np.array_equal(mine, items[off:off + len(mine)])
+            off += len(mine)
+        assert off == len(items)
+        work = [area(cg.tf32_items_rank(er, 1e9, nranks, r)) for r in range(nranks)]
+        assert max(work) < 1.05 * min(work)                # interleaved rows balance the triangle
 
 
 def test_argument_checks(cuda_lib):

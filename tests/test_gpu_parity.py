@@ -573,6 +573,30 @@ def test_tf32_collapsed_ensembles(cb, nall, nat, copies):
     assert np.array_equal(got3["dup"], ref["dup"]) and got3["npairs"] == ref["npairs"]
 
 
+@pytest.mark.parametrize("cfg,nall", [("C3dense", None), ("C3adv", 30000), ("C4ext", None)])
+def test_full_size_unfriendly_equal_fp64(cb, cfg, nall):
+    """The unfriendly bench workloads at (or near) full size: collapsed ensemble (1000 copies per
+    conformer), near-miss ensemble, extended chain.  Links of the screen path == FP64-only kernels, with
+    and without the dense-item policy, in one pass and sharded over 8 virtual ranks."""
+    ens = synth.make_config(cfg, nall=nall)
+    env = cb.Env(ethr=1e9)
+    ref, rref, _ = _stage_a(cb, ens, env, "notf32")
+    got, rgot, info = _stage_a(cb, ens, env)
+    assert info["variant"] == 2 and info["flags"] == 0
+    assert np.array_equal(got["dup"], ref["dup"]) and got["npairs"] == ref["npairs"]
+    got2, _, info2 = _stage_a(cb, ens, env, "nodense")
+    assert np.array_equal(got2["dup"], ref["dup"])
+    from crest_b200 import cregen
+    ctx = cb.CregenContext()
+    ctx.upload(env, ens["at"], ens["xyz"], ens["er"])
+    ctx.pack()
+    for r in range(8):
+        ctx.pairs(env, r, 8)
+    many = ctx.download()
+    ctx.close()
+    assert np.array_equal(many["dup"], ref["dup"]) and many["npairs"] == ref["npairs"]
+
+
 def test_tf32_adversarial_near_misses(cb):
     """One conformer, noise of 0.135 A per coordinate: every pair at RMSD ~ 0.33 A, i.e. no match at all
     (nothing for the largest-j-wins pruning to use) but inside the zone the TF32 bound cannot decide.
