@@ -489,7 +489,9 @@ def run_ours(args):
                         "atoms_padded": info["A_padded"], "launches_per_step": launches_step,
                         "candidates": info["candidates"], "candidate_fraction": info["candidates"] / max(my_pairs, 1),
                         "exact_evaluations": info["exact_evals"],
-                        "dense_items": info["dense_items"], "flags": info["flags"], "fp64_path": fp64_path},
+                        "dense_items": info["dense_items"], "dense_rows_tried": info["dense_rows_tried"],
+                        "dense_rows_matched": info["dense_rows_matched"], "flags": info["flags"],
+                        "fp64_path": fp64_path},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                          "frac": achieved / peak, "traffic": tr["bytes"] if tr else None,
                          "traffic_source": tr, "peak_source": peak_src, "cublas_tf32_tflops": tf32_cublas,

@@ -363,8 +363,9 @@ class CregenContext:
         buf = (C.c_longlong * 16)()
         _lib.check(self._L.crest_cuda_ctx_info(self._h, C.byref(thr), rank, nranks, buf))
         keys = ["tiles_shard", "tiles_total", "A", "A_padded", "grid", "smem", "launches",
-                "variant", "candidates", "dense_items", "violations", "exact_evals", "flags"]
-        return dict(zip(keys, list(buf)[:13]))
+                "variant", "candidates", "dense_items", "violations", "exact_evals", "flags",
+                "dense_rows_tried", "dense_rows_matched"]
+        return dict(zip(keys, list(buf)[:15]))
 
     def download(self, want_xyz=False, stream=0):
         rot = np.zeros((max(self.nall, 1), 3))

@@ -544,17 +544,17 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
       c->cap_tf_hn = nh;
     }
     if (!c->tf.cand_count) {
-      CREST_CUDA_TRY(cudaMalloc(&c->tf.cand_count, sizeof(unsigned) * 8));   // counters, see Tf32Buffers
-      CREST_CUDA_TRY(cudaMemset(c->tf.cand_count, 0, sizeof(unsigned) * 8));
+      CREST_CUDA_TRY(cudaMalloc(&c->tf.cand_count, sizeof(unsigned) * 16));   // counters, see Tf32Buffers
+      CREST_CUDA_TRY(cudaMemset(c->tf.cand_count, 0, sizeof(unsigned) * 16));
       CREST_CUDA_TRY(cudaMalloc(&c->d_npairs_scratch, sizeof(unsigned long long)));
     }
     // candidate bitmask (pair_tf32.cu): one pass over all columns if that fits the budget (default
     // 2 GB, CREST_CUDA_TUNE maskmb=<MB>), else passes of whole segments; never less than one segment
     // of 4096 columns.  Zeroed once: cand_scan_kernel clears what the screen sets.
     {
-      const size_t full = tf32_mask_words(0, nall, 0, nall);
+      const size_t full = tf32_mask_words(0, nall, 0, nall, 1);
       const size_t budget = ((size_t)(tune().mask_mb > 0 ? tune().mask_mb : 2048) << 20) / sizeof(unsigned);
-      const size_t one_seg = (size_t)nall * 128;
+      const size_t one_seg = ((size_t)nall + 256) * 128;
       const size_t want = std::max<size_t>(std::min(full, std::max(budget, one_seg)), 128);
       if (want > c->tf.cm_words || (tune().mask_mb > 0 && want != c->tf.cm_words)) {
         cudaFree(c->tf.cmask); cudaFree(c->tf.fmask);
@@ -610,7 +610,7 @@ int begin_call(crest_cuda_ctx* c, cudaStream_t st) {
   CREST_CUDA_TRY(cudaMemsetAsync(c->d_dup, 0, sizeof(int) * (size_t)(c->nall ? c->nall : 1), st));
   CREST_CUDA_TRY(cudaMemsetAsync(c->d_npairs, 0, sizeof(unsigned long long), st));
   if (c->use_tf32) {
-    CREST_CUDA_TRY(cudaMemsetAsync(c->tf.cand_count, 0, sizeof(unsigned) * 8, st));
+    CREST_CUDA_TRY(cudaMemsetAsync(c->tf.cand_count, 0, sizeof(unsigned) * 16, st));
   }
   c->launches = 0;
   return 0;
@@ -695,7 +695,7 @@ int pairs_stage(crest_cuda_ctx* c, int enantio, const crest_cuda_thresholds* thr
     tb_.chunk = c->stage_chunk[stage];
     const int row_lo = c->stage_tile[stage] * 128, row_hi = std::min(c->stage_tile[stage + 1] * 128, c->nall);
     if (launch_pair_tf32(a, fb, tb_, c->d_tf_items, c->tf_items.data(), (int)(i0 + tb), (int)(i0 + te),
-                         row_lo, row_hi, a.g.debug == 3, nsf, st, &c->last_grid, &c->last_smem, &c->launches))
+                         row_lo, row_hi, rank, nranks, a.g.debug == 3, nsf, st, &c->last_grid, &c->last_smem, &c->launches))
       return 1;
     c->last_variant = 2;
     return 0;
@@ -815,13 +815,14 @@ int crest_cuda_ctx_info(crest_cuda_ctx* c, const crest_cuda_thresholds* thr, int
   crest_cuda_shard_range(T, rank, nranks, &tb, &te);
   if (c->last_variant == 2) { tb = 0; te = T; }
   info[7] = c->last_variant;
-  info[8] = info[9] = info[10] = info[11] = info[12] = 0;
+  info[8] = info[9] = info[10] = info[11] = info[12] = info[13] = info[14] = 0;
   if (c->last_variant == 2 && c->tf.cand_count) {
-    unsigned h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    unsigned h[16] = {};
     CREST_CUDA_TRY(cudaSetDevice(c->device));
     CREST_CUDA_TRY(cudaDeviceSynchronize());
     CREST_CUDA_TRY(cudaMemcpy(h, c->tf.cand_count, sizeof(h), cudaMemcpyDeviceToHost));
     info[8] = h[3]; info[9] = h[5]; info[10] = h[2]; info[11] = h[0]; info[12] = h[1] | (h[7] << 1);
+    info[13] = h[8]; info[14] = h[9];
   }
   info[0] = te - tb;
   info[1] = T;

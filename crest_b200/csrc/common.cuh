@@ -189,9 +189,9 @@ int launch_tf32_accum_check(const Tf32Buffers& tb, int nall, const float* d_dump
 // rows [row_lo, row_hi) = the i-tiles the items belong to (a stage; 0, nall for the whole ensemble)
 int launch_pair_tf32(const PairArgs& a, const PairArgs& fb, const Tf32Buffers& tb, const void* d_items,
                      const int* h_items, int item_begin, int item_end, int row_lo, int row_hi,
-                     int all_cand, int nstage_tile, cudaStream_t stream, int* grid_out, int* smem_out,
-                     long long* launches_out);
-size_t tf32_mask_words(int row_lo, int row_hi, int col0, int col_end);
+                     int rank, int nranks, int all_cand, int nstage_tile, cudaStream_t stream, int* grid_out,
+                     int* smem_out, long long* launches_out);
+size_t tf32_mask_words(int row_lo, int row_hi, int col0, int col_end, int nranks);
 int launch_backtrack(int nall, int* d_dup, cudaStream_t stream);
 int launch_rmsd_pairs(int A, int n, const double* d_packed, long long npairs, const int* d_i,
                       const int* d_j, double* d_rmsd, double* d_rmsd_m, cudaStream_t stream);

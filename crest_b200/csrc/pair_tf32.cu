@@ -135,6 +135,12 @@ __device__ __forceinline__ void ld_batch(uint32_t taddr, uint32_t (&v)[9][4]) {
 
 struct TfItem { int I; int g_begin; int g_end; int g_gate_end; };
 
+// Row of conformer i in the candidate bitmask of a rank that owns the i-tiles I % nranks == rank: its
+// owned tiles are stored back to back (tile ordinal I / nranks), so the mask holds no rows of other ranks.
+__host__ __device__ __forceinline__ long long mask_row(int i, int nranks) {
+  return (long long)((i >> 7) / nranks) * 128 + (i & 127);
+}
+
 struct TfArgs {
   const float* Xa;        // [tile][comp][chunk][128][4]
   const float* Xb;        // [group][chunk][48][4]
@@ -155,7 +161,8 @@ struct TfArgs {
   // cm_stride 32-bit words; written with red.or, read top-down and cleared by cand_scan_kernel
   unsigned* cmask;
   unsigned* fmask;        // debug (all_cand): same geometry, bit set = the screen called the pair far
-  int cm_row0, cm_col0;
+  int cm_row0, cm_col0;   // cm_row0 = mask_row of the first row the pass can touch
+  int cm_nranks;
   long long cm_stride;
   float* dump;            // accumulate-error probe (debug 7): raw TMEM covariances, [i][j][9], row stride dump_n
   int dump_n;
@@ -239,7 +246,7 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
     // this row already has can change it
     if (!(DBG && a.all_cand) && j0 + 3 < dupi) return;
     const int rel = j0 - a.cm_col0;
-    const size_t w = (size_t)(i - a.cm_row0) * (size_t)a.cm_stride + (size_t)(rel >> 5);
+    const size_t w = (size_t)(mask_row(i, a.cm_nranks) - a.cm_row0) * (size_t)a.cm_stride + (size_t)(rel >> 5);
     atomicOr(a.cmask + w, cand << (rel & 31));
     if (DBG && a.all_cand && farbits) atomicOr(a.fmask + w, (farbits & cand) << (rel & 31));
     my_cand += __popc(cand);
@@ -662,10 +669,12 @@ struct ScanArgs {
   XView xv; const double* xn; const double* rot; const double* aniso;
   unsigned* cmask; unsigned* fmask;
   int row0, col0, col_end, nall;      // rows [row0, nall) x columns [col0, col_end) of this pass
+  int mrow0, nranks, rank;            // mask_row of row0; rows of i-tiles I % nranks == rank only
   long long stride;                   // words per row (multiple of 128)
   const unsigned char* dense;         // [segment][i-tile] != 0: candidate-dense item (classify_items_kernel)
   unsigned char* unfinished;          // [row] set when a row gives up inside a dense item (-> DMMA re-run)
-  int dense_budget;                   // exact evaluations a row may spend inside dense items (0: none)
+  int dense_budget;                   // exact evaluations a row may spend inside dense items: > 0 fixed,
+                                      // 0 none (every dense item re-done), < 0 adaptive (see the kernel)
   int segcols, ntile;                 // columns per segment (multiple of 128), i-tiles
   Gates g;
   int* dup;
@@ -724,17 +733,31 @@ cand_scan_kernel(const ScanArgs a) {
   const int warps = (gridDim.x * blockDim.x) >> 5;
   const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   unsigned n_eval = 0, n_viol = 0;
-  // longest rows first (descending i), round-robin over the warps of the grid
-  for (int i = a.nall - 1 - wid; i > a.col0 && i >= a.row0; i -= warps) {
+  // owned rows only, longest first (descending i), round-robin over the warps of the grid
+  const long long mtop = mask_row(a.nall - 1, a.nranks) + 128;       // upper bound of the compact row index
+  for (long long mr = mtop - 1 - wid; mr >= a.mrow0; mr -= warps) {
+    const int i = (int)(((mr >> 7) * a.nranks + a.rank) << 7) + (int)(mr & 127);
+    if (i >= a.nall || i <= a.col0 || i < a.row0) continue;
     const int jend = min(i, a.col_end);                       // columns [col0, jend) hold pairs of row i
     if (jend <= a.col0) continue;
-    unsigned* const rowp = a.cmask + (size_t)(i - a.row0) * (size_t)a.stride;
-    const unsigned* const frow = a.fmask ? a.fmask + (size_t)(i - a.row0) * (size_t)a.stride : nullptr;
+    unsigned* const rowp = a.cmask + (size_t)(mr - a.mrow0) * (size_t)a.stride;
+    const unsigned* const frow = a.fmask ? a.fmask + (size_t)(mr - a.mrow0) * (size_t)a.stride : nullptr;
     const int m0 = a.dup[i];
     int m = m0;                                               // best link so far (j + 1)
     bool done = false;                                        // row decided: only clearing remains
-    int budget = a.dense_budget;                              // evaluations left inside dense items
-    bool gave_up = false;
+    // Evaluations this row may spend inside candidate-dense items before its share goes to the FP64 tensor
+    // kernel.  Measured: where rows DO end in a match (collapsed ensembles, extended chains
+    // with many copies) scanning on is 2x cheaper than the re-run even after thousands of misses; where
+    // nothing matches (near-miss ensemble) every evaluation is wasted.  The rows of a launch tell which
+    // case it is: counters[8] rows that met a dense item, counters[9] those that still ended in a match.
+    // Start with a probe of 512; once 256 rows have reported, rows get 4096 while >= 1/8 of them succeed
+    // and 64 otherwise.  Budgets only steer work between two exact paths - the links do not depend on them.
+    int budget = a.dense_budget;
+    if (budget < 0) {
+      const unsigned tried = a.counters[8], won = a.counters[9];
+      budget = tried < 256u ? 512 : (won * 8u >= tried ? 4096 : 64);
+    }
+    bool gave_up = false, met_dense = false;
     const unsigned char* const dense_i = a.dense ? a.dense + (i >> 7) : nullptr;
     for (int blk = (jend - 1 - a.col0) >> 12; blk >= 0; --blk) {     // 128 words = 4096 columns
       uint4* const wp = reinterpret_cast<uint4*>(rowp + (size_t)blk * 128) + lane;
@@ -757,6 +780,7 @@ cand_scan_kernel(const ScanArgs a) {
           const int cbase = a.col0 + widx * 32;
           if (!a.debug_all && cbase + 32 <= m) { done = true; break; }               // whole word below the link
           const bool in_dense = dense_i && dense_i[(size_t)(cbase / a.segcols) * a.ntile];
+          met_dense |= in_dense;
           if (in_dense && budget <= 0) {       // this row's share of the item goes to the FP64 tensor kernel
             gave_up = true;
             continue;
@@ -795,6 +819,10 @@ cand_scan_kernel(const ScanArgs a) {
     // a row that skipped candidates inside a dense item needs the FP64 tensor kernel for them even if it
     // found a match further down: the skipped ones sit at HIGHER j
     if (lane == 0 && gave_up) a.unfinished[i] = 1;
+    if (lane == 0 && met_dense && a.dense_budget < 0) {
+      atomicAdd(a.counters + 8, 1u);
+      if (!gave_up) atomicAdd(a.counters + 9, 1u);
+    }
   }
   n_eval = __reduce_add_sync(0xffffffffu, n_eval);
   n_viol = __reduce_add_sync(0xffffffffu, n_viol);
@@ -1014,9 +1042,11 @@ static long long mask_stride(int col0, int col_end) {
   const long long w = ((long long)(col_end - col0) + 31) / 32;
   return (w + 127) / 128 * 128;
 }
-size_t tf32_mask_words(int row_lo, int row_hi, int col0, int col_end) {
+size_t tf32_mask_words(int row_lo, int row_hi, int col0, int col_end, int nranks) {
   const int r0 = row_lo > col0 ? row_lo : col0;
-  return (size_t)(row_hi > r0 ? row_hi - r0 : 0) * (size_t)mask_stride(col0, col_end);
+  if (row_hi <= r0) return 0;
+  const long long rows = mask_row(row_hi - 1, nranks) + 128 - ((long long)((r0 >> 7) / nranks) * 128);
+  return (size_t)rows * (size_t)mask_stride(col0, col_end);
 }
 
 static int launch_tf32_screen(const TfArgs& a, bool slab, int grid, int smem, cudaStream_t stream) {
@@ -1053,8 +1083,8 @@ static int launch_tf32_screen(const TfArgs& a, bool slab, int grid, int smem, cu
 //   pair_tf32 screen -> classify_items -> FP64 tensor kernel on dense items -> cand_scan (top-down)
 int launch_pair_tf32(const PairArgs& pa, const PairArgs& fb_in, const Tf32Buffers& tb, const void* d_items,
                      const int* h_items, int item_begin, int item_end, int row_lo, int row_hi,
-                     int all_cand, int nstage_tile, cudaStream_t stream, int* grid_out, int* smem_out,
-                     long long* launches_out) {
+                     int rank, int nranks, int all_cand, int nstage_tile, cudaStream_t stream, int* grid_out,
+                     int* smem_out, long long* launches_out) {
   if (grid_out) *grid_out = 0;
   if (item_end - item_begin <= 0) return 0;
   TfArgs a{};
@@ -1100,7 +1130,7 @@ int launch_pair_tf32(const PairArgs& pa, const PairArgs& fb_in, const Tf32Buffer
       int q = pb;
       const int s = seg_of(q - 1);
       while (q > item_begin && seg_of(q - 1) == s) --q;
-      if (tf32_mask_words(row_lo, row_hi, s * segcols, col_end) > tb.cm_words) {
+      if (tf32_mask_words(row_lo, row_hi, s * segcols, col_end, nranks) > tb.cm_words) {
         if (pb == pe) { set_error("candidate bitmask too small for one segment (%zu words)", tb.cm_words); return 1; }
         break;
       }
@@ -1110,13 +1140,14 @@ int launch_pair_tf32(const PairArgs& pa, const PairArgs& fb_in, const Tf32Buffer
     const int col0 = s_lo * segcols;
     a.item_begin = pb; a.item_end = pe;
     const int row0 = std::max(row_lo, col0);
-    a.cm_row0 = row0; a.cm_col0 = col0; a.cm_stride = mask_stride(col0, col_end);
+    const long long mrow0 = (long long)((row0 >> 7) / nranks) * 128;
+    a.cm_row0 = (int)mrow0; a.cm_nranks = nranks; a.cm_col0 = col0; a.cm_stride = mask_stride(col0, col_end);
     const int nitems = pe - pb;
     const int grid = nitems < nsm ? nitems : nsm;
     if (grid > grid_max) grid_max = grid;
     CREST_CUDA_TRY(cudaMemsetAsync(tb.cand_count + 6, 0, sizeof(unsigned), stream));
     if (all_cand)
-      CREST_CUDA_TRY(cudaMemsetAsync(tb.fmask, 0, sizeof(unsigned) * tf32_mask_words(row_lo, row_hi, col0, col_end), stream));
+      CREST_CUDA_TRY(cudaMemsetAsync(tb.fmask, 0, sizeof(unsigned) * tf32_mask_words(row_lo, row_hi, col0, col_end, nranks), stream));
     if (launch_tf32_screen(a, slab, grid, smem, stream)) return 1;
     ClassifyArgs c{};
     c.items = a.items; c.item_begin = pb; c.item_end = pe; c.item_cnt = tb.item_cnt;
@@ -1131,11 +1162,12 @@ int launch_pair_tf32(const PairArgs& pa, const PairArgs& fb_in, const Tf32Buffer
     e.xv = make_xview(pa.X, pa.L); e.xn = pa.xn; e.rot = pa.rot; e.aniso = pa.aniso;
     e.cmask = tb.cmask; e.fmask = a.fmask;
     e.row0 = row0; e.col0 = col0; e.col_end = col_end; e.nall = row_hi; e.stride = a.cm_stride;
+    e.mrow0 = (int)mrow0; e.nranks = nranks; e.rank = nranks > 1 ? rank : 0;
     e.dense = all_cand ? nullptr : tb.dense; e.unfinished = tb.unfinished;
-    e.dense_budget = (c.force_dense > 0) ? 0 : (tune().dense_budget > 0 ? tune().dense_budget : 64);
+    e.dense_budget = (c.force_dense > 0) ? 0 : (tune().dense_budget > 0 ? tune().dense_budget : -1);
     e.segcols = segcols; e.ntile = ntile;
     e.g = pa.g; e.dup = pa.dup; e.counters = tb.cand_count; e.debug_all = all_cand ? 1 : 0;
-    const int rows = row_hi - row0;
+    const int rows = (row_hi - row0) / nranks + 128;
     int sgrid = (rows + 7) / 8;
     if (sgrid > nsm * 8) sgrid = nsm * 8;
     if (sgrid < 1) sgrid = 1;

@@ -240,7 +240,8 @@ int crest_cuda_ctx_download(crest_cuda_ctx* ctx, double* rot, double* xyz_axis, 
  * [9]=work items the classifier found candidate-dense, [10]=screen violations counted in the
  * CREST_CUDA_DEBUG=3 self-check (must be 0), [11]=exact FP64 evaluations the top-down scan spent
  * (<= [8]: a row ends at its first match), [12]=flags: 1 unsafe magnitudes (every item re-done in FP64),
- * 2 dense work list overflowed (items left to the scan).  Counters accumulate since the last ctx_pack.
+ * 2 dense work list overflowed (items left to the scan), [13]=rows that met a candidate-dense item,
+ * [14]=those that ended inside their evaluation budget.  Counters accumulate since the last ctx_pack.
  * info must hold 16 entries; reading [8..12] synchronises the device. */
 int crest_cuda_ctx_info(crest_cuda_ctx* ctx, const crest_cuda_thresholds* thr, int rank,
                         int nranks, long long* info);
