@@ -44,6 +44,8 @@ def parse():
     p.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU-baseline sample time")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--from-file", action="store_true",
+                   help="also time xyz file -> rdensemble -> cregen_esort -> cregen_CRE (SURVEY 8 f1); N=1")
     p.add_argument("--no-fp64", action="store_true", help="skip the FP64-only pass reported in kernels.fp64_path")
     return p.parse_args()
 
@@ -446,6 +448,31 @@ def run_ours(args):
         if world > 1:
             dist.barrier(group=cpu_group)
 
+    from_file = None
+    if rank == 0 and world == 1 and args.from_file:
+        import tempfile
+        d = tempfile.mkdtemp(dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+        fn = os.path.join(d, "ens.xyz")
+        perm = np.random.default_rng(0).permutation(nall)      # a trajectory is not energy sorted
+        cb.wrensemble(fn, at, xyz[perm], er[perm])
+        ts = []
+        for _ in range(3):
+            t0 = time.perf_counter()
+            r = cb.rdensemble(fn, want_comments=False)
+            t1 = time.perf_counter()
+            xs, es, order, nout = cb.cregen_esort(r["xyz"], r["er"])
+            t2 = time.perf_counter()
+            full = cb.cregen_CRE_inplace(env, nat, nout, r["at"], xs[:nout], es[:nout])
+            ts.append((t1 - t0, t2 - t1, time.perf_counter() - t2))
+        best = min(ts, key=sum)
+        from_file = {"file_mb": os.path.getsize(fn) / 1e6, "rdensemble_ms": best[0] * 1e3,
+                     "cregen_esort_ms": best[1] * 1e3, "cregen_cre_ms": best[2] * 1e3, "total_ms": sum(best) * 1e3,
+                     "kept": int(full.nallout),
+                     "note": "xyz text file (reference layout, strucreader.f90:1679-1698) in /dev/shm -> "
+                             "crest_cuda_rdensemble (mmap, threaded line index, one CUDA thread per atom record) -> "
+                             "crest_cuda_cregen_esort (reference quicksort order) -> crest_cuda_cregen_cre; best of 3"}
+        os.remove(fn)
+        os.rmdir(d)
     if rank == 0:
         A = info["A"]
         fp64_peak = fp64_peak_tflops(torch, dev)
@@ -498,6 +525,8 @@ def run_ours(args):
                          "fp64_tensor_peak": fp64_peak, "note": note},
             "clocks": clocks, "e2e": e2e, "cregen_wall": cregen_wall,
         }
+        if from_file:
+            line["from_file"] = from_file
         if world == 1 and not args.no_cpu_baseline:
             cbase = cpu_sample(ens, args, args.cpu_seconds)
             cbase.pop("pairs"), cbase.pop("seconds")

@@ -23,6 +23,7 @@
 #include <string>
 #include <vector>
 #include "common.cuh"
+#include "ensemble_fast.cuh"
 #include "../../include/crest_cuda.h"
 
 namespace {
@@ -139,24 +140,40 @@ bool coordline(const std::string& line, std::string* sym, double* xyz) {
   return false;
 }
 
+// Records of a memory-mapped file through its line index (ensemble_fast.cu): what `read(ich,'(a)')`
+// delivers, one record per call, '\r' of DOS files dropped.
 struct LineReader {
-  FILE* f;
-  std::string buf;
-  explicit LineReader(FILE* fp) : f(fp) {}
+  const char* data;
+  const std::vector<unsigned long long>& ls;
+  size_t k = 0;
+  LineReader(const crest::MappedFile& f, const std::vector<unsigned long long>& index) : data(f.data), ls(index) {}
+  size_t nlines() const { return ls.size() - 1; }
   bool next(std::string& out) {
-    out.clear();
-    char tmp[1024];
-    bool any = false;
-    while (fgets(tmp, sizeof(tmp), f)) {
-      any = true;
-      const size_t n = strlen(tmp);
-      out.append(tmp, n);
-      if (n && tmp[n - 1] == '\n') { out.pop_back(); break; }
-    }
-    if (!out.empty() && out.back() == '\r') out.pop_back();
-    return any;
+    if (k >= nlines()) return false;
+    size_t b = ls[k], e = ls[k + 1];
+    ++k;
+    if (e > b && data[e - 1] == '\n') --e;
+    if (e > b && data[e - 1] == '\r') --e;
+    out.assign(data + b, e - b);
+    return true;
+  }
+  bool skip(size_t n) {                      // n records without looking at them; false at end of file
+    if (k + n > nlines()) { k = nlines(); return false; }
+    k += n;
+    return true;
   }
 };
+
+// atom records are converted on the device when there is one and the file is large enough to pay for the
+// transfer of its text (ensemble_fast.cu); the host loop below is the same coordline() either way
+bool use_device_parser(size_t natom_records) {
+  if (natom_records < 200000) return false;
+  const char* e = getenv("CREST_CUDA_IO");
+  if (e && !strcmp(e, "host")) return false;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return false; }
+  return n > 0;
+}
 
 // `read(ich,*,iostat=io) dum`: skip empty records, then the first item must be an integer.
 // returns -1 end of file, 1 conversion error (record consumed), 0 ok
@@ -218,35 +235,63 @@ int crest_cuda_e2i(const char* label) { return label ? e2i(label) : 0; }
 int crest_cuda_rdensemble_param(const char* fname, int* nat, int* nall) {
   if (!fname || !nat || !nall) { set_error("bad argument"); return 1; }
   *nat = 0; *nall = 0;
-  FILE* f = fopen(fname, "r");
-  if (!f) return 0;                                     // `inquire(exist)`: absent file = empty ensemble
-  LineReader R(f);
-  std::string line, sym;
-  bool eof = false;
-  while (!eof) {
+  crest::MappedFile f;
+  if (f.open_read(fname)) return 0;                     // `inquire(exist)`: absent file = empty ensemble
+  std::vector<unsigned long long> ls;
+  crest::index_lines(f.data, f.size, ls);
+  LineReader R(f, ls);
+  std::string line;
+  // pass 1: the record structure (count record, comment record, `dum` atom records)
+  std::vector<long long> first;                         // first atom record of every complete structure
+  std::vector<long> count;
+  for (;;) {
     long dum;
     const int io = read_count(R, &dum);
     if (io < 0) break;
     if (io > 0) continue;
     if (!R.next(line)) break;                           // comment line
-    bool bad = false;
-    for (long i = 0; i < dum; ++i) {
-      if (!R.next(line)) { eof = true; break; }
-      // `read(ich,*) str,x,y,z`: a symbol item followed by three reals
-      size_t pos = 0, b[4], e[4];
-      int n = 0;
-      while (n < 4 && next_item(line, pos, b[n], e[n])) ++n;
-      double v;
-      if (n < 4 || !parse_real(line.data() + b[1], line.data() + e[1], &v) ||
-          !parse_real(line.data() + b[2], line.data() + e[2], &v) ||
-          !parse_real(line.data() + b[3], line.data() + e[3], &v)) bad = true;
+    if (dum < 0) dum = 0;
+    const long long l0 = (long long)R.k;
+    if (!R.skip((size_t)dum)) break;                    // truncated last structure: not counted
+    first.push_back(l0);
+    count.push_back(dum);
+  }
+  // pass 2: a structure counts only if every atom record reads as `str x y z`
+  const size_t ns = first.size();
+  std::vector<char> bad(ns, 0);
+  size_t total = 0;
+  long common = ns ? count[0] : 0;
+  for (size_t s = 0; s < ns; ++s) { total += (size_t)count[s]; if (count[s] != common) common = -1; }
+  bool done = false;
+  if (common > 0 && use_device_parser(total)) {
+    std::vector<unsigned> flags;
+    if (crest::parse_atoms_device(f, ls, first, (int)common, nullptr, flags, 1) == 0) {
+      for (size_t s = 0; s < ns; ++s)
+        for (long j = 0; j < common; ++j)
+          if (flags[s * (size_t)common + j] == 2) { bad[s] = 1; break; }
+      done = true;
     }
-    if (eof) break;
-    if (bad) continue;
-    if (dum > *nat) *nat = (int)dum;
+  }
+  if (!done)
+    for (size_t s = 0; s < ns; ++s) {
+      R.k = (size_t)first[s];
+      for (long i = 0; i < count[s]; ++i) {
+        R.next(line);
+        // `read(ich,*) str,x,y,z`: a symbol item followed by three reals
+        size_t pos = 0, b[4], e[4];
+        int n = 0;
+        while (n < 4 && next_item(line, pos, b[n], e[n])) ++n;
+        double v;
+        if (n < 4 || !parse_real(line.data() + b[1], line.data() + e[1], &v) ||
+            !parse_real(line.data() + b[2], line.data() + e[2], &v) ||
+            !parse_real(line.data() + b[3], line.data() + e[3], &v)) { bad[s] = 1; break; }
+      }
+    }
+  for (size_t s = 0; s < ns; ++s) {
+    if (bad[s]) continue;
+    if (count[s] > *nat) *nat = (int)count[s];
     *nall += 1;
   }
-  fclose(f);
   return 0;
 }
 
@@ -255,12 +300,15 @@ int crest_cuda_rdensemble(const char* fname, int nat, int nall, int* at, double*
   if (!fname || nat <= 0 || nall < 0 || !at || (!xyz && nall) || comment_len < 0) {
     set_error("bad argument"); return 1;
   }
-  FILE* f = fopen(fname, "r");
-  if (!f) { set_error("cannot open %s", fname); return 1; }
-  LineReader R(f);
+  crest::MappedFile f;
+  if (f.open_read(fname)) { set_error("cannot open %s", fname); return 1; }
+  std::vector<unsigned long long> ls;
+  crest::index_lines(f.data, f.size, ls);
+  LineReader R(f, ls);
   std::string line, sym;
-  for (size_t k = 0; k < (size_t)3 * nat * nall; ++k) xyz[k] = 0.0;   // `xyz = 0.0_wp`
   if (comments) memset(comments, ' ', (size_t)comment_len * nall);
+  // pass 1: the record structure; energies and comments are taken on the way
+  std::vector<long long> first;
   int i = 0;
   bool eof = false;
   while (i < nall && !eof) {
@@ -287,23 +335,50 @@ int crest_cuda_rdensemble(const char* fname, int nat, int nall, int* at, double*
       while (!c.empty() && c.back() == ' ') c.pop_back();
       memcpy(comments + (size_t)comment_len * i, c.data(), c.size() < (size_t)comment_len ? c.size() : (size_t)comment_len);
     }
-    for (long j = 0; j < dum; ++j) {
-      if (!R.next(line)) { eof = true; break; }
-      double v[3];
-      if (!coordline(line, &sym, v)) {
-        fclose(f);
-        set_error("%s: structure %d, atom %ld: cannot read a coordinate line", fname, i + 1, j + 1);
-        return 1;
-      }
-      double* dst = xyz + ((size_t)i * nat + j) * 3;
-      dst[0] = v[0]; dst[1] = v[1]; dst[2] = v[2];
-      at[j] = e2i(sym);
-    }
-    if (eof) break;
+    const long long l0 = (long long)R.k;
+    if (!R.skip((size_t)nat)) { eof = true; break; }
+    first.push_back(l0);
     ++i;
   }
-  fclose(f);
-  if (nread) *nread = i;
+  const size_t ns = first.size();
+  // pass 2: the atom records
+  auto host_record = [&](size_t s, long j, bool want_sym) -> bool {
+    R.k = (size_t)first[s] + (size_t)j;
+    R.next(line);
+    double v[3];
+    if (!coordline(line, &sym, v)) return false;
+    double* dst = xyz + (s * (size_t)nat + j) * 3;
+    dst[0] = v[0]; dst[1] = v[1]; dst[2] = v[2];
+    if (want_sym) at[j] = e2i(sym);
+    return true;
+  };
+  bool done = false;
+  if (ns && use_device_parser(ns * (size_t)nat)) {
+    std::vector<unsigned> flags;
+    if (crest::parse_atoms_device(f, ls, first, nat, xyz, flags, 0) == 0) {
+      done = true;
+      for (size_t q = 0; q < flags.size(); ++q) {
+        if (flags[q] == 0) continue;
+        const size_t s = q / (size_t)nat;
+        const long j = (long)(q % (size_t)nat);
+        if (!host_record(s, j, false)) {                // flag 1: beyond the exact fast path; flag 2: does not scan
+          set_error("%s: structure %d, atom %ld: cannot read a coordinate line", fname, (int)s + 1, j + 1);
+          return 1;
+        }
+      }
+      // the symbols: `at` holds what the LAST structure read says, like the record-by-record loop
+      for (long j = 0; j < nat; ++j) host_record(ns - 1, j, true);
+    }
+  }
+  if (!done)
+    for (size_t s = 0; s < ns; ++s)
+      for (long j = 0; j < nat; ++j)
+        if (!host_record(s, j, true)) {
+          set_error("%s: structure %d, atom %ld: cannot read a coordinate line", fname, (int)s + 1, j + 1);
+          return 1;
+        }
+  for (size_t k = (size_t)3 * nat * ns; k < (size_t)3 * nat * nall; ++k) xyz[k] = 0.0;   // `xyz = 0.0_wp`
+  if (nread) *nread = (int)ns;
   if (eof) { set_error("error while reading ensemble file."); return 1; }   // strucreader.f90:476-478
   return 0;
 }
