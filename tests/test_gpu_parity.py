@@ -80,7 +80,7 @@ def rows_of_allpairs(rmat, n):
 
 
 GOLD_FILES = sorted(p for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-                    if "pairs_kat" not in p and not os.path.basename(p).startswith("f"))
+                    if "pairs_kat" not in p and not os.path.basename(p).startswith(("f", "c3_full")))
 
 
 @pytest.mark.parametrize("path", GOLD_FILES, ids=lambda p: os.path.basename(p)[:-4])
@@ -422,11 +422,42 @@ def test_full_size_properties_c3(cb, oracle):
         if np.any(np.abs(r - 0.125) <= RMSD_TOL) or np.any(np.abs(r - 0.25) <= RMSD_TOL):
             listed.add(i)
         assert dup[i] == exp or i in listed, (i, dup[i], exp)
-    assert set(diff.tolist()) <= listed or len(diff) <= 8, diff[:20]
+    assert set(diff.tolist()) <= listed, diff[:20]
     # rot. constants of the sampled rows
     ref_rot = oracle.rotconst(at, xyz[rows])
     assert np.abs(rot[rows] / ref_rot - 1).max() < ROT_TOL
     ctx.close()
+
+
+def test_full_size_golden_c3(cb):
+    """BASELINE config C3 at FULL size against the oracle's complete result (tests/golden/c3_full.npz:
+    5.0e9 pairs through oracle/, 6869 s on 7 threads, tests/make_golden_c3_full.py): WHOLE arrays - the
+    stage-A links after the root chase, the kept-first order, the rotamer groups, the count - are
+    identical; the oracle found no row within 1e-6 A of a threshold, so nothing is exempt."""
+    import hashlib
+    g = np.load(os.path.join(GOLDEN, "c3_full.npz"))
+    ens = synth.make_config("C3")
+    at, xyz, er = ens["at"], ens["xyz"], ens["er"]
+    assert hashlib.sha256(xyz.tobytes() + er.tobytes() + at.tobytes()).hexdigest() == str(g["input_sha256"])
+    n, nat, _ = xyz.shape
+    assert len(g["boundary_rows"]) == 0
+    env = cb.Env(ethr=1e9)
+    a = cb.cregen_dup(env, nat, n, at, xyz, er, want_xyz=False)
+    assert a["npairs"] == int(g["klong"]) == n * (n - 1) // 2
+    assert np.array_equal(a["dup"], g["dup"])
+    full = cb.cregen_CRE(env, nat, n, at, xyz, er)
+    assert full.nallout == int(g["nallout"])
+    assert np.array_equal(full.order, g["orderref"])
+    assert np.array_equal(full.group, g["group"])
+    assert np.abs(full.rot / g["rot"] - 1).max() < ROT_TOL
+    # and the FP64-only kernels
+    from crest_b200 import cregen
+    cregen.set_tune("notf32")
+    try:
+        b = cb.cregen_dup(env, nat, n, at, xyz, er, want_xyz=False)
+    finally:
+        cregen.set_tune(None)
+    assert np.array_equal(b["dup"], g["dup"])
 
 
 # ------------------------------------------------------------------------------------------------

@@ -296,7 +296,7 @@ def test_band_equals_allpairs_inside_band(oracle):
 
 
 GOLD_FILES = sorted(p for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-                    if not os.path.basename(p).startswith("f"))   # f2_/f3_: tests/test_compare.py
+                    if not os.path.basename(p).startswith(("f", "c3_full")))   # f2_/f3_: tests/test_compare.py
 
 
 def gold_kwargs(g):
