@@ -11,164 +11,27 @@
 //       (rmat > rthr and mirror rmsd < 0.75 rthr), uniqueCore(rmat, nrot, rthr) = number of
 //       "backbone" structures, enantiofac spread over equal symmetry symbols (symmap).
 //
-// Both need the RMSD itself as a double (no float32 rounding, no "far" screen), so the covariance
-// is accumulated in FP64 on the CUDA cores from a (3A x N) coordinate matrix (row = component*A +
-// atom, conformer index fastest: a 32-conformer tile row is one 256 B run) and the quartic of
-// qcp.cuh is solved per pair.  Sizes are small next to the CREGEN triangle (maxcompare x rotamers).
+// Both need the RMSD itself as a double (no float32 rounding, no "far" screen).  They run on the SAME FP64
+// tensor mainloops as CREGEN's FP64 path (pair_col.cu for <= 88 atoms, pair_tile.cu above; DMMA m8n8k4,
+// bulk-copy operand rings): each ensemble is packed by pack_axis into the operand layout (the rigid motion
+// it applies does not change an RMSD), the sweep is a rectangular (compare) or block-diagonal (intraconf)
+// item list, and every valid pair leaves the kernel through sink_pair (qcp.cuh) instead of the CREGEN
+// decisions.  Round 1 ran these on the CUDA cores at 0.17 of the DGEMM peak.
 //
 // uniqueCore (entropic.f90:1074-1095) is order dependent as written, but its count is not: i opens
 // a new group iff mp(i) == 0 when the loop reaches it, and mp(i) is set by exactly those earlier
 // i' < i with mat(i',i) < thr (every i' writes ALL its neighbours, whether or not it opened a
 // group).  So  uniqueCore = #{ i : no j < i with rmat(i,j) < thr }  — a per-row OR like K4.
+#include <algorithm>
 #include <vector>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
-#include "common.cuh"
+#include "ctx.cuh"
 #include "qcp.cuh"
-#include "../../include/crest_cuda.h"
 
 namespace crest {
-
-constexpr int kBT = 32;   // conformers per tile edge
-constexpr int kBK = 16;   // atoms per shared-memory chunk
-
-// One warp per structure: gather the selected atoms, remove their unweighted centroid
-// (ls_rmsd.f90:105-119), write the (3A x npad) matrix and the centred squared norm.
-__global__ void __launch_bounds__(128)
-bp_center_kernel(int nat, int n, int A, const int* __restrict__ sel, const double* __restrict__ xyz,
-                 int npad, double* __restrict__ Xc, double* __restrict__ xn) {
-  const int lane = threadIdx.x & 31;
-  const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (s >= n) return;
-  const double* x = xyz + (size_t)3 * nat * s;
-  double c[3] = {0, 0, 0};
-  for (int k = lane; k < A; k += 32) {
-    const int at = sel ? sel[k] : k;
-    for (int a = 0; a < 3; ++a) c[a] += x[3 * at + a];
-  }
-  for (int a = 0; a < 3; ++a) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) c[a] += __shfl_xor_sync(0xffffffffu, c[a], o);
-    c[a] /= (double)A;
-  }
-  double sq = 0.0;
-  for (int k = lane; k < A; k += 32) {
-    const int at = sel ? sel[k] : k;
-    for (int a = 0; a < 3; ++a) {
-      const double v = x[3 * at + a] - c[a];
-      sq += v * v;
-      Xc[((size_t)a * A + k) * npad + s] = v;
-    }
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
-  if (lane == 0) xn[s] = sq;
-}
-
-struct BpArgs {
-  const double* X1; const double* xn1; int n1, npad1;   // i side
-  const double* X2; const double* xn2; int n2, npad2;   // j side
-  int A;
-  // MODE 0 (compare): dense rectangle, block ids per structure, rmat(nconf1,nconf2) as ordered bits
-  const int* blk1; const int* blk2; int nconf1;
-  unsigned long long* rmat_bits;
-  // MODE 1 (intra): tile list {i0, j0, lim, co}; pairs j < i < lim
-  const int4* tiles;
-  int* has_earlier;    // [n1] 1 = some j < i of the same conformer with rmsd < rthr
-  int* enantio;        // [nconf] 1 = enantiomer probe fired
-  double rthr, rthr_enantio;
-};
-
-template <int MODE>
-__global__ void __launch_bounds__(256, 2)   // <= 128 registers: two CTAs per SM (ncu: 130 registers gave one)
-bp_pair_kernel(const BpArgs p, int ntj) {
-  __shared__ __align__(16) double xs[kBK][3][kBT];
-  __shared__ __align__(16) double ys[kBK][3][kBT];
-  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
-  int i0, j0, lim = 0, co = 0;
-  if (MODE == 0) {
-    i0 = (blockIdx.x / ntj) * kBT;
-    j0 = (blockIdx.x % ntj) * kBT;
-  } else {
-    const int4 t = p.tiles[blockIdx.x];
-    i0 = t.x; j0 = t.y; lim = t.z; co = t.w;
-  }
-  double r[2][2][9];
-#pragma unroll
-  for (int u = 0; u < 2; ++u)
-#pragma unroll
-    for (int v = 0; v < 2; ++v)
-#pragma unroll
-      for (int z = 0; z < 9; ++z) r[u][v][z] = 0.0;
-
-  for (int k0 = 0; k0 < p.A; k0 += kBK) {
-    const int kc = min(kBK, p.A - k0);
-    for (int e = tid; e < kBK * 3 * kBT; e += 256) {
-      const int cf = e & 31, a = (e >> 5) % 3, kk = e / 96;
-      double xv = 0.0, yv = 0.0;
-      if (kk < kc) {
-        // the matrices are zero padded to a multiple of 32 conformers (+ one tile for ragged tile
-        // origins of the block-diagonal mode), so no conformer bound is needed
-        xv = p.X1[((size_t)a * p.A + k0 + kk) * p.npad1 + i0 + cf];
-        yv = p.X2[((size_t)a * p.A + k0 + kk) * p.npad2 + j0 + cf];
-      }
-      xs[kk][a][cf] = xv;
-      ys[kk][a][cf] = yv;
-    }
-    __syncthreads();
-#pragma unroll 4
-    for (int kk = 0; kk < kBK; ++kk) {
-      double2 xa[3], ya[3];
-#pragma unroll
-      for (int a = 0; a < 3; ++a) {
-        xa[a] = *reinterpret_cast<const double2*>(&xs[kk][a][2 * ty]);
-        ya[a] = *reinterpret_cast<const double2*>(&ys[kk][a][2 * tx]);
-      }
-#pragma unroll
-      for (int a = 0; a < 3; ++a)
-#pragma unroll
-        for (int b = 0; b < 3; ++b) {
-          r[0][0][3 * a + b] = fma(xa[a].x, ya[b].x, r[0][0][3 * a + b]);
-          r[0][1][3 * a + b] = fma(xa[a].x, ya[b].y, r[0][1][3 * a + b]);
-          r[1][0][3 * a + b] = fma(xa[a].y, ya[b].x, r[1][0][3 * a + b]);
-          r[1][1][3 * a + b] = fma(xa[a].y, ya[b].y, r[1][1][3 * a + b]);
-        }
-    }
-    __syncthreads();
-  }
-
-  const double invA = 1.0 / (double)p.A;
-#pragma unroll
-  for (int u = 0; u < 2; ++u)
-#pragma unroll
-    for (int v = 0; v < 2; ++v) {
-      const int i = i0 + 2 * ty + u, j = j0 + 2 * tx + v;
-      if (MODE == 0) {
-        if (i >= p.n1 || j >= p.n2) continue;
-        const int ci = p.blk1[i], cj = p.blk2[j];
-        if (ci < 0 || cj < 0) continue;
-        const double s = p.xn1[i] + p.xn2[j];
-        const double e = pair_e(r[u][v], s, 0, 0);
-        const double val = sqrt(fmax(0.0, e) * invA);      // ls_rmsd.f90:163
-        // non-negative doubles order like their bit patterns; the plain read only filters
-        // (the slot decreases monotonically), the atomic decides
-        unsigned long long* slot = p.rmat_bits + ci + (size_t)p.nconf1 * cj;
-        const unsigned long long bits = (unsigned long long)__double_as_longlong(val);
-        if (bits < *reinterpret_cast<volatile unsigned long long*>(slot)) atomicMin(slot, bits);
-      } else {
-        if (!(j < i && i < lim)) continue;
-        const double s = p.xn1[i] + p.xn2[j];
-        const double e = pair_e(r[u][v], s, 0, 0);
-        const double val = sqrt(fmax(0.0, e) * invA);
-        if (val < p.rthr) p.has_earlier[i] = 1;            // entropic.f90:1088 via uniqueCore
-        if (val > p.rthr) {                                // entropic.f90:1024-1031
-          const double em = pair_e(r[u][v], s, 0, 1);
-          const double vm = sqrt(fmax(0.0, em) * invA);
-          if (vm < p.rthr_enantio) p.enantio[co] = 1;
-        }
-      }
-    }
-}
 
 namespace {
 
@@ -188,19 +51,59 @@ struct DevBuf {   // frees on scope exit; every entry point below is a self-cont
   }
 };
 
-// upload xyz(3,nat,n), centre on the selected atoms, leave Xc (3A x npad, zero padded) and xn
-int center_ensemble(DevBuf& buf, int nat, int n, int A, const int* d_sel, const double* xyz,
-                    int* npad_out, double** Xc_out, double** xn_out) {
-  const int npad = (n + kBT - 1) / kBT * kBT + kBT;
-  double *d_xyz, *d_X, *d_xn;
-  if (buf.alloc(&d_xyz, (size_t)3 * nat * n) || buf.alloc(&d_X, (size_t)3 * A * npad) ||
-      buf.alloc(&d_xn, (size_t)npad)) return 1;
-  CREST_CUDA_TRY(cudaMemcpy(d_xyz, xyz, sizeof(double) * 3 * nat * (size_t)n, cudaMemcpyHostToDevice));
-  CREST_CUDA_TRY(cudaMemset(d_X, 0, sizeof(double) * 3 * A * (size_t)npad));
-  CREST_CUDA_TRY(cudaMemset(d_xn, 0, sizeof(double) * npad));
-  bp_center_kernel<<<(n + 3) / 4, 128>>>(nat, n, A, d_sel, d_xyz, npad, d_X, d_xn);
-  CREST_CUDA_TRY(cudaGetLastError());
-  *npad_out = npad; *Xc_out = d_X; *xn_out = d_xn;
+struct CtxOwner {   // a context for the duration of one call
+  crest_cuda_ctx* c = nullptr;
+  ~CtxOwner() { crest_cuda_ctx_destroy(c); }
+};
+
+// ensemble -> FP64 operand layout (X, centred squared norms) through the CREGEN pack kernel.  The masses
+// only steer the rigid frame pack_axis chooses, which no RMSD depends on: every atom counts as carbon.
+int pack_operand(CtxOwner& o, int nat, int n, const double* xyz, const int* mask) {
+  if (crest_cuda_ctx_create(&o.c, -1)) return 1;
+  o.c->fp64_only = true;
+  std::vector<int> at((size_t)nat, 6);
+  std::vector<double> er((size_t)(n > 0 ? n : 1), 0.0);
+  if (crest_cuda_ctx_upload(o.c, nat, n, at.data(), xyz, er.data(), mask, 0)) return 1;
+  return crest_cuda_ctx_pack(o.c, nullptr);
+}
+
+// the sweep: work = column items {J, u_begin, u_end, 0} (A <= 88) or row tiles {panel, j-tile, 0, 0}
+int run_sink(const crest_cuda_ctx* ci, const PairSink& sink, const std::vector<int4>& work) {
+  if (work.empty()) return 0;
+  DevBuf buf;
+  int4* d_work;
+  if (buf.alloc(&d_work, work.size())) return 1;
+  CREST_CUDA_TRY(cudaMemcpy(d_work, work.data(), sizeof(int4) * work.size(), cudaMemcpyHostToDevice));
+  PairArgs a{};
+  a.sink = sink;
+  a.X = ci->d_X; a.xn = ci->d_xn; a.er = ci->d_er; a.rot = ci->d_rot; a.aniso = ci->d_aniso;
+  a.nall = ci->nall; a.dup = ci->d_dup; a.npairs = ci->d_npairs; a.n8 = (ci->nall + 7) / 8;
+  a.L = ci->L;
+  a.g.ethr = 1e300; a.g.E1 = a.g.E2 = 0.0; a.g.E2_up = 0.0f; a.g.enantio = 0; a.g.debug = 0;
+  int grid = 0, smem = 0;
+  const bool timing = getenv("CREST_CUDA_TIMING") && atoi(getenv("CREST_CUDA_TIMING")) > 0;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (timing) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, nullptr); }
+  if (ci->use_col) {
+    if (launch_pair_cols(a, d_work, 0, (int)work.size(), nullptr, &grid, &smem)) return 1;
+  } else {
+    int ns = 0;
+    pair_smem_bytes(ci->L, &ns);
+    a.tiles = d_work; a.tile_begin = 0; a.tile_end = (long long)work.size();
+    if (launch_pair_tiles(a, ns, nullptr, &grid, &smem)) return 1;
+  }
+  if (timing) cudaEventRecord(e1, nullptr);
+  CREST_CUDA_TRY(cudaDeviceSynchronize());
+  if (timing) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double pairs = sink.mode == 1 ? (double)sink.ni * sink.nj : 0.0;
+    fprintf(stderr, "[blockpair] sweep kernel (%s, %zu items, grid %d): %.3f ms%s", ci->use_col ? "pair_col" : "pair_tile",
+            work.size(), grid, ms, pairs > 0 ? "" : "\n");
+    if (pairs > 0) fprintf(stderr, " = %.3g pairs/s, %.2f TFLOP/s (18*A per pair)\n", pairs / (ms * 1e-3),
+                           18.0 * sink.A * pairs / (ms * 1e-3) / 1e12);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+  }
   return 0;
 }
 
@@ -244,10 +147,9 @@ int crest_cuda_compare_blocks(int nat, int nall1, const double* xyz1, int nconf1
   int n1 = 0, n2 = 0;
   for (int c = 0; c < nconf1; ++c) n1 = e1[c] > n1 ? e1[c] : n1;
   for (int c = 0; c < nconf2; ++c) n2 = e2[c] > n2 ? e2[c] : n2;
+  CtxOwner c1, c2;
+  if (pack_operand(c1, nat, n1, xyz1, nullptr) || pack_operand(c2, nat, n2, xyz2, nullptr)) return 1;
   DevBuf buf;
-  int npad1, npad2; double *X1, *X2, *xn1, *xn2;
-  if (center_ensemble(buf, nat, n1, nat, nullptr, xyz1, &npad1, &X1, &xn1)) return 1;
-  if (center_ensemble(buf, nat, n2, nat, nullptr, xyz2, &npad2, &X2, &xn2)) return 1;
   int *d_b1, *d_b2; unsigned long long* d_r;
   if (buf.alloc(&d_b1, (size_t)n1) || buf.alloc(&d_b2, (size_t)n2) || buf.alloc(&d_r, nout)) return 1;
   CREST_CUDA_TRY(cudaMemcpy(d_b1, blk1.data(), sizeof(int) * n1, cudaMemcpyHostToDevice));
@@ -255,14 +157,27 @@ int crest_cuda_compare_blocks(int nat, int nall1, const double* xyz1, int nconf1
   // +inf seed: the reference's 100 (ensemblecomp.f90:228) is overwritten by every rotamer pair
   std::vector<double> seed(nout, __builtin_inf());
   CREST_CUDA_TRY(cudaMemcpy(d_r, seed.data(), sizeof(double) * nout, cudaMemcpyHostToDevice));
-  BpArgs p{};
-  p.X1 = X1; p.xn1 = xn1; p.n1 = n1; p.npad1 = npad1;
-  p.X2 = X2; p.xn2 = xn2; p.n2 = n2; p.npad2 = npad2;
-  p.A = nat; p.blk1 = d_b1; p.blk2 = d_b2; p.nconf1 = nconf1; p.rmat_bits = d_r;
-  const long long nti = (n1 + kBT - 1) / kBT, ntj = (n2 + kBT - 1) / kBT;
-  if (nti * ntj > 0x7fffffffLL) { set_error("compare: too many tiles"); return 1; }
-  bp_pair_kernel<0><<<(unsigned)(nti * ntj), 256>>>(p, (int)ntj);
-  CREST_CUDA_TRY(cudaGetLastError());
+  PairSink k{};
+  k.mode = 1; k.Xj = c2.c->d_X; k.xnj = c2.c->d_xn; k.ni = n1; k.nj = n2;
+  k.blk_i = d_b1; k.blk_j = d_b2; k.nconf1 = nconf1; k.rmat_bits = d_r; k.A = nat;
+  // the whole n1 x n2 rectangle: ensemble 2 in resident j-tiles of 64, ensemble 1 streaming past them
+  std::vector<int4> work;
+  const int nJ = (n2 + 63) / 64;
+  if (c1.c->use_col) {
+    const int nu = (n1 + kUnit - 1) / kUnit;
+    int nseg = (148 * 8 + nJ - 1) / nJ;                  // >= 8 items per SM
+    if (nseg > nu) nseg = nu;
+    if (nseg < 1) nseg = 1;
+    for (int sg = 0; sg < nseg; ++sg) {                  // segment-major: concurrent CTAs stream the same i-units
+      const int u0 = (int)((long long)nu * sg / nseg), u1 = (int)((long long)nu * (sg + 1) / nseg);
+      if (u1 > u0) for (int J = 0; J < nJ; ++J) work.push_back(make_int4(J, u0, u1, 0));
+    }
+  } else {
+    const int np = (n1 + kPanel - 1) / kPanel;
+    for (int P = 0; P < np; ++P)
+      for (int J = 0; J < nJ; ++J) work.push_back(make_int4(P, J, 0, 0));
+  }
+  if (run_sink(c1.c, k, work)) return 1;
   CREST_CUDA_TRY(cudaMemcpy(rmat, d_r, sizeof(double) * nout, cudaMemcpyDeviceToHost));
   return 0;
 }
@@ -318,34 +233,60 @@ int crest_cuda_intraconf(int nat, int nall, const double* xyz, const int* inc, i
   }
   if ((int)sel.size() != rednat) { set_error("inc(:) must hold 0/1 flags"); return 1; }
   const double rthr = 0.125;                           // entropic.f90:974
-  std::vector<int4> tiles;
   int nmax = 0;
+  std::vector<int> conf_of((size_t)(nall > 0 ? nall : 1), -1);
   for (int c = 0; c < nconf; ++c) {
     if (nrot[c] <= 1) continue;
     const int lo = low[c] - 1, hi = lo + nrot[c];
     if (lo < 0 || hi > nall) { set_error("conformer %d: rotamers [%d,%d] outside 1..%d", c + 1, low[c], hi, nall); return 1; }
     nmax = hi > nmax ? hi : nmax;
-    for (int i0 = lo; i0 < hi; i0 += kBT)
-      for (int j0 = lo; j0 <= i0; j0 += kBT) tiles.push_back(make_int4(i0, j0, hi, c));
+    for (int s = lo; s < hi; ++s) conf_of[s] = c;      // later conformers win, as in the tile list of round 1
   }
   std::vector<int> has((size_t)(nmax > 0 ? nmax : 1), 0), en((size_t)(nconf > 0 ? nconf : 1), 0);
-  if (!tiles.empty()) {
+  if (nmax > 0) {
+    std::vector<int> mask((size_t)nat, 0);
+    for (int k : sel) mask[k] = 1;
+    CtxOwner cx;
+    if (pack_operand(cx, nat, nmax, xyz, mask.data())) return 1;
     DevBuf buf;
-    int npad; double *X, *xn; int *d_sel, *d_has, *d_en; int4* d_tiles;
-    if (buf.alloc(&d_sel, sel.size())) return 1;
-    CREST_CUDA_TRY(cudaMemcpy(d_sel, sel.data(), sizeof(int) * sel.size(), cudaMemcpyHostToDevice));
-    if (center_ensemble(buf, nat, nmax, rednat, d_sel, xyz, &npad, &X, &xn)) return 1;
-    if (buf.alloc(&d_has, has.size()) || buf.alloc(&d_en, en.size()) || buf.alloc(&d_tiles, tiles.size())) return 1;
+    int *d_conf, *d_has, *d_en;
+    if (buf.alloc(&d_conf, (size_t)nmax) || buf.alloc(&d_has, has.size()) || buf.alloc(&d_en, en.size())) return 1;
+    CREST_CUDA_TRY(cudaMemcpy(d_conf, conf_of.data(), sizeof(int) * nmax, cudaMemcpyHostToDevice));
     CREST_CUDA_TRY(cudaMemset(d_has, 0, sizeof(int) * has.size()));
     CREST_CUDA_TRY(cudaMemset(d_en, 0, sizeof(int) * en.size()));
-    CREST_CUDA_TRY(cudaMemcpy(d_tiles, tiles.data(), sizeof(int4) * tiles.size(), cudaMemcpyHostToDevice));
-    BpArgs p{};
-    p.X1 = X; p.xn1 = xn; p.n1 = nmax; p.npad1 = npad;
-    p.X2 = X; p.xn2 = xn; p.n2 = nmax; p.npad2 = npad;
-    p.A = rednat; p.tiles = d_tiles; p.has_earlier = d_has; p.enantio = d_en;
-    p.rthr = rthr; p.rthr_enantio = rthr * 0.75;
-    bp_pair_kernel<1><<<(unsigned)tiles.size(), 256>>>(p, 0);
-    CREST_CUDA_TRY(cudaGetLastError());
+    PairSink k{};
+    k.mode = 2; k.ni = nmax; k.nj = nmax; k.blk_i = d_conf; k.blk_j = d_conf;
+    k.has_earlier = d_has; k.enantio = d_en; k.rthr = rthr; k.rthr_enantio = rthr * 0.75; k.A = rednat;
+    // block diagonal: per conformer the j-tiles its rotamers touch and, per j-tile, the rows at or below it;
+    // a (row block, j-tile) shared by neighbouring small conformers is listed once
+    std::vector<int4> work;
+    std::vector<long long> seen;
+    const bool col = cx.c->use_col;
+    const int rb = col ? kUnit : kPanel;               // rows per work unit
+    for (int c = 0; c < nconf; ++c) {
+      if (nrot[c] <= 1) continue;
+      const int lo = low[c] - 1, hi = lo + nrot[c];
+      for (int J = lo / 64; J <= (hi - 1) / 64; ++J) {
+        const int r0 = std::max(lo, J * 64) / rb, r1 = (hi - 1) / rb + 1;
+        if (col) {
+          const long long key = ((long long)J << 40) | ((long long)r0 << 20) | r1;
+          if (std::find(seen.begin(), seen.end(), key) == seen.end()) {
+            seen.push_back(key);
+            work.push_back(make_int4(J, r0, r1, 0));
+          }
+        } else {
+          for (int P = r0; P < r1; ++P) {
+            const long long key = ((long long)J << 32) | P;
+            if (std::find(seen.begin(), seen.end(), key) == seen.end()) {
+              seen.push_back(key);
+              work.push_back(make_int4(P, J, 0, 0));
+            }
+          }
+        }
+        if (seen.size() > 64) seen.erase(seen.begin(), seen.begin() + 32);   // neighbours only can collide
+      }
+    }
+    if (run_sink(cx.c, k, work)) return 1;
     CREST_CUDA_TRY(cudaMemcpy(has.data(), d_has, sizeof(int) * has.size(), cudaMemcpyDeviceToHost));
     CREST_CUDA_TRY(cudaMemcpy(en.data(), d_en, sizeof(int) * en.size(), cudaMemcpyDeviceToHost));
   }

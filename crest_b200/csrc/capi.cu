@@ -489,7 +489,7 @@ int crest_cuda_ctx_upload(crest_cuda_ctx* c, int nat, int nall, const int* at, c
   c->tf_items_ethr = std::numeric_limits<double>::quiet_NaN();
   c->stage_tile.clear();
   c->dup_target = nullptr;
-  c->use_tf32 = !tune().no_tf32 && nall >= 2;
+  c->use_tf32 = !tune().no_tf32 && !c->fp64_only && nall >= 2;
   if (c->use_col) { c->tf.nslab = 1; c->tf.kslab = c->L.KU; }
   else { c->tf.kslab = kTfSlabSlots; c->tf.nslab = (c->L.nslab * c->L.KU + kTfSlabSlots - 1) / kTfSlabSlots; }
   c->ntile = (nall + 127) / 128;

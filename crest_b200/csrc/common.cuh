@@ -117,7 +117,26 @@ int launch_pack_axis(int nat, int nall, const int* d_at, const double* d_xyz, co
                      cudaStream_t stream);
 int launch_rotconst(int nat, int n, const int* d_at, const double* d_xyz, double* d_rot,
                     cudaStream_t stream);
+// Pair SINK: the callers of rmsd() beside cregen_CRE (blockpair.cu: compare_ensembles, intraconfRMSD) run
+// the SAME FP64 tensor mainloops (pair_col.cu / pair_tile.cu) over rectangular or block-diagonal item
+// lists; instead of the CREGEN decisions every valid pair gets its exact RMSD and goes to the sink.
+struct PairSink {
+  int mode;               // 0 none (CREGEN), 1 compare_blocks (min per block pair), 2 intraconf
+  const double* Xj;       // j-side operand and norms (mode 1: the second ensemble; else the i side)
+  const double* xnj;
+  int ni, nj;             // structures on either side
+  const int* blk_i;       // block (conformer) id per structure, -1 = none
+  const int* blk_j;
+  int nconf1;
+  unsigned long long* rmat_bits;   // mode 1: rmat(nconf1, nconf2) as ordered bit patterns, atomicMin
+  int* has_earlier;       // mode 2: [ni] 1 = some j < i of the same conformer with rmsd < rthr
+  int* enantio;           // mode 2: [nconf] 1 = enantiomer probe fired
+  double rthr, rthr_enantio;
+  int A;                  // atoms in the RMSD
+};
+
 struct PairArgs {
+  PairSink sink;         // zero-initialised = CREGEN
   const double* X;       // packed coordinates
   const double* xn;      // centred squared norms
   const double* er;      // energies (Hartree, ascending)

@@ -41,6 +41,7 @@ struct crest_cuda_ctx {
   long long launches = 0;
   int last_grid = 0, last_smem = 0;
   // tensor-core screen (pair_tf32.cu): TF32 operand copies, candidate list, its own work list
+  bool fp64_only = false;              // set before ctx_upload: no TF32 operands / candidate mask (blockpair.cu)
   bool use_tf32 = false;
   int ntile = 0;                       // i-tiles of 128 conformers
   crest::Tf32Buffers tf{};

@@ -120,6 +120,7 @@ __device__ __forceinline__ unsigned unit_block(double (&cur)[2][9][2], const dou
 struct ColItem { int J; int u_begin; int u_end; int edge; };
 
 struct ColArgs {
+  PairSink sink;         // mode != 0: every valid pair goes to sink_pair (blockpair.cu)
   const double* X;       // column layout: [unit][comp][16][KS]
   const double* xn;
   const double* er;
@@ -154,6 +155,17 @@ __device__ __forceinline__ void unit_exact(const ColArgs& a, const ColWarp& w,
                                            const double (&acc)[2][9][2], const UnitMeta& m,
                                            unsigned cand) {
   const int i = m.i;
+  if (a.sink.mode) {
+#pragma unroll 1
+    for (int q = 0; q < 4; ++q) {
+      if (!((cand >> q) & 1u)) continue;
+      const int nj = q >> 1, p = q & 1;
+      const int j = m.j0w + nj * 8 + 2 * w.tq + p;
+      sink_pair(a.sink, i, j, acc[nj][0][p], acc[nj][1][p], acc[nj][2][p], acc[nj][3][p], acc[nj][4][p],
+                acc[nj][5][p], acc[nj][6][p], acc[nj][7][p], acc[nj][8][p], m.xni + m.xnj[nj][p]);
+    }
+    return;
+  }
 #pragma unroll
   for (int nj = 0; nj < 2; ++nj) {
     unsigned hit[2] = {0u, 0u};
@@ -229,7 +241,9 @@ __device__ __forceinline__ void unit_meta(const ColArgs& a, const ColWarp& w, in
     for (int p = 0; p < 2; ++p) {
       const int j = m.j0w + nj * 8 + 2 * w.tq + p;
       m.xnj[nj][p] = xnj_item[nj][p];
-      ok |= ((iok && (j < i)) ? 1u : 0u) << (nj * 2 + p);
+      // CREGEN and intraconf: the triangle j < i; compare (sink mode 1): the whole rectangle
+      const bool jok = a.sink.mode == 1 ? j < a.sink.nj : j < i;
+      ok |= ((iok && jok) ? 1u : 0u) << (nj * 2 + p);
     }
   if (item_edge) {
     // max de of the unit sits at (largest i, smallest j)
@@ -313,12 +327,12 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
 #pragma unroll
       for (int p = 0; p < 2; ++p) {
         const int j = J * kColJ + w.wj * 16 + nj * 8 + 2 * w.tq + p;
-        xnj_item[nj][p] = a.xn[min(j, a.nall - 1)];
+        xnj_item[nj][p] = a.sink.mode == 1 ? a.sink.xnj[min(j, a.sink.nj - 1)] : a.xn[min(j, a.nall - 1)];
       }
     if (is_producer) {
       mbar_wait(&jempty_bar, (jn & 1) ^ 1);      // previous j-tile released by all 8 warps
       mbar_expect_tx(&jfull_bar, 4 * unit_bytes);
-      bulk_g2s(sJ, a.X + (size_t)(4 * J) * unit_doubles, 4 * unit_bytes, &jfull_bar);
+      bulk_g2s(sJ, (a.sink.mode == 1 ? a.sink.Xj : a.X) + (size_t)(4 * J) * unit_doubles, 4 * unit_bytes, &jfull_bar);
     }
     __syncwarp();
     mbar_wait(&jfull_bar, jn & 1);
@@ -339,7 +353,7 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
   for (int y = 0; y < 2; ++y)
 #pragma unroll
     for (int p = 0; p < 2; ++p) { mA.xnj[y][p] = 0.0; mB.xnj[y][p] = 0.0; }
-  const bool all_cand = a.rmat != nullptr;
+  const bool all_cand = a.rmat != nullptr || a.sink.mode != 0;
   const float e2_up = a.g.E2_up;
 
   // one pipeline step: multiply unit (cur) while screening the previous one (prev), then finish prev
@@ -461,6 +475,7 @@ int launch_pair_cols(const PairArgs& pa, const void* d_items, int item_begin, in
   const int nitems = pa.work_count ? (1 << 30) : item_end - item_begin;
   if (nitems <= 0) return 0;
   ColArgs a{};
+  a.sink = pa.sink;
   a.X = pa.X; a.xn = pa.xn; a.er = pa.er; a.rot = pa.rot; a.aniso = pa.aniso;
   a.items = static_cast<const ColItem*>(d_items);
   a.item_begin = item_begin; a.item_end = item_end;

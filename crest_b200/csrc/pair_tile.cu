@@ -117,8 +117,8 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
 #pragma unroll
     for (int p = 0; p < kJPanels; ++p)
       bulk_g2s(dst + chunk * (1 + p),
-               a.X + ((size_t)(p_J * kJPanels + p) * L.nslab + p_slab) * chunk, chunk_bytes,
-               &full_bar[st]);
+               (a.sink.mode == 1 ? a.sink.Xj : a.X) + ((size_t)(p_J * kJPanels + p) * L.nslab + p_slab) * chunk,
+               chunk_bytes, &full_bar[st]);
     ++p_it;
     if (++p_slab == L.nslab) { p_slab = 0; p_tile += gridDim.x; }
   };
@@ -150,7 +150,8 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
     const int i0 = I * kTileI + wi * 16;       // first i of this warp
     const int j0 = J * kTileJ + wj * 16;       // first j of this warp
     // warp-level activity: any pair with j < i, i < nall
-    const bool active = (j0 < i0 + 16) && (i0 < a.nall) && (j0 < a.nall);
+    const bool active = a.sink.mode == 1 ? (i0 < a.nall) && (j0 < a.sink.nj)
+                                         : (j0 < i0 + 16) && (i0 < a.nall) && (j0 < a.nall);
 
     double acc[2][2][9][2];
 #pragma unroll
@@ -205,6 +206,22 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
     }
     if (!active || a.g.debug == 1) continue;
     if (prof) tc = clock64();
+    if (a.sink.mode) {
+      // rmsd() callers beside cregen_CRE (blockpair.cu): every valid pair to the sink
+#pragma unroll 1
+      for (int q = 0; q < 8; ++q) {
+        const int mi = q >> 2, nj = (q >> 1) & 1, p = q & 1;
+        const int i = i0 + mi * 8 + c, j = j0 + nj * 8 + 2 * tq + p;
+        const bool ok = i < a.nall && (a.sink.mode == 1 ? j < a.sink.nj : j < i);
+        if (!ok) continue;
+        const double xni = a.xn[i];
+        const double xnjv = a.sink.mode == 1 ? a.sink.xnj[j] : a.xn[j];
+        sink_pair(a.sink, i, j, acc[mi][nj][0][p], acc[mi][nj][1][p], acc[mi][nj][2][p], acc[mi][nj][3][p],
+                  acc[mi][nj][4][p], acc[mi][nj][5][p], acc[mi][nj][6][p], acc[mi][nj][7][p], acc[mi][nj][8][p],
+                  xni + xnjv);
+      }
+      continue;
+    }
 
     // ------------------------------ fused epilogue ------------------------------
     // Pass 1 (branch-free, 8 independent pairs per lane): quartic invariants of each 3x3 R and
@@ -222,7 +239,7 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
 #pragma unroll
       for (int p = 0; p < 2; ++p) {
         const int j = j0 + nj * 8 + 2 * tq + p;
-        xnj[nj][p] = (j < a.nall) ? a.xn[j] : 0.0;
+        xnj[nj][p] = a.sink.mode == 1 ? ((j < a.sink.nj) ? a.sink.xnj[j] : 0.0) : ((j < a.nall) ? a.xn[j] : 0.0);
         lam_j[nj][p] = 0.5f * __fsub_rd(f64_to_f32_trunc(xnj[nj][p]) * 0.999998f, e2_up);
       }
     unsigned cand = 0;

@@ -155,6 +155,14 @@ static __device__ __noinline__ double pair_e_exact(double r0, double r1, double 
   return pair_e(r, s, enantio, 0);
 }
 
+// Sink of the rmsd() callers beside cregen_CRE (common.cuh PairSink): r = FP64 covariance of pair (i, j),
+// s = |x_i|^2 + |y_j|^2.  Out of line: it runs for every pair of a compare / intraconf sweep but must not
+// bloat the CREGEN kernels' hot loops.
+struct PairSink;
+static __device__ __noinline__ void sink_pair(const PairSink& k, int i, int j, double r0, double r1, double r2,
+                                              double r3, double r4, double r5, double r6, double r7, double r8,
+                                              double s);
+
 // Branch-free screen: true  =>  PROVEN  e = s - 2*lambda_max > Ecut  (the pair cannot pass the
 // 2*rthr gate), false => undecided, run the exact solve.
 // With lam = (s - Ecut)/2 the claim is lambda_max < lam.  For a real-rooted quartic P (the
@@ -362,4 +370,34 @@ __device__ __forceinline__ bool equalrotaniso_dev(const double* roti, const doub
   return r1 && r2 && r3;
 }
 
+}  // namespace crest
+
+namespace crest {
+static __device__ __noinline__ void sink_pair(const PairSink& k, int i, int j, double r0, double r1, double r2,
+                                              double r3, double r4, double r5, double r6, double r7, double r8,
+                                              double s) {
+  const double r[9] = {r0, r1, r2, r3, r4, r5, r6, r7, r8};
+  const double invA = 1.0 / (double)k.A;
+  if (k.mode == 1) {
+    // compare_ensembles (ensemblecomp.f90:213-248): minimum all-atom RMSD per (conformer, conformer) block
+    const int ci = k.blk_i[i], cj = k.blk_j[j];
+    if (ci < 0 || cj < 0) return;
+    const double val = sqrt(fmax(0.0, pair_e(r, s, 0, 0)) * invA);         // ls_rmsd.f90:163
+    // non-negative doubles order like their bit patterns; the plain read only filters (the slot decreases
+    // monotonically), the atomic decides
+    unsigned long long* slot = k.rmat_bits + ci + (size_t)k.nconf1 * cj;
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(val);
+    if (bits < *reinterpret_cast<volatile unsigned long long*>(slot)) atomicMin(slot, bits);
+  } else {
+    // intraconfRMSD (entropic.f90:1000-1047): rotamers of ONE conformer, j < i
+    const int ci = k.blk_i[i];
+    if (ci < 0 || ci != k.blk_j[j]) return;
+    const double val = sqrt(fmax(0.0, pair_e(r, s, 0, 0)) * invA);
+    if (val < k.rthr) k.has_earlier[i] = 1;                                // entropic.f90:1088 via uniqueCore
+    if (val > k.rthr) {                                                    // entropic.f90:1024-1031
+      const double vm = sqrt(fmax(0.0, pair_e(r, s, 0, 1)) * invA);
+      if (vm < k.rthr_enantio) k.enantio[ci] = 1;
+    }
+  }
+}
 }  // namespace crest
