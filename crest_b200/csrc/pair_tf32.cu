@@ -182,8 +182,7 @@ struct TfArgs {
 template <bool DBG>
 __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v)[9][4], const float* hnp,
                                              int j0, int i, bool iok, f2_t hic2, bool rowfast,
-                                             bool gate, bool slow, int dupi,
-                                             unsigned long long& my_pairs, unsigned& my_cand) {
+                                             bool gate, bool slow, int item_index, unsigned& my_pairs) {
   if (DBG && a.dump) {     // probe of the tensor core's FP32 accumulation (tf32_accum_check_kernel)
     if (iok)
 #pragma unroll
@@ -244,12 +243,14 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
   if (cand) {
     // the reference keeps the LARGEST matching j (cregen.f90:1353-1373): nothing at or below the link
     // this row already has can change it
-    if (!(DBG && a.all_cand) && j0 + 3 < dupi) return;
+    // (rare path: the link and the item counter are touched here, not carried in registers through the
+    // issue-bound loop)
+    if (!(DBG && a.all_cand) && j0 + 3 < a.dup[i]) return;
     const int rel = j0 - a.cm_col0;
     const size_t w = (size_t)(mask_row(i, a.cm_nranks) - a.cm_row0) * (size_t)a.cm_stride + (size_t)(rel >> 5);
     atomicOr(a.cmask + w, cand << (rel & 31));
     if (DBG && a.all_cand && farbits) atomicOr(a.fmask + w, (farbits & cand) << (rel & 31));
-    my_cand += __popc(cand);
+    atomicAdd(a.item_cnt + item_index, (unsigned)__popc(cand));
   }
 }
 
@@ -260,21 +261,22 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
 template <int NST, bool DBG>
 __device__ __forceinline__ void epilogue_groups(const TfArgs& a, const TfItem& item, int i, bool iok, int sq, int lane,
                                                 uint32_t lane_base, uint32_t dfull0, uint32_t dempty0,
-                                                uint32_t& t, uint32_t& ph, unsigned long long& my_pairs,
-                                                int item_index) {
+                                                uint32_t& t, uint32_t& ph, int item_index) {
   const float hic = __fadd_rd(a.hn[i], a.cE);
-  const int dupi = iok ? a.dup[i] : 0;
-  unsigned my_cand = 0;
+  unsigned my_pairs = 0;                                  // <= 4 * 256 per item and lane
   const f2_t hic2 = f2_pack(hic, hic);
   const bool rowfast = iok && hic > 0.0f;
-  const float* hnp = a.hn + item.g_begin * 16 + sq * 4;
   const int g_diag = item.I * 8;                          // first group with g*16 + 15 >= I*128
-  if (!DBG && rowfast)                                    // the fast path's pairs: 4 per lane and group
-    my_pairs += 4ull * (unsigned)max(0, min(item.g_end, g_diag) - max(item.g_begin, item.g_gate_end));
-  int j0 = item.g_begin * 16 + sq * 4;
-  for (int g = item.g_begin; g < item.g_end; ++g, hnp += 16, j0 += 16) {
-    const bool gate = g < item.g_gate_end;
-    const bool slow = gate || (g >= g_diag);
+  // the loop runs on ONE induction variable, j0 (first j of this warp's four pairs): the group's norms sit
+  // at hn + j0, and a group is "slow" (per-pair gate and/or diagonal) unless j0 lies in [f0, f0 + flen)
+  const int fast_b = max(item.g_begin, item.g_gate_end), fast_e = max(fast_b, min(item.g_end, g_diag));
+  if (!DBG && rowfast) my_pairs += 4u * (unsigned)(fast_e - fast_b);   // the fast path's pairs: 4 per lane and group
+  const int f0 = fast_b * 16 + sq * 4;
+  const unsigned flen = (unsigned)(fast_e - fast_b) * 16u;
+  const int j_end = item.g_end * 16 + sq * 4;
+  for (int j0 = item.g_begin * 16 + sq * 4; j0 < j_end; j0 += 16) {
+    const bool slow = (unsigned)(j0 - f0) >= flen;
+    const bool gate = j0 < f0;                             // below the fast range: pairs may fail the energy gate
     uint32_t v[9][4];
     mbar_wait_a(dfull0 + 8u * t, ph);
     tc_fence_after();
@@ -283,14 +285,13 @@ __device__ __forceinline__ void epilogue_groups(const TfArgs& a, const TfItem& i
     tc_fence_before();
     __syncwarp();
     if (elect_one()) mbar_arrive_a(dempty0 + 8u * t);    // this warp's 4 pairs are in registers
-    screen_batch<DBG>(a, v, hnp, j0, i, iok, hic2, rowfast, gate, slow, dupi, my_pairs, my_cand);
+    screen_batch<DBG>(a, v, a.hn + j0, j0, i, iok, hic2, rowfast, gate, slow, item_index, my_pairs);
     if (NST == 2) { ph ^= t; t ^= 1u; }
     else if (++t == (uint32_t)NST) { t = 0; ph ^= 1u; }
   }
-  if (__any_sync(0xffffffffu, my_cand != 0)) {
-    const unsigned c = __reduce_add_sync(0xffffffffu, my_cand);
-    if (lane == 0) atomicAdd(a.item_cnt + item_index, c);
-  }
+  // one counter update per warp and item: nothing of it stays live across items
+  my_pairs = __reduce_add_sync(0xffffffffu, my_pairs);
+  if (lane == 0 && my_pairs) atomicAdd(a.npairs, (unsigned long long)my_pairs);
 }
 
 template <int KSTEPS, bool DBG>
@@ -411,7 +412,6 @@ pair_tf32_kernel(const TfArgs a) {
     uint32_t t = 0, ph = 0, pht = 0;
     uint32_t dfull0 = smem_u32(&d_full[0]), dempty0 = smem_u32(&d_empty[0]);
     asm volatile("" : "+r"(dfull0), "+r"(dempty0));
-    unsigned long long my_pairs = 0;
     const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + kDBase + (uint32_t)(sq * 12);
     for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
       const TfItem item = a.items[k];
@@ -439,11 +439,8 @@ pair_tf32_kernel(const TfArgs a) {
         __syncwarp();
         if (lane == 0) { mbar_arrive(&at_full); mbar_arrive(&a_empty); }
       }
-      epilogue_groups<kTfDStages, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, my_pairs, k);
+      epilogue_groups<kTfDStages, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, k);
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) my_pairs += __shfl_xor_sync(0xffffffffu, my_pairs, o);
-    if (lane == 0 && my_pairs) atomicAdd(a.npairs, my_pairs);
   }
   tc_fence_before();
   __syncthreads();
@@ -586,17 +583,13 @@ pair_tf32_slab_kernel(const TfArgs a) {
     uint32_t t = 0, ph = 0;
     uint32_t dfull0 = smem_u32(&d_full[0]), dempty0 = smem_u32(&d_empty[0]);
     asm volatile("" : "+r"(dfull0), "+r"(dempty0));
-    unsigned long long my_pairs = 0;
     const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(sq * 12);
     for (int k = a.item_begin + blockIdx.x; k < a.item_end; k += gridDim.x) {
       const TfItem item = a.items[k];
       const int i = item.I * 128 + q * 32 + lane;
       const bool iok = i < a.nall;
-      epilogue_groups<kSlabBlock, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, my_pairs, k);
+      epilogue_groups<kSlabBlock, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, k);
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) my_pairs += __shfl_xor_sync(0xffffffffu, my_pairs, o);
-    if (lane == 0 && my_pairs) atomicAdd(a.npairs, my_pairs);
   }
   tc_fence_before();
   __syncthreads();
