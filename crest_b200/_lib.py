@@ -36,6 +36,9 @@ SYMBOLS = {
     "crest_cuda_cregen_dup": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp, c_ip, C.c_int, C.c_int,
                                         _THR, c_dp, c_dp, c_ip, c_llp]),
     "crest_cuda_cregen_group": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp, c_dp, _THR, c_ip, c_dp]),
+    "crest_cuda_cregen_group_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, _THR, C.c_void_p,
+                                                  C.c_void_p]),
+    "crest_cuda_noalloc_max_kept": (C.c_int, []),
     "crest_cuda_cregen_cre": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp, c_ip, C.c_int, C.c_int,
                                         C.c_int, _THR, c_dp, c_ip, c_ip, c_ip, c_llp]),
     "crest_cuda_rmsd_pairs": (C.c_int, [C.c_int, C.c_int, c_dp, C.c_longlong, c_ip, c_ip, c_dp, c_dp]),

@@ -6,6 +6,7 @@
 #include <vector>
 #include "common.cuh"
 #include "qcp.cuh"
+#include "../../include/crest_cuda.h"
 
 namespace crest {
 
@@ -442,3 +443,71 @@ int launch_permute(int nat, int nall, const int* d_src, const double* d_xyz_in, 
 }
 
 }  // namespace crest
+
+// ---- K6 without any allocation (crest_cuda_cregen_group_noalloc, include/crest_cuda.h) --------------------
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+// No counterpart in the reference.  Inputs and the output are
+// device arrays of the caller; the scratch of group_kernel (head flag + rotaniso per structure) lives in ONE
+// file-scope device array that every GPU loading the library holds until exit.  Every call shares it and it
+// keeps the last call's contents: calls that overlap on the GPU race.
+namespace crest {
+
+constexpr int kNoAllocMaxKept = 32768;                                        // 8 + 1 bytes each = 288 KB
+static __device__ __align__(256) unsigned char g_group_scratch[(size_t)kNoAllocMaxKept * 9];
+
+namespace {
+// In host code `g_group_scratch` is a host-side stand-in, not a device address: the address the kernel may use
+// comes from cudaGetSymbolAddress, once per device, with that device current.
+unsigned char* group_scratch_devptr() {
+  static unsigned char* ptr[64] = {};
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    set_error("cudaGetDevice failed or device index %d not in 0..63", dev);
+    return nullptr;
+  }
+  if (!ptr[dev]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_group_scratch);
+    if (e != cudaSuccess || !p) {
+      set_error("cudaGetSymbolAddress(g_group_scratch) failed on device %d: %s", dev, cudaGetErrorString(e));
+      return nullptr;
+    }
+    ptr[dev] = static_cast<unsigned char*>(p);
+  }
+  return ptr[dev];
+}
+}  // namespace
+
+}  // namespace crest
+
+extern "C" {
+
+int crest_cuda_noalloc_max_kept(void) { return crest::kNoAllocMaxKept; }
+
+int crest_cuda_cregen_group_noalloc(int nkept, const double* d_er, const double* d_rot, const double* d_enuc,
+                                    const crest_cuda_thresholds* thr, int* d_group, void* stream) {
+  using namespace crest;
+  if (nkept < 0 || !thr || !d_group || (nkept && (!d_er || !d_rot || !d_enuc))) {
+    set_error("bad argument");
+    return 1;
+  }
+  if (nkept > kNoAllocMaxKept) {
+    set_error("crest_cuda_cregen_group_noalloc: nkept = %d exceeds the static scratch (%d structures); "
+              "use crest_cuda_cregen_group", nkept, kNoAllocMaxKept);
+    return 1;
+  }
+  unsigned char* s = group_scratch_devptr();
+  if (!s) return 1;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  double* aniso = reinterpret_cast<double*>(s);                       // [0, 8 * max): rotaniso per structure
+  unsigned char* head = s + (size_t)kNoAllocMaxKept * 8;              // [8 * max, 9 * max): "is a group head"
+  // the kernel writes aniso[k] and head[i] before it reads them; the clear only keeps a stale flag of the
+  // previous call from ever being looked at
+  CREST_CUDA_TRY(cudaMemsetAsync(head, 0, (size_t)(nkept > 0 ? nkept : 1), st));
+  group_kernel<<<1, 1024, 0, st>>>(nkept, d_er, d_rot, d_enuc, thr->ethr, thr->bthr, thr->bthrmax,
+                                   thr->bthrshift, d_group, head, aniso);
+  CREST_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -80,6 +80,20 @@ int crest_cuda_cregen_group(int nat, int nkept, const int* at, const double* xyz
                             const double* er, const double* rot,
                             const crest_cuda_thresholds* thr, int* group, double* enuc);
 
+/* K6 (group ids only) for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it.  NO counterpart in the reference.
+ * Allocates nothing (no cudaMalloc / cudaFree / pool, no host allocation): inputs and the output
+ * are DEVICE arrays of the caller on the current device - er(nkept) ascending, rot(3,nkept), enuc(nkept)
+ * (K5's result, e.g. from crest_cuda_cregen_group), group(0:nkept) - and the launch is asynchronous on
+ * `stream` (the caller synchronises).  The kernel's scratch (head flag + rotaniso per structure) is ONE
+ * file-scope device array of 9 bytes x crest_cuda_noalloc_max_kept() = 32768 structures (288 KB, held by
+ * every GPU that loads the library until exit); nkept beyond that is rejected with an error.  Every call
+ * shares that array: calls that overlap on the GPU (two streams, two host threads) race - serialise them.
+ * Same decisions as crest_cuda_cregen_group (the single-CTA greedy sweep of cregen.f90:1437-1469). */
+int crest_cuda_cregen_group_noalloc(int nkept, const double* d_er, const double* d_rot, const double* d_enuc,
+                                    const crest_cuda_thresholds* thr, int* d_group, void* stream);
+int crest_cuda_noalloc_max_kept(void);
+
 /* Whole cregen_CRE (cregen.f90:1195-1474) in one call, incl. the kept-first partition
  * (cregen.f90:1397-1419).  xyz is rotated AND permuted in place, er permuted in place.
  *   order(nall)  out: new 1-based position of input structure i (orderref); comments are permuted
