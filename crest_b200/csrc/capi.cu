@@ -64,6 +64,7 @@ static void parse_tune(const char* e, Tune& t) {
   if (std::strstr(e, "forcedense")) t.force_dense = 1;
   if (std::strstr(e, "nodense")) t.no_dense = 1;
   if (std::strstr(e, "nostage")) t.no_stage = 1;
+  if (std::strstr(e, "evenblocks")) t.even_blocks = 1;
   if (const char* q = std::strstr(e, "blocks=")) if (std::sscanf(q + 7, "%d", &v) == 1) t.blocks = v;
   if (const char* q = std::strstr(e, "densebudget=")) if (std::sscanf(q + 12, "%d", &v) == 1) t.dense_budget = v;
   if (const char* q = std::strstr(e, "maskmb=")) if (std::sscanf(q + 7, "%d", &v) == 1) t.mask_mb = v;

@@ -157,20 +157,53 @@ struct Phase {   // CREST_CUDA_TIMING=1: phase wall times on stderr (developer a
   }
 };
 
-// Row blocks of the upload pipeline: whole 128-row tiles, about 36 MB of geometry each, 2-8 blocks; one
-// block when the FP64-only kernels run (their work lists are not staged) or the ensemble is small.
-// Measured on C3 (144 MB, pageable, profiles/r02_timeline_c3.txt): 1 block 16.1 ms, 4 blocks 14.6 ms,
-// 6 blocks 14.9, 8 blocks 15.3 - the pair work available after a fraction f of the rows is f^2, so the
-// GPU starves until ~1/4 of the upload whatever the cut, and every extra stage costs ~0.1 ms of tails.
+// Row blocks of the upload pipeline (whole 128-row tiles); one block when the FP64-only kernels run (their
+// work lists are not staged) or the ensemble is small.  The ensemble is energy sorted and pair (i, j) needs
+// rows i and j < i only: after a fraction f of the rows is on the device, f^2 of the pair work can run.
+// With rho = (pair time per GPU) / (upload time) the GPU that started on a first block f1 stays busy if the
+// next boundary is at most f + rho f^2 (the work of the rows so far lasts until the next block has landed).
+//   compute bound (rho >= 1.5; C3 on 1-2 GPUs): a SMALL first block and boundaries growing by that rule -
+//     C3 on one GPU: 0.10, 0.14, 0.20, 0.32, 0.62, 1 - so the GPU starts ~0.7 ms after the call instead of
+//     after a third of the upload (measured, profiles/r02_b_timeline_n1.txt: 3 equal blocks, first pair
+//     kernel 1.9 ms into a 14.8 ms call whose kernels take 12.4 ms);
+//   upload bound (rho < 1.5; many GPUs, large molecules): equal blocks of ~36 MB x (GPUs / 2), 2-8 of them;
+//     every stage costs ~0.1 ms of tails and, on 8 GPUs, 56 peer copies (profiles/r02_b_timeline_n8.txt).
+// The time estimates only shape the schedule; results do not depend on it.
 std::vector<int> plan_blocks(const crest_cuda_ctx* c, bool staged, int ngpu) {
   std::vector<int> b{0, c->ntile};
   const size_t bytes = (size_t)24 * c->nat * c->nall;
-  int nb = 1;
-  // per GPU the pair work shrinks with the GPU count while the upload (host memcpy bound) does not:
-  // fewer, larger blocks then
-  if (staged && bytes >= ((size_t)24 << 20))
-    nb = (int)std::min<size_t>(8, std::max<size_t>(2, bytes / (((size_t)36 << 20) * (size_t)std::max(1, ngpu / 2))));
-  if (tune().blocks > 0) nb = tune().blocks;
+  if (tune().blocks > 0) {
+    const int nb = std::min(tune().blocks, c->ntile);
+    if (nb <= 1) return b;
+    b.clear();
+    for (int k = 0; k <= nb; ++k) b.push_back((int)((long long)c->ntile * k / nb));
+    return b;
+  }
+  if (!staged || bytes < ((size_t)24 << 20)) return b;
+  // rough rates: staged upload ~40 GB/s (PCIe 5 x16 with the staging threads keeping up), screen kernel
+  // ~4.2e11 pairs/s per GPU up to 88 atoms, ~300 TFLOP/s of 18 A flop per pair on the slab kernel above
+  const double t_up = (double)bytes / 40e9;
+  const double pairs = 0.5 * (double)c->nall * c->nall;
+  const double t_pair = (c->use_col ? pairs / 4.2e11 : pairs * 18.0 * c->nsel / 3.0e14) / std::max(1, ngpu);
+  const double rho = t_pair / t_up;
+  if (rho >= 1.5 && !tune().even_blocks) {
+    std::vector<double> f;
+    for (double f1 = 0.10; f1 < 0.5; f1 += 0.05) {          // a larger first block if 8 stages do not reach the end
+      f.assign(1, f1);
+      while (f.back() < 1.0 && f.size() < 9) f.push_back(f.back() + std::max(0.9 * rho * f.back() * f.back(), 0.04));
+      if (f.back() >= 1.0) break;
+    }
+    if (f.back() >= 1.0 && f.size() >= 2) {
+      b.assign(1, 0);
+      for (size_t k = 0; k + 1 < f.size(); ++k) {
+        const int t = (int)(f[k] * c->ntile + 0.5);
+        if (t > b.back() && t < c->ntile) b.push_back(t);
+      }
+      b.push_back(c->ntile);
+      return b;
+    }
+  }
+  int nb = (int)std::min<size_t>(8, std::max<size_t>(2, bytes / (((size_t)36 << 20) * (size_t)std::max(1, ngpu / 2))));
   if (nb > c->ntile) nb = c->ntile;
   if (nb <= 1) return b;
   b.clear();
@@ -510,12 +543,15 @@ int crest_cuda_cregen_cre(int nat, int nall, const int* at, double* xyz, double*
   int gather_threads = 0;
   std::vector<std::thread> gth;
   if (stage) {
-    gather_threads = std::max(1, std::min(8, (int)std::thread::hardware_concurrency() - 1));
+    // non-temporal stores, 12-16 threads: 1.9 ms for the 144 MB of C3 against 4.2 ms with 8 memcpy threads
+    // (profiles/r02_hostcopy_microbench.txt)
+    gather_threads = std::max(1, std::min(16, (int)std::thread::hardware_concurrency() - 1));
     for (int t = 0; t < gather_threads; ++t)
       gth.emplace_back([&, t] {
         const size_t p0 = n * t / gather_threads, p1 = n * (t + 1) / gather_threads;
         for (size_t p = p0; p < p1; ++p)
-          std::memcpy(xyz + rec * p, stage + rec * (size_t)src[p], rec * sizeof(double));
+          fast_copy(xyz + rec * p, stage + rec * (size_t)src[p], rec * sizeof(double));
+        fast_copy_fence();
       });
   }
   int rc = launch_group(nout, c->d_er2, c->d_rot2, c->d_enuc, thr->ethr, thr->bthr, thr->bthrmax, thr->bthrshift,

@@ -29,7 +29,12 @@ struct BlockGate {
   bool wait(int block);
 };
 
-// dir 0: host -> device, 1: device -> host.  nthreads < 0: default (4 per device, <= 16).  Blocking.
+// memcpy with non-temporal stores (AVX2; plain memcpy below 512 bytes or without AVX2).  Weakly ordered:
+// fast_copy_fence() before another agent (DMA engine, another thread) reads the destination.
+void fast_copy(void* dst, const void* src, size_t n);
+void fast_copy_fence();
+
+// dir 0: host -> device, 1: device -> host.  nthreads < 0: default (hardware threads - 2, <= 16).  Blocking.
 // Returns 0 ok, 1 error (text set).  Leaves an arbitrary current device.
 int staged_copy(const std::vector<CopySeg>& segs, int dir, int nthreads, int nblocks, BlockGate* gate);
 // one segment on `device`; restores the current device
