@@ -267,16 +267,29 @@ int stage_a(Engine& E, int nat, int nall, const int* at, const double* xyz, cons
       if (o1 > o0) segs.push_back({E.c[d]->device, (char*)E.c[d]->d_xyz + o0, (char*)const_cast<double*>(xyz) + o0, o1 - o0, k});
     }
   }
+  // The upload starts NOW, beside the per-GPU set-up below: d_xyz is reserved, every stream of the engine was
+  // idle when the previous call returned, and nothing of the set-up touches d_xyz.
+  BlockGate gate;
+  gate.reset(nb, 1 << 30);                                   // armed before the copier starts
+  int copy_rc = 0;
+  const int T = copy_threads();
+  std::thread copier([&] { copy_rc = staged_copy(segs, 0, T, nb, &gate); });
   if (run_parallel([&](int d) -> int {
         crest_cuda_ctx* c = E.c[d];
         CREST_CUDA_TRY(cudaSetDevice(c->device));
-        CREST_CUDA_TRY(cudaDeviceSynchronize());             // the staging streams do not order against earlier work
+        // ctx_upload's small copies and memsets ran on the legacy default stream, which the engine's
+        // non-blocking streams do not order against (a pageable cudaMemcpy returns before its DMA has landed)
+        CREST_CUDA_TRY(cudaStreamSynchronize(cudaStreamLegacy));
         c->dup_target = c0->d_dup;
         if (begin_call(c, c->stream)) return 1;
         if (staged && plan_stages(c, thr->ethr, n, d, tb, c->stream)) return 1;
         if (d == 0) CREST_CUDA_TRY(cudaEventRecord(E.ev_zero, c->stream));
         return 0;
-      })) return 1;
+      })) {
+    copier.join();
+    for (int d = 0; d < n; ++d) { cudaSetDevice(E.c[d]->device); cudaDeviceSynchronize(); }
+    return 1;
+  }
   const double t_plan = hms();
   std::vector<cudaEvent_t> tev;
   std::vector<double> t_gate((size_t)nb, 0.0), t_enq((size_t)nb, 0.0);
@@ -286,11 +299,6 @@ int stage_a(Engine& E, int nat, int nall, const int* at, const double* xyz, cons
     for (auto& e : tev) cudaEventCreate(&e);
     cudaEventRecord(tev[0], c0->stream);
   }
-  BlockGate gate;
-  gate.reset(nb, 1 << 30);                                   // armed before the copier starts
-  int copy_rc = 0;
-  const int T = copy_threads();
-  std::thread copier([&] { copy_rc = staged_copy(segs, 0, T, nb, &gate); });
   // phase 2 (per GPU): as block k lands, pull the other GPUs' shares, pack, run this GPU's rows of it
   const int rc = run_parallel([&](int d) -> int {
     crest_cuda_ctx* c = E.c[d];
