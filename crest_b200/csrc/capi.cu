@@ -65,9 +65,13 @@ static void parse_tune(const char* e, Tune& t) {
   if (std::strstr(e, "nodense")) t.no_dense = 1;
   if (std::strstr(e, "nostage")) t.no_stage = 1;
   if (std::strstr(e, "evenblocks")) t.even_blocks = 1;
+  if (const char* q = std::strstr(e, "blockf1=")) if (std::sscanf(q + 8, "%d", &v) == 1) t.block_f1 = v;
+  if (const char* q = std::strstr(e, "blockgain=")) if (std::sscanf(q + 10, "%d", &v) == 1) t.block_gain = v;
+  if (std::strstr(e, "packold")) t.pack_old = 1;
   if (const char* q = std::strstr(e, "blocks=")) if (std::sscanf(q + 7, "%d", &v) == 1) t.blocks = v;
   if (const char* q = std::strstr(e, "densebudget=")) if (std::sscanf(q + 12, "%d", &v) == 1) t.dense_budget = v;
   if (const char* q = std::strstr(e, "maskmb=")) if (std::sscanf(q + 7, "%d", &v) == 1) t.mask_mb = v;
+  if (const char* q = std::strstr(e, "scanocc=")) if (std::sscanf(q + 8, "%d", &v) == 1) t.scan_occ = v;
   if (const char* q = std::strstr(e, "packg=")) if (std::sscanf(q + 6, "%d", &v) == 1) t.pack_g = v;
   if (const char* q = std::strstr(e, "copythr=")) if (std::sscanf(q + 8, "%d", &v) == 1) t.copy_threads = v;
   if (const char* q = std::strstr(e, "groupcap=")) if (std::sscanf(q + 9, "%d", &v) == 1) t.group_cap = v;
@@ -235,7 +239,11 @@ int tf_items_host(int n, const double* er, double ethr, std::vector<int>& items,
   // >= 16 items per CTA and rank: the CTAs of a rank take its items round-robin, so the stage lasts
   // ceil(items / 148) items (measured on C3: 128-group items cost nothing against 256, 64 cost 1.3 %)
   // `total` already is this rank's share when a rank is given
-  long long chunk = tune().chunk > 0 ? tune().chunk : total / (148LL * 16 * (rank < 0 ? nr : 1));
+  const long long per_cta = 148LL * (rank < 0 ? nr : 1);
+  long long chunk = tune().chunk > 0 ? tune().chunk : total / (per_cta * 16);
+  // small lists (the first row blocks of the upload pipeline, C2): an item re-loads its 96 KB i-tile, so
+  // items below 64 groups trade balance for operand traffic - 4 items per CTA are enough there
+  if (tune().chunk <= 0 && chunk < 64) chunk = std::min(64LL, std::max(chunk, total / (per_cta * 4)));
   chunk = chunk / 8 * 8;       // segments are whole 128-column blocks of the candidate bitmask
   if (chunk < 8) chunk = 8;
   if (chunk > 256) chunk = 256;

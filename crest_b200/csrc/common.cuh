@@ -33,7 +33,7 @@ struct PackLayout {
 
 // Developer knobs (env CREST_CUDA_TUNE="slab=<8-atom blocks per slab>,stages=<n>,dist=<n>,skew=<clk>"),
 // read once; 0 = automatic.  Used to A/B the pipeline shape on the GPU box without rebuilding.
-struct Tune { int blocks = 0, even_blocks = 0, no_stage = 0, force_dense = 0, no_dense = 0, mask_mb = 0, dense_budget = 0, slab_blocks = 0, stages = 0, dist = 0, skew = -1, force_tile = 0, no_half = 0, no_tf32 = 0, cand_cap = 0, chunk = 0, seq_group = 0, group_cap = 0, copy_threads = -1, pack_g = 0; };
+struct Tune { int blocks = 0, even_blocks = 0, block_f1 = 0, block_gain = 0, no_stage = 0, force_dense = 0, no_dense = 0, mask_mb = 0, dense_budget = 0, slab_blocks = 0, stages = 0, dist = 0, skew = -1, force_tile = 0, no_half = 0, no_tf32 = 0, cand_cap = 0, chunk = 0, seq_group = 0, group_cap = 0, copy_threads = -1, pack_g = 0, pack_old = 0, scan_occ = 0; };
 const Tune& tune();
 void set_tune(const char* spec);   // re-parse the knobs (tests A/B kernel variants in one process)
 

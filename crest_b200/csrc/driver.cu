@@ -162,10 +162,11 @@ struct Phase {   // CREST_CUDA_TIMING=1: phase wall times on stderr (developer a
 // rows i and j < i only: after a fraction f of the rows is on the device, f^2 of the pair work can run.
 // With rho = (pair time per GPU) / (upload time) the GPU that started on a first block f1 stays busy if the
 // next boundary is at most f + rho f^2 (the work of the rows so far lasts until the next block has landed).
-//   compute bound (rho >= 1.5; C3 on 1-2 GPUs): a SMALL first block and boundaries growing by that rule -
-//     C3 on one GPU: 0.10, 0.14, 0.20, 0.32, 0.62, 1 - so the GPU starts ~0.7 ms after the call instead of
-//     after a third of the upload (measured, profiles/r02_b_timeline_n1.txt: 3 equal blocks, first pair
-//     kernel 1.9 ms into a 14.8 ms call whose kernels take 12.4 ms);
+//   compute bound (rho >= 1.5; C3 on 1-2 GPUs): a small first block (0.20) and boundaries growing by
+//     f <- f + 2 rho f^2 - C3 on one GPU: 0.20, 0.46, 1.  The rule f + rho f^2 itself (0.10, 0.14, 0.20, 0.31,
+//     0.61, 1) starts the GPU earlier and is 0.1 ms faster on C3, but every stage ends in the tail of its
+//     slowest rows, and on a collapsed ensemble (C3dense: rows that burn their evaluation budget) six stages
+//     cost 4 ms more than three (profiles/r02_d_block_schedule.txt; knobs blockf1=<%>, blockgain=<%>);
 //   upload bound (rho < 1.5; many GPUs, large molecules): equal blocks of ~36 MB x (GPUs / 2), 2-8 of them;
 //     every stage costs ~0.1 ms of tails and, on 8 GPUs, 56 peer copies (profiles/r02_b_timeline_n8.txt).
 // The time estimates only shape the schedule; results do not depend on it.
@@ -188,9 +189,12 @@ std::vector<int> plan_blocks(const crest_cuda_ctx* c, bool staged, int ngpu) {
   const double rho = t_pair / t_up;
   if (rho >= 1.5 && !tune().even_blocks) {
     std::vector<double> f;
-    for (double f1 = 0.10; f1 < 0.5; f1 += 0.05) {          // a larger first block if 8 stages do not reach the end
+    const double f1_0 = tune().block_f1 > 0 ? 0.01 * tune().block_f1 : 0.20;
+    const double gain = tune().block_gain > 0 ? 0.01 * tune().block_gain : 2.0;
+    for (double f1 = f1_0; f1 < 0.5; f1 += 0.05) {          // a larger first block if 8 stages do not reach the end
       f.assign(1, f1);
-      while (f.back() < 1.0 && f.size() < 9) f.push_back(f.back() + std::max(0.9 * rho * f.back() * f.back(), 0.04));
+      while (f.back() < 1.0 && f.size() < 9)
+        f.push_back(f.back() + std::max(gain * rho * f.back() * f.back(), 0.4 * f1_0));
       if (f.back() >= 1.0) break;
     }
     if (f.back() >= 1.0 && f.size() >= 2) {

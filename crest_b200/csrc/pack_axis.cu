@@ -188,6 +188,42 @@ __device__ __forceinline__ void axis0_tensor(int n, Get get, int sl, Sym3& a, do
   a.a33 = group_sum<G>(t6) + 6.0e-10;
 }
 
+// same, with the masses from a table indexed by what get() returns in z (shared memory: the lookup
+// through c_ams diverges over the lanes of a warp)
+template <int G, class Get>
+__device__ __forceinline__ void axis0_tensor_m(int n, Get get, const double* __restrict__ mass, int sl, Sym3& a,
+                                               double cma[3]) {
+  double sw = 0.0, sx = 0.0, sy = 0.0, sz = 0.0;
+  for (int k = sl; k < n; k += G) {
+    int z; double x, y, zc;
+    get(k, z, x, y, zc);
+    const double m = mass[z];
+    sw += m; sx += m * x; sy += m * y; sz += m * zc;
+  }
+  sw = group_sum<G>(sw) + 1.0e-20;
+  sx = group_sum<G>(sx) / sw; sy = group_sum<G>(sy) / sw; sz = group_sum<G>(sz) / sw;
+  cma[0] = sx; cma[1] = sy; cma[2] = sz;
+  double t1 = 0, t2 = 0, t3 = 0, t4 = 0, t5 = 0, t6 = 0;
+  for (int k = sl; k < n; k += G) {
+    int z; double x, y, zc;
+    get(k, z, x, y, zc);
+    const double m = mass[z];
+    x -= sx; y -= sy; zc -= sz;
+    t1 += m * (y * y + zc * zc);
+    t2 -= m * x * y;
+    t3 += m * (zc * zc + x * x);
+    t4 -= m * zc * x;
+    t5 -= m * y * zc;
+    t6 += m * (x * x + y * y);
+  }
+  a.a11 = group_sum<G>(t1) + 1.0e-10;
+  a.a12 = group_sum<G>(t2) + 2.0e-10;
+  a.a22 = group_sum<G>(t3) + 3.0e-10;
+  a.a13 = group_sum<G>(t4) + 4.0e-10;
+  a.a23 = group_sum<G>(t5) + 5.0e-10;
+  a.a33 = group_sum<G>(t6) + 6.0e-10;
+}
+
 // the eigenproblem of one structure: moments -> rot (MHz), eigenvectors.  Called per LANE by the
 // pack kernel (32 different structures per warp) and lane-uniformly by rotconst_kernel.
 __device__ __noinline__ void axis0_solve(const Sym3& a, double rot[3], Mat3& evec) {
@@ -368,6 +404,207 @@ pack_axis_kernel(int nat, int nall, const int* __restrict__ at, const double* __
   }
 }
 
+
+// ---- pack_axis, one pass over the ensemble (round 2) ---------------------------------------------------
+// The kernel above reads every conformer from global memory in seven dependent sweeps; ncu's source page
+// puts 70 % of its stall samples on the FP64 adds that consume those loads (latency, one wave of warps)
+// and 431 MB of DRAM reads on a 144 MB input.  Here a warp stages its NC = 32 / G conformers in shared
+// memory ONCE (coalesced 16-byte loads, all independent), every pass - CMA, inertia tensor, rotation in
+// place, second tensor, centroid, norm - runs out of shared memory with G lanes per conformer, and the two
+// outputs leave as coalesced 16-byte stores: xyz_axis straight from the staged copy, the FP64 operand X
+// row by row in ITS layout (lanes along the atom slots).  The conformer stride in shared memory is odd (in
+// doubles), so the G-lanes-per-conformer passes are bank-conflict free.  All G lanes of a conformer hold
+// its reduced tensor, so every lane runs the 3x3 eigen-solve (no exchange; the solve is ~2 % of the time).
+// Per-conformer arithmetic is the reference's operation order as before (-fmad=false); only the
+// association of the atom sums depends on G.
+template <int G>
+__global__ void __launch_bounds__(64, 8)
+pack_axis_smem_kernel(int nat, int nall, const int* __restrict__ at, const double* __restrict__ xyz,
+                      const int* __restrict__ sel, int nsel, int rot_from_mask, PackLayout L,
+                      double* __restrict__ xyz_axis, double* __restrict__ rot_out,
+                      double* __restrict__ aniso_out, double* __restrict__ X, double* __restrict__ xn_out,
+                      int stride) {
+  constexpr int NC = 32 / G;
+  extern __shared__ double sm[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int g = lane / G, sl = lane % G;
+  const int n3 = 3 * nat;
+  double* const mass = sm;                                   // [nat]            (block)
+  int* const sel_s = reinterpret_cast<int*>(sm + nat);       // [nsel] -> 3 * atom index   (block)
+  double* const cs = sm + nat + (nsel + 1) / 2 + (size_t)wib * ((size_t)NC * stride + 4 * NC);   // [NC][stride]
+  double* const cen = cs + (size_t)NC * stride;              // [NC][4] centroid of the RMSD subset
+  for (int k = threadIdx.x; k < nat; k += blockDim.x) mass[k] = mass_of(at[k]);
+  for (int k = threadIdx.x; k < nsel; k += blockDim.x) sel_s[k] = 3 * sel[k];
+  __syncthreads();
+  const int c0 = (blockIdx.x * nwarp + wib) * NC;
+  if (c0 >= nall) return;
+  const int nc = min(NC, nall - c0);
+  const bool live = g < nc;
+  const double* const mine = cs + (size_t)(live ? g : 0) * stride;   // idle groups recompute conformer c0
+
+  // ---- stage: global -> shared, 16 bytes per lane and step when 3*nat is even
+  {
+    const double* src = xyz + (size_t)n3 * c0;
+    constexpr int NB = NC < 4 ? NC : 4;                       // conformers per batch of independent loads
+    if ((n3 & 1) == 0) {
+      for (int cb = 0; cb < nc; cb += NB)
+        for (int r = 2 * lane; r < n3; r += 64) {
+          double2 v[NB];
+#pragma unroll
+          for (int c = 0; c < NB; ++c)
+            if (cb + c < nc) v[c] = *reinterpret_cast<const double2*>(src + (size_t)(cb + c) * n3 + r);
+#pragma unroll
+          for (int c = 0; c < NB; ++c)
+            if (cb + c < nc) {
+              cs[(size_t)(cb + c) * stride + r] = v[c].x;
+              cs[(size_t)(cb + c) * stride + r + 1] = v[c].y;
+            }
+        }
+    } else {
+      for (int cb = 0; cb < nc; cb += NB)
+        for (int r = lane; r < n3; r += 32) {
+          double v[NB];
+#pragma unroll
+          for (int c = 0; c < NB; ++c)
+            if (cb + c < nc) v[c] = src[(size_t)(cb + c) * n3 + r];
+#pragma unroll
+          for (int c = 0; c < NB; ++c)
+            if (cb + c < nc) cs[(size_t)(cb + c) * stride + r] = v[c];
+        }
+    }
+  }
+  __syncwarp();
+
+  // ---- axis_4: CMA + inertia tensor (all atoms), eigenproblem, right-handed frame
+  Sym3 a;
+  double cma[3];
+  {
+    auto get_all = [&](int k, int& z, double& x, double& y, double& zc) {
+      z = k; x = mine[3 * k]; y = mine[3 * k + 1]; zc = mine[3 * k + 2];
+    };
+    axis0_tensor_m<G>(nat, get_all, mass, sl, a, cma);
+  }
+  double rot[3];
+  Mat3 ev;
+  axis0_solve(a, rot, ev);
+  {
+    const double xsum = ev.m[0][0] * (ev.m[1][1] * ev.m[2][2] - ev.m[2][1] * ev.m[1][2]) +
+                        ev.m[0][1] * (ev.m[1][2] * ev.m[2][0] - ev.m[1][0] * ev.m[2][2]) +
+                        ev.m[0][2] * (ev.m[1][0] * ev.m[2][1] - ev.m[1][1] * ev.m[2][0]);
+    if (xsum < 0.0) { ev.m[0][0] = -ev.m[0][0]; ev.m[1][0] = -ev.m[1][0]; ev.m[2][0] = -ev.m[2][0]; }
+  }
+  // ---- rotate in place (each atom is owned by one lane)
+  if (live) {
+    double* own = cs + (size_t)g * stride;
+    for (int k = sl; k < nat; k += G) {
+      const double x = own[3 * k] - cma[0], y = own[3 * k + 1] - cma[1], z = own[3 * k + 2] - cma[2];
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        double s = 0.0;
+        s = s + x * ev.m[0][j];
+        s = s + y * ev.m[1][j];
+        s = s + z * ev.m[2][j];
+        own[3 * k + j] = s;
+      }
+    }
+  }
+  __syncwarp();
+  // ---- axis_1 on the rotated (sub)structure -> rot. constants
+  {
+    double cma2[3];
+    if (rot_from_mask) {
+      auto get_sub = [&](int k, int& z, double& x, double& y, double& zc) {
+        const int q3 = sel_s[k];
+        z = q3 / 3; x = mine[q3]; y = mine[q3 + 1]; zc = mine[q3 + 2];
+      };
+      axis0_tensor_m<G>(nsel, get_sub, mass, sl, a, cma2);
+    } else {
+      auto get_rot = [&](int k, int& z, double& x, double& y, double& zc) {
+        z = k; x = mine[3 * k]; y = mine[3 * k + 1]; zc = mine[3 * k + 2];
+      };
+      axis0_tensor_m<G>(nat, get_rot, mass, sl, a, cma2);
+    }
+  }
+  axis0_solve(a, rot, ev);
+  if (live && sl == 0) {
+    const int conf = c0 + g;
+    rot_out[3 * conf + 0] = rot[0];
+    rot_out[3 * conf + 1] = rot[1];
+    rot_out[3 * conf + 2] = rot[2];
+    aniso_out[conf] = rotaniso_dev(rot[0], rot[1], rot[2]);
+  }
+  // ---- RMSD subset: unweighted centroid (ls_rmsd.f90:105-119) and centred squared norm
+  {
+    double cx = 0.0, cy = 0.0, cz = 0.0;
+    for (int k = sl; k < nsel; k += G) {
+      const int q3 = sel_s[k];
+      cx += mine[q3]; cy += mine[q3 + 1]; cz += mine[q3 + 2];
+    }
+    const double inv_n = 1.0 / (double)nsel;
+    cx = group_sum<G>(cx) * inv_n; cy = group_sum<G>(cy) * inv_n; cz = group_sum<G>(cz) * inv_n;
+    double nrm = 0.0;
+    for (int k = sl; k < nsel; k += G) {
+      const int q3 = sel_s[k];
+      const double x = mine[q3] - cx, y = mine[q3 + 1] - cy, z = mine[q3 + 2] - cz;
+      nrm += x * x + y * y + z * z;
+    }
+    nrm = group_sum<G>(nrm);
+    if (live && sl == 0) {
+      cen[4 * g] = cx; cen[4 * g + 1] = cy; cen[4 * g + 2] = cz;
+      xn_out[c0 + g] = nrm;
+    }
+  }
+  __syncwarp();
+  // ---- xyz_axis: the staged copy, coalesced
+  {
+    double* dst = xyz_axis + (size_t)n3 * c0;
+    if ((n3 & 1) == 0) {
+      for (int c = 0; c < nc; ++c)
+#pragma unroll 2
+        for (int r = 2 * lane; r < n3; r += 64)
+          *reinterpret_cast<double2*>(dst + (size_t)c * n3 + r) =
+              make_double2(cs[(size_t)c * stride + r], cs[(size_t)c * stride + r + 1]);
+    } else {
+      for (int c = 0; c < nc; ++c)
+        for (int r = lane; r < n3; r += 32) dst[(size_t)c * n3 + r] = cs[(size_t)c * stride + r];
+    }
+  }
+  // ---- packed operand X: chunk [panel][slab][comp][rows][KS]; per (slab, comp, conformer) one row of KU
+  // slots, lanes along the slots (two per lane: KU and KS are even).  Slot k holds selected atom ks:
+  // identity, except in a half tail where the <= 4 atoms of the last block sit at its even slots.
+  {
+    const int kpad = L.nslab * L.KU, last0 = kpad - 8;
+    const int panel = c0 / L.rows, row0 = c0 % L.rows;            // NC divides L.rows: one panel per warp
+    for (int slab = 0; slab < L.nslab; ++slab) {
+      double* chunk = X + ((size_t)panel * L.nslab + slab) * L.chunk_doubles();
+      for (int kk = 2 * lane; kk < L.KU; kk += 64) {
+        int q3[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int k = slab * L.KU + kk + h;
+          int ks = k;
+          if (L.half_tail && k >= last0) ks = ((k - last0) & 1) ? -1 : last0 + ((k - last0) >> 1);
+          q3[h] = (ks >= 0 && ks < nsel) ? sel_s[ks] : -1;
+        }
+#pragma unroll
+        for (int comp = 0; comp < 3; ++comp) {
+#pragma unroll 4
+          for (int c = 0; c < nc; ++c) {
+            {
+              const double* src = cs + (size_t)c * stride;
+              const double ce = cen[4 * c + comp];
+              double2 v;
+              v.x = q3[0] >= 0 ? src[q3[0] + comp] - ce : 0.0;
+              v.y = q3[1] >= 0 ? src[q3[1] + comp] - ce : 0.0;
+              *reinterpret_cast<double2*>(chunk + ((size_t)comp * L.rows + row0 + c) * L.KS + kk) = v;
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(128)
 rotconst_kernel(int nat, int n, const int* __restrict__ at, const double* __restrict__ xyz,
                 double* __restrict__ rot_out) {
@@ -391,14 +628,48 @@ int launch_pack_axis(int nat, int nall, const int* d_at, const double* d_xyz, co
                      double* d_rot, double* d_aniso, double* d_X, double* d_xn,
                      cudaStream_t stream) {
   if (nall <= 0) return 0;
+  int dev = 0, nsm = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+  // One-pass kernel: G lanes per conformer, NC = 32 / G conformers staged per warp.  The passes are chains
+  // of FP64 operations on shared-memory operands: they need ~16 resident warps per SM to keep the pipes busy
+  // (measured with 8: 12 % warps active, issue 27 %, no faster than the multi-sweep kernel), so G = the
+  // smallest power of two whose staged copy stays under 16 KB per warp (C3, 60 atoms: G = 4, 8 conformers =
+  // 11.6 KB; C5, 40 atoms: G = 2; C4, 300 atoms: G = 16, two conformers).
+  // nat > 1200 (one conformer > 29 KB) and CREST_CUDA_TUNE `packold` take the multi-sweep kernel.
+  const int stride = (3 * nat) | 1;                             // doubles per staged conformer, odd
+  int G2 = 2;
+  while (G2 < 32 && (size_t)(32 / G2) * stride * 8 > (size_t)16 << 10) G2 <<= 1;
+  // G depends on the atom count ONLY: the association of the atom sums follows G, and rot / xyz_axis must not
+  // depend on how the upload pipeline cut the ensemble into row blocks (test_engine_upload_pipeline_blocks)
+  if (tune().pack_g < 0 && (tune().pack_g == -2 || tune().pack_g == -4 || tune().pack_g == -8 ||
+                            tune().pack_g == -16 || tune().pack_g == -32)) G2 = -tune().pack_g;   // packg=-<G>: force
+  const bool one_pass = !tune().pack_old && (size_t)(32 / G2) * stride * 8 <= (size_t)29 << 10;
+  if (one_pass) {
+    const int NC = 32 / G2, wpb = 2;
+    const int nwarp = (nall + NC - 1) / NC;
+    const dim3 grid((nwarp + wpb - 1) / wpb), block(wpb * 32);
+    const size_t smem = sizeof(double) * ((size_t)nat + (nsel + 1) / 2 + (size_t)wpb * ((size_t)NC * stride + 4 * NC));
+#define CREST_PACK1_ARGS nat, nall, d_at, d_xyz, d_sel, nsel, rot_from_mask, L, d_xyz_axis, d_rot, d_aniso, d_X, d_xn, stride
+#define CREST_PACK1(GG)                                                                                     \
+    case GG:                                                                                                \
+      CREST_CUDA_TRY(cudaFuncSetAttribute(pack_axis_smem_kernel<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+      pack_axis_smem_kernel<GG><<<grid, block, smem, stream>>>(CREST_PACK1_ARGS);                          \
+      break;
+    switch (G2) {
+      CREST_PACK1(2) CREST_PACK1(4) CREST_PACK1(8) CREST_PACK1(16) CREST_PACK1(32)
+      default: set_error("pack_axis: bad lane group %d", G2); return 1;
+    }
+#undef CREST_PACK1
+#undef CREST_PACK1_ARGS
+    CREST_CUDA_TRY(cudaGetLastError());
+    return 0;
+  }
   // Conformers per warp: 32 when that still gives every SM its 24 resident warps' worth of work
   // (C3: 3125 warps, one wave); otherwise halve down to one round of 32/G conformers so that small
   // ensembles (C4: 20 000 x 300) are not serialised inside a few hundred warps.
   int G = tune().pack_g;
   if (G != 4 && G != 16) G = 8;
-  int dev = 0, nsm = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
   int W = 32;
   while (W > 32 / G && (nall + W - 1) / W < nsm * 16) W >>= 1;
   const int wpb = 2;

@@ -719,7 +719,8 @@ __device__ __forceinline__ unsigned exact_pair8(const ScanArgs& a, int i, int j,
   return res;
 }
 
-__global__ void __launch_bounds__(256)
+template <int kMinBlocks>
+__global__ void __launch_bounds__(256, kMinBlocks)
 cand_scan_kernel(const ScanArgs a) {
   const int lane = threadIdx.x & 31, sub = lane & 7, grp = lane >> 3;
   const unsigned gmask = 0xFFu << (lane & 24);
@@ -752,22 +753,46 @@ cand_scan_kernel(const ScanArgs a) {
     }
     bool gave_up = false, met_dense = false;
     const unsigned char* const dense_i = a.dense ? a.dense + (i >> 7) : nullptr;
-    for (int blk = (jend - 1 - a.col0) >> 12; blk >= 0; --blk) {     // 128 words = 4096 columns
+    // The row's words are read 8 blocks (8 x 512 B per warp) at a time: the loads of a batch are independent,
+    // and nearly every block is empty - read one by one, the dependent DRAM round trips (12 per row on C3,
+    // 3552 resident warps) were most of this kernel's time.
+    constexpr int kScanBatch = 8;
+    for (int btop = (jend - 1 - a.col0) >> 12; btop >= 0; btop -= kScanBatch) {     // block = 128 words = 4096 columns
+      unsigned nonempty = 0u;
+      {
+        unsigned orw[kScanBatch];
+#pragma unroll
+        for (int t = 0; t < kScanBatch; ++t) {
+          orw[t] = 0u;
+          if (btop - t >= 0) {
+            const uint4 v = *(reinterpret_cast<const uint4*>(rowp + (size_t)(btop - t) * 128) + lane);
+            orw[t] = v.x | v.y | v.z | v.w;
+          }
+        }
+#pragma unroll
+        for (int t = 0; t < kScanBatch; ++t)
+          if (__any_sync(0xffffffffu, orw[t] != 0u)) nonempty |= 1u << t;
+      }
+      while (nonempty) {
+      const int tsel = __ffs(nonempty) - 1;                  // highest block of the batch first
+      nonempty &= nonempty - 1u;
+      const int blk = btop - tsel;
       uint4* const wp = reinterpret_cast<uint4*>(rowp + (size_t)blk * 128) + lane;
-      uint4 w = *wp;
+      uint4 w = *wp;                                         // a rare re-read (L2): the batch kept one OR word per block
       const bool nz = (w.x | w.y | w.z | w.w) != 0u;
       unsigned any = __ballot_sync(0xffffffffu, nz);
-      if (!any) continue;
       if (nz) *wp = make_uint4(0u, 0u, 0u, 0u);
       if (done) continue;
       while (any && !done) {
         const int src = 31 - __clz(any);
         any &= ~(1u << src);
-        const unsigned w4[4] = {__shfl_sync(0xffffffffu, w.x, src), __shfl_sync(0xffffffffu, w.y, src),
-                                __shfl_sync(0xffffffffu, w.z, src), __shfl_sync(0xffffffffu, w.w, src)};
-#pragma unroll
+        const unsigned w4x = __shfl_sync(0xffffffffu, w.x, src), w4y = __shfl_sync(0xffffffffu, w.y, src);
+        const unsigned w4z = __shfl_sync(0xffffffffu, w.z, src), w4w = __shfl_sync(0xffffffffu, w.w, src);
+        // ONE copy of the evaluation code: unrolled over the four words the kernel was 129 KB of SASS and a third
+        // of its stall samples were instruction fetches (`no_instruction`, profiles/r02_d_scan_ncu.txt)
+#pragma unroll 1
         for (int q = 3; q >= 0 && !done; --q) {
-          unsigned word = w4[q];
+          unsigned word = q == 3 ? w4w : (q == 2 ? w4z : (q == 1 ? w4y : w4x));
           if (!word) continue;
           const int widx = blk * 128 + src * 4 + q;
           const int cbase = a.col0 + widx * 32;
@@ -807,6 +832,7 @@ cand_scan_kernel(const ScanArgs a) {
           }
         }
       }
+      }   // while (nonempty)
     }
     if (lane == 0 && m > m0) atomicMax_system(a.dup + i, m);
     // a row that skipped candidates inside a dense item needs the FP64 tensor kernel for them even if it
@@ -1162,9 +1188,15 @@ int launch_pair_tf32(const PairArgs& pa, const PairArgs& fb_in, const Tf32Buffer
     e.g = pa.g; e.dup = pa.dup; e.counters = tb.cand_count; e.debug_all = all_cand ? 1 : 0;
     const int rows = (row_hi - row0) / nranks + 128;
     int sgrid = (rows + 7) / 8;
-    if (sgrid > nsm * 8) sgrid = nsm * 8;
+    if (sgrid > nsm * 12) sgrid = nsm * 12;          // whole waves at 2, 3 or 4 resident blocks per SM
     if (sgrid < 1) sgrid = 1;
-    cand_scan_kernel<<<sgrid, 256, 0, stream>>>(e);
+    // resident warps per SM: the scan is a chain of latencies per row (mask words, operand gathers, the quartic
+    // solve), so it is paid in warps - 2 blocks at 128 registers, 3 at 80 (some spills), 4 at 64 (`scanocc=`)
+    switch (tune().scan_occ) {
+      case 2: cand_scan_kernel<2><<<sgrid, 256, 0, stream>>>(e); break;
+      case 4: cand_scan_kernel<4><<<sgrid, 256, 0, stream>>>(e); break;
+      default: cand_scan_kernel<3><<<sgrid, 256, 0, stream>>>(e); break;
+    }
     CREST_CUDA_TRY(cudaGetLastError());
     // unfinished units of dense items on the FP64 tensor kernel (idle CTAs return at once when the list is empty)
     if (!all_cand) {

@@ -258,7 +258,13 @@ def test_staged_pageable_copies(cb):
         cregen.set_tune(tune)
         try:
             d = cb.cregen_dup(env, nat, nall, ens["at"], ens["xyz"], ens["er"], want_xyz=True)
-            x, e = ens["xyz"].copy(), ens["er"].copy()
+            # in/out geometry at an address that is NOT 32-byte aligned: the staging copies and the permuted
+            # gather use non-temporal 32-byte stores with unaligned heads and tails (hostcopy.cu fast_copy)
+            buf = np.empty(ens["xyz"].size + 1)
+            x = buf[1:].reshape(ens["xyz"].shape)
+            assert x.ctypes.data % 32 != 0 or buf.ctypes.data % 32 != 0
+            x[...] = ens["xyz"]
+            e = ens["er"].copy()
             r = cb.cregen_CRE_inplace(env, nat, nall, ens["at"], x, e)
         finally:
             cregen.set_tune(None)
