@@ -182,7 +182,7 @@ struct TfArgs {
 template <bool DBG>
 __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v)[9][4], const float* hnp,
                                              int j0, int i, bool iok, f2_t hic2, bool rowfast,
-                                             bool gate, bool slow, int item_index, unsigned& my_pairs) {
+                                             bool gate, bool slow, uint32_t* slot, unsigned& my_pairs) {
   if (DBG && a.dump) {     // probe of the tensor core's FP32 accumulation (tf32_accum_check_kernel)
     if (iok)
 #pragma unroll
@@ -243,14 +243,16 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
   if (cand) {
     // the reference keeps the LARGEST matching j (cregen.f90:1353-1373): nothing at or below the link
     // this row already has can change it
-    // (rare path: the link and the item counter are touched here, not carried in registers through the
-    // issue-bound loop)
-    if (!(DBG && a.all_cand) && j0 + 3 < a.dup[i]) return;
+    // (the link of the row and the item's candidate count live in this thread's two shared-memory words,
+    // not in registers of the issue-bound loop and not in global memory: with a global load of dup[i] and a
+    // same-address atomicAdd per emitting lane, an ensemble where most groups emit - C3adv - spent 62 of its
+    // 73 ms screen time here)
+    if (!(DBG && a.all_cand) && j0 + 3 < (int)slot[0]) return;
     const int rel = j0 - a.cm_col0;
     const size_t w = (size_t)(mask_row(i, a.cm_nranks) - a.cm_row0) * (size_t)a.cm_stride + (size_t)(rel >> 5);
     atomicOr(a.cmask + w, cand << (rel & 31));
     if (DBG && a.all_cand && farbits) atomicOr(a.fmask + w, (farbits & cand) << (rel & 31));
-    atomicAdd(a.item_cnt + item_index, (unsigned)__popc(cand));
+    slot[kTfEpiWarps * 32] += (unsigned)__popc(cand);
   }
 }
 
@@ -261,7 +263,10 @@ __device__ __forceinline__ void screen_batch(const TfArgs& a, const uint32_t (&v
 template <int NST, bool DBG>
 __device__ __forceinline__ void epilogue_groups(const TfArgs& a, const TfItem& item, int i, bool iok, int sq, int lane,
                                                 uint32_t lane_base, uint32_t dfull0, uint32_t dempty0,
-                                                uint32_t& t, uint32_t& ph, int item_index) {
+                                                uint32_t& t, uint32_t& ph, int item_index, uint32_t* slot) {
+  // slot[0] = the row's current link (links only change between kernels), slot[512] = candidates of this lane
+  slot[0] = iok ? (uint32_t)a.dup[i] : 0u;
+  slot[kTfEpiWarps * 32] = 0u;
   const float hic = __fadd_rd(a.hn[i], a.cE);
   unsigned my_pairs = 0;                                  // <= 4 * 256 per item and lane
   const f2_t hic2 = f2_pack(hic, hic);
@@ -285,13 +290,15 @@ __device__ __forceinline__ void epilogue_groups(const TfArgs& a, const TfItem& i
     tc_fence_before();
     __syncwarp();
     if (elect_one()) mbar_arrive_a(dempty0 + 8u * t);    // this warp's 4 pairs are in registers
-    screen_batch<DBG>(a, v, a.hn + j0, j0, i, iok, hic2, rowfast, gate, slow, item_index, my_pairs);
+    screen_batch<DBG>(a, v, a.hn + j0, j0, i, iok, hic2, rowfast, gate, slow, slot, my_pairs);
     if (NST == 2) { ph ^= t; t ^= 1u; }
     else if (++t == (uint32_t)NST) { t = 0; ph ^= 1u; }
   }
   // one counter update per warp and item: nothing of it stays live across items
   my_pairs = __reduce_add_sync(0xffffffffu, my_pairs);
   if (lane == 0 && my_pairs) atomicAdd(a.npairs, (unsigned long long)my_pairs);
+  const unsigned ncand = __reduce_add_sync(0xffffffffu, slot[kTfEpiWarps * 32]);
+  if (lane == 0 && ncand) atomicAdd(a.item_cnt + item_index, ncand);
 }
 
 template <int KSTEPS, bool DBG>
@@ -305,6 +312,7 @@ pair_tf32_kernel(const TfArgs a) {
   __shared__ __align__(8) uint64_t b_full[kTfBStagesMax], b_empty[kTfBStagesMax];
   __shared__ __align__(8) uint64_t d_full[kTfDStagesMax], d_empty[kTfDStagesMax];
   __shared__ uint32_t tmem_base_smem;
+  __shared__ uint32_t epi_slot[2 * kTfEpiWarps * 32];   // per epilogue thread: row link, candidate count (screen_batch)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int nchunk = 2 * KSTEPS;
@@ -439,7 +447,8 @@ pair_tf32_kernel(const TfArgs a) {
         __syncwarp();
         if (lane == 0) { mbar_arrive(&at_full); mbar_arrive(&a_empty); }
       }
-      epilogue_groups<kTfDStages, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, k);
+      epilogue_groups<kTfDStages, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, k,
+                                       epi_slot + threadIdx.x);
     }
   }
   tc_fence_before();
@@ -478,6 +487,7 @@ pair_tf32_slab_kernel(const TfArgs a) {
   __shared__ __align__(8) uint64_t b_full[kTfBStagesMax], b_empty[kTfBStagesMax];
   __shared__ __align__(8) uint64_t d_full[kSlabBlock], d_empty[kSlabBlock];
   __shared__ uint32_t tmem_base_smem;
+  __shared__ uint32_t epi_slot[2 * kTfEpiWarps * 32];   // per epilogue thread: row link, candidate count (screen_batch)
   constexpr int nchunk = 2 * kSlabKsteps;
   constexpr uint32_t a_comp_bytes = (uint32_t)nchunk * 2048u;
   constexpr uint32_t a_bytes = 3u * a_comp_bytes;            // one slab of the i-tile
@@ -588,7 +598,8 @@ pair_tf32_slab_kernel(const TfArgs a) {
       const TfItem item = a.items[k];
       const int i = item.I * 128 + q * 32 + lane;
       const bool iok = i < a.nall;
-      epilogue_groups<kSlabBlock, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, k);
+      epilogue_groups<kSlabBlock, DBG>(a, item, i, iok, sq, lane_p, lane_base, dfull0, dempty0, t, ph, k,
+                                       epi_slot + threadIdx.x);
     }
   }
   tc_fence_before();
@@ -1192,10 +1203,13 @@ int launch_pair_tf32(const PairArgs& pa, const PairArgs& fb_in, const Tf32Buffer
     if (sgrid < 1) sgrid = 1;
     // resident warps per SM: the scan is a chain of latencies per row (mask words, operand gathers, the quartic
     // solve), so it is paid in warps - 2 blocks at 128 registers, 3 at 80 (some spills), 4 at 64 (`scanocc=`)
-    switch (tune().scan_occ) {
+    // Measured (profiles/r02_d_scan_occupancy.txt): up to 88 atoms 4 blocks win (C3 422 us against 482, C5 500 us
+    // per pass against 620); with K slabs the evaluation loop is long and the spills cost more than the warps
+    // bring (C4ext: 24.6 ms pair stage at 4, 21.9 at 3, 20.2 at 2)
+    switch (tune().scan_occ > 0 ? tune().scan_occ : (col_layout ? 4 : 2)) {
       case 2: cand_scan_kernel<2><<<sgrid, 256, 0, stream>>>(e); break;
-      case 4: cand_scan_kernel<4><<<sgrid, 256, 0, stream>>>(e); break;
-      default: cand_scan_kernel<3><<<sgrid, 256, 0, stream>>>(e); break;
+      case 3: cand_scan_kernel<3><<<sgrid, 256, 0, stream>>>(e); break;
+      default: cand_scan_kernel<4><<<sgrid, 256, 0, stream>>>(e); break;
     }
     CREST_CUDA_TRY(cudaGetLastError());
     // unfinished units of dense items on the FP64 tensor kernel (idle CTAs return at once when the list is empty)
