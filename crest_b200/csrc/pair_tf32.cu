@@ -730,17 +730,64 @@ __device__ __forceinline__ unsigned exact_pair8(const ScanArgs& a, int i, int j,
   return res;
 }
 
+// The same decision for EVERY set bit of one 32-column word at once, one lane per candidate (bit b -> lane b):
+// each lane contracts its own pair serially (the row of i is a broadcast load).  One such step costs about
+// three of the 8-lanes-per-candidate steps above and decides up to 32 candidates instead of 4 - the path of
+// rows that keep missing inside a block of near-identical structures, where the one-warp-per-row scan used to
+// end in a tail of rows with hundreds of sequential steps (C3dense: ~1 ms per launch on any number of GPUs).
+// Returns the ballot of duplicate links.
+__device__ __noinline__ unsigned exact_word32(const ScanArgs& a, int i, int cbase, unsigned livebits, int lane) {
+  const bool live = (livebits >> lane) & 1u;
+  const int j = cbase + lane;
+  bool dupl = false;
+  if (live) {
+    const size_t cs = (size_t)a.xv.rows * a.xv.KS;
+    double r[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int sd = 0; sd < a.xv.nslab; ++sd) {
+      const double* xi = a.xv.row(i, 0, sd);
+      const double* xj = a.xv.row(j, 0, sd);
+#pragma unroll 2
+      for (int k = 0; k < a.xv.KU; ++k) {
+        const double x0 = xi[k], x1 = xi[cs + k], x2 = xi[2 * cs + k];
+        const double y0 = xj[k], y1 = xj[cs + k], y2 = xj[2 * cs + k];
+        r[0] = fma(x0, y0, r[0]); r[1] = fma(x0, y1, r[1]); r[2] = fma(x0, y2, r[2]);
+        r[3] = fma(x1, y0, r[3]); r[4] = fma(x1, y1, r[4]); r[5] = fma(x1, y2, r[5]);
+        r[6] = fma(x2, y0, r[6]); r[7] = fma(x2, y1, r[7]); r[8] = fma(x2, y2, r[8]);
+      }
+    }
+    const double s = a.xn[i] + a.xn[j];
+    const Quartic q = quartic_of(r);
+    const double c1 = a.g.enantio ? -q.c1abs : -8.0 * q.det;
+    if (!screen_far(q, c1, s, fma(1e-8, s, a.g.E2))) {
+      const double e = pair_e_exact(r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], r[8], s, a.g.enantio);
+      if (e < a.g.E2) {
+        dupl = e < a.g.E1;
+        if (!dupl)
+          dupl = equalrotaniso_dev(a.rot + 3 * (size_t)i, a.rot + 3 * (size_t)j, a.aniso[i], a.aniso[j],
+                                   a.g.bthr_half, a.g.bthrmax, a.g.bthrshift);
+      }
+    }
+  }
+  return __ballot_sync(0xffffffffu, dupl);
+}
+
 template <int kMinBlocks>
 __global__ void __launch_bounds__(256, kMinBlocks)
 cand_scan_kernel(const ScanArgs a) {
   const int lane = threadIdx.x & 31, sub = lane & 7, grp = lane >> 3;
   const unsigned gmask = 0xFFu << (lane & 24);
-  const int warps = (gridDim.x * blockDim.x) >> 5;
-  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  // rows are handed out through a queue (counters[10], zeroed per launch), longest first: a row that keeps
+  // missing inside a dense block is hundreds of sequential steps, and with rows dealt round-robin the slowest
+  // SM of a C3dense launch was busy 5.0 M cycles against 2.9 M on average (profiles/r02_h_scan_dense_ncu.txt)
   unsigned n_eval = 0, n_viol = 0;
   // owned rows only, longest first (descending i), round-robin over the warps of the grid
   const long long mtop = mask_row(a.nall - 1, a.nranks) + 128;       // upper bound of the compact row index
-  for (long long mr = mtop - 1 - wid; mr >= a.mrow0; mr -= warps) {
+  for (;;) {
+    unsigned ticket = 0;
+    if (lane == 0) ticket = atomicAdd(a.counters + 10, 1u);
+    ticket = __shfl_sync(0xffffffffu, ticket, 0);
+    const long long mr = mtop - 1 - (long long)ticket;
+    if (mr < a.mrow0) break;
     const int i = (int)(((mr >> 7) * a.nranks + a.rank) << 7) + (int)(mr & 127);
     if (i >= a.nall || i <= a.col0 || i < a.row0) continue;
     const int jend = min(i, a.col_end);                       // columns [col0, jend) hold pairs of row i
@@ -763,11 +810,13 @@ cand_scan_kernel(const ScanArgs a) {
       budget = tried < 256u ? 512 : (won * 8u >= tried ? 4096 : 64);
     }
     bool gave_up = false, met_dense = false;
+    int misses = 0;                                           // candidates of this row evaluated without a match
     const unsigned char* const dense_i = a.dense ? a.dense + (i >> 7) : nullptr;
     // The row's words are read 8 blocks (8 x 512 B per warp) at a time: the loads of a batch are independent,
     // and nearly every block is empty - read one by one, the dependent DRAM round trips (12 per row on C3,
     // 3552 resident warps) were most of this kernel's time.
     constexpr int kScanBatch = 8;
+    constexpr int kScanWideAfter = 8, kScanWideBits = 6;     // wide steps after 8 misses, for words with >= 6 candidates
     for (int btop = (jend - 1 - a.col0) >> 12; btop >= 0; btop -= kScanBatch) {     // block = 128 words = 4096 columns
       unsigned nonempty = 0u;
       {
@@ -816,6 +865,19 @@ cand_scan_kernel(const ScanArgs a) {
           }
           const unsigned fword = frow ? frow[widx] : 0u;
           while (word && !done) {
+            if (!a.debug_all && misses >= kScanWideAfter && __popc(word) >= kScanWideBits) {
+              // wide step: all remaining candidates of the word, one lane each
+              const int below = m - cbase;                    // bits < below are at or under the current link
+              const unsigned livebits = below <= 0 ? word : (below >= 32 ? 0u : word & (0xFFFFFFFFu << below));
+              const unsigned hits = livebits ? exact_word32(a, i, cbase, livebits, lane) : 0u;
+              if ((livebits >> lane) & 1u) ++n_eval;
+              if (hits) m = cbase + (31 - __clz(hits)) + 1;
+              if (in_dense) budget -= __popc(livebits);
+              misses += __popc(livebits);
+              if (hits || livebits != word) done = true;      // a match, or candidates under the link: the row is decided
+              word = 0u;
+              continue;
+            }
             // the four highest candidates of the word, one per 8-lane group
             int bsel = -1;
 #pragma unroll
@@ -838,6 +900,7 @@ cand_scan_kernel(const ScanArgs a) {
             hit = __reduce_max_sync(0xffffffffu, hit);
             if (hit > m) m = hit;
             if (in_dense) budget -= 4;
+            misses += 4;
             // a match ends the row (the reference keeps the largest j), and so does a pruned candidate
             if (!a.debug_all && (hit > 0 || __any_sync(0xffffffffu, pruned))) done = true;
           }
@@ -1176,6 +1239,7 @@ int launch_pair_tf32(const PairArgs& pa, const PairArgs& fb_in, const Tf32Buffer
     const int grid = nitems < nsm ? nitems : nsm;
     if (grid > grid_max) grid_max = grid;
     CREST_CUDA_TRY(cudaMemsetAsync(tb.cand_count + 6, 0, sizeof(unsigned), stream));
+    CREST_CUDA_TRY(cudaMemsetAsync(tb.cand_count + 10, 0, sizeof(unsigned), stream));   // row queue of cand_scan_kernel
     if (all_cand)
       CREST_CUDA_TRY(cudaMemsetAsync(tb.fmask, 0, sizeof(unsigned) * tf32_mask_words(row_lo, row_hi, col0, col_end, nranks), stream));
     if (launch_tf32_screen(a, slab, grid, smem, stream)) return 1;
