@@ -44,6 +44,7 @@ struct Engine {
   void* h_stage = nullptr;                   // pinned staging of the whole-CREGEN call's geometry
   size_t h_stage_bytes = 0;
   cudaStream_t copy_st[kMaxGpu] = {};        // D2H of xyz_axis into h_stage under the pair stage
+  bool hint_dense = false;                   // the previous call met candidate-dense work items (plan_blocks)
 };
 Engine g_eng;
 std::mutex g_mu;                             // the one-call entry points are serialised
@@ -66,6 +67,7 @@ void engine_destroy() {
   free_copy_slots();
   E.n = 0;
   E.inited = false;
+  E.hint_dense = false;
 }
 
 // devices: n == 1 -> the CURRENT device (a caller that has selected its GPU keeps it); n > 1 -> 0..n-1
@@ -170,7 +172,7 @@ struct Phase {   // CREST_CUDA_TIMING=1: phase wall times on stderr (developer a
 //   upload bound (rho < 1.5; many GPUs, large molecules): equal blocks of ~36 MB x (GPUs / 2), 2-8 of them;
 //     every stage costs ~0.1 ms of tails and, on 8 GPUs, 56 peer copies (profiles/r02_b_timeline_n8.txt).
 // The time estimates only shape the schedule; results do not depend on it.
-std::vector<int> plan_blocks(const crest_cuda_ctx* c, bool staged, int ngpu) {
+std::vector<int> plan_blocks(const crest_cuda_ctx* c, bool staged, int ngpu, bool hint_dense) {
   std::vector<int> b{0, c->ntile};
   const size_t bytes = (size_t)24 * c->nat * c->nall;
   if (tune().blocks > 0) {
@@ -181,6 +183,12 @@ std::vector<int> plan_blocks(const crest_cuda_ctx* c, bool staged, int ngpu) {
     return b;
   }
   if (!staged || bytes < ((size_t)24 << 20)) return b;
+  // An ensemble with candidate-dense items (collapsed ensembles, floppy macrocycles) pays for every stage: each
+  // one ends in the tail of its slowest rows and re-classifies its items - C4ext takes 23.7 ms as one block,
+  // 27.6 as two, 34.5 as three (profiles/r02_i_c4ext_blocks.txt).  Density is only known afterwards, so the
+  // engine remembers it: CREST calls CREGEN 5-20 times per search on ensembles of the same kind, and a call
+  // that met dense items makes the next one run as a single block (first call: the schedule below).
+  if (hint_dense) return b;
   // rough rates: staged upload ~40 GB/s (PCIe 5 x16 with the staging threads keeping up), screen kernel
   // ~4.2e11 pairs/s per GPU up to 88 atoms, ~300 TFLOP/s of 18 A flop per pair on the slab kernel above
   const double t_up = (double)bytes / 40e9;
@@ -256,7 +264,7 @@ int stage_a(Engine& E, int nat, int nall, const int* at, const double* xyz, cons
   const double t_reserve = hms();
   if (nall == 0) return 0;
   staged = tf32_path(c0, 0, nullptr) && nall >= 2;
-  tb = plan_blocks(c0, staged, n);
+  tb = plan_blocks(c0, staged, n, E.hint_dense);
   const int nb = (int)tb.size() - 1;
   const size_t rec = (size_t)24 * nat;                       // bytes per structure
 
@@ -378,6 +386,11 @@ int stage_a(Engine& E, int nat, int nall, const int* at, const double* xyz, cons
   }
   if (npairs) *npairs = np;
   CREST_CUDA_TRY(cudaSetDevice(c0->device));
+  if (staged) {                                              // density of this call = the next call's block schedule
+    unsigned h[16] = {};
+    CREST_CUDA_TRY(cudaMemcpy(h, c0->tf.cand_count, sizeof(h), cudaMemcpyDeviceToHost));
+    E.hint_dense = h[5] != 0u;
+  }
   ph.lap(E, "upload | pack | pairs | early D2H");
   if (tl) {
     std::fprintf(stderr, "[timeline] host: reserve done %.3f, begin+plan done %.3f, all synced at %.3f ms (%d blocks)\n",
