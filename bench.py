@@ -460,7 +460,8 @@ def run_ours(args):
             t0 = time.perf_counter()
             r = cb.rdensemble(fn, want_comments=False)
             t1 = time.perf_counter()
-            xs, es, order, nout = cb.cregen_esort(r["xyz"], r["er"])
+            xs, es = r["xyz"], r["er"]
+            order, nout = cregen.cregen_esort_inplace(xs, es)      # in place, like the reference
             t2 = time.perf_counter()
             full = cb.cregen_CRE_inplace(env, nat, nout, r["at"], xs[:nout], es[:nout])
             ts.append((t1 - t0, t2 - t1, time.perf_counter() - t2))

@@ -263,6 +263,25 @@ def cregen_esort(xyz, energies, ewin=1e9):
     return xs, er, order[:nall], nout.value
 
 
+def cregen_esort_inplace(xyz, energies, ewin=1e9):
+    """As the reference (cregen.f90:1038-1121 sorts its arrays in place): xyz (nall,nat,3) float64 C-order and
+    energies float64 are permuted in place; returns (order, nallout)."""
+    L = _lib.lib()
+    if not (isinstance(energies, np.ndarray) and energies.dtype == np.float64 and energies.flags.c_contiguous):
+        raise TypeError("cregen_esort_inplace needs a C-contiguous float64 energy array")
+    nall = len(energies)
+    nat = 1
+    if xyz is not None:
+        if not (isinstance(xyz, np.ndarray) and xyz.dtype == np.float64 and xyz.flags.c_contiguous):
+            raise TypeError("cregen_esort_inplace needs C-contiguous float64 xyz")
+        nat = xyz.shape[1]
+    order = np.zeros(max(nall, 1), np.int32)
+    nout = C.c_int(0)
+    _lib.check(L.crest_cuda_cregen_esort(nat, nall, _dp(xyz) if xyz is not None else None, _dp(energies),
+                                         float(ewin), _ip(order), C.byref(nout)))
+    return order[:nall], nout.value
+
+
 def rmsdalign(at, xyz):
     """cregen_rmsdalign (cregen.f90:2229-2283) on the GPU; returns the aligned copy of xyz."""
     L = _lib.lib()

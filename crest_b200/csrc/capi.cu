@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdlib>
+#include <functional>
 #include <cstring>
 #include <limits>
 #include <utility>
@@ -902,42 +903,80 @@ int crest_cuda_cregen_esort(int nat, int nall, double* xyz, double* energies, do
   std::vector<int> was(nall);              // after sorting: element at position p WAS at was[p]
   for (int i = 0; i < nall; ++i) was[i] = i;
   double* a = energies;
-  std::vector<std::pair<int, int>> stack;
-  if (nall > 0) stack.emplace_back(0, nall - 1);
-  while (!stack.empty()) {
-    const int first = stack.back().first, last = stack.back().second;
-    stack.pop_back();
-    // 1-based (first+last)/2 of the reference == 0-based (first+last+2)/2 - 1
-    const double x = a[(first + last + 2) / 2 - 1];
-    int i = first, j = last;
-    for (;;) {
-      while (a[i] < x) ++i;
-      while (x < a[j]) --j;
-      if (i >= j) break;
-      std::swap(a[i], a[j]);
-      std::swap(was[i], was[j]);
-      ++i; --j;
+  // The reference's quicksort (quicksort.f90:140-165) - Hoare partition, middle pivot, unstable: the order of
+  // equal energies is part of the contract.  After a partition the two sub-ranges never interact, so they can
+  // be sorted by different threads without changing a single swap: the first few levels hand their left
+  // range to a new thread (large ranges only), the rest is the serial loop on an explicit stack.
+  std::function<void(int, int, int)> sort_range = [&](int lo, int hi, int depth) {
+    std::vector<std::pair<int, int>> stack;
+    std::vector<std::thread> helpers;
+    stack.emplace_back(lo, hi);
+    while (!stack.empty()) {
+      const int first = stack.back().first, last = stack.back().second;
+      stack.pop_back();
+      // 1-based (first+last)/2 of the reference == 0-based (first+last+2)/2 - 1
+      const double x = a[(first + last + 2) / 2 - 1];
+      int i = first, j = last;
+      for (;;) {
+        while (a[i] < x) ++i;
+        while (x < a[j]) --j;
+        if (i >= j) break;
+        std::swap(a[i], a[j]);
+        std::swap(was[i], was[j]);
+        ++i; --j;
+      }
+      const bool left = first < i - 1, right = j + 1 < last;
+      if (left && right && depth < 4 && (i - 1 - first) > (1 << 15) && (last - j - 1) > (1 << 15)) {
+        const int l0 = first, l1 = i - 1;
+        helpers.emplace_back([&sort_range, l0, l1, depth] { sort_range(l0, l1, depth + 1); });
+        ++depth;                                           // this thread keeps the right range
+        stack.emplace_back(j + 1, last);
+        continue;
+      }
+      if (left) stack.emplace_back(first, i - 1);
+      if (right) stack.emplace_back(j + 1, last);
     }
-    if (first < i - 1) stack.emplace_back(first, i - 1);
-    if (j + 1 < last) stack.emplace_back(j + 1, last);
-  }
+    for (auto& h : helpers) h.join();
+  };
+  if (nall > 0) sort_range(0, nall - 1, 0);
   for (int p = 0; p < nall; ++p) order[was[p]] = p + 1;     // structure i IS NOW at order[i] (1-based)
   if (xyz && nall > 0) {
-    // the permutation of the geometries moves 24*nat*nall bytes twice (C5: 2 x 0.96 GB): a few threads,
-    // each a contiguous range of destination records
+    // the permutation of the geometries moves 24*nat*nall bytes twice (C5: 2 x 0.96 GB): up to 16 threads,
+    // each a contiguous range of destination records, non-temporal stores (hostcopy.cu fast_copy), and a
+    // scratch buffer that is NOT zero-filled first (a std::vector would add a third pass over it)
     const size_t rec = (size_t)3 * nat;
-    std::vector<double> tmp(rec * nall);
-    int T = (int)std::min<size_t>(8, std::max<size_t>(1, (rec * nall * sizeof(double)) >> 24));
+    // scratch up to 256 MB is kept between calls (CREST sorts 5-20 ensembles per search; a fresh mapping costs
+    // a page fault and a zeroed page per 4 KB - as much as the copy itself), larger ones are returned at once
+    static double* keep = nullptr;
+    static size_t keep_bytes = 0;
+    const size_t need = sizeof(double) * rec * nall;
+    double* tmp = nullptr;
+    if (need <= ((size_t)256 << 20)) {
+      if (need > keep_bytes) {
+        std::free(keep);
+        keep = static_cast<double*>(std::malloc(need));
+        keep_bytes = keep ? need : 0;
+      }
+      tmp = keep;
+    } else {
+      tmp = static_cast<double*>(std::malloc(need));
+    }
+    if (!tmp) { set_error("cregen_esort: out of host memory (%zu bytes)", need); return 1; }
+    int T = (int)std::min<size_t>(16, std::max<size_t>(1, (rec * nall * sizeof(double)) >> 23));
     const int hw = (int)std::thread::hardware_concurrency();
     if (hw > 0 && T > hw) T = hw;
     auto part = [&](int t) {
       const size_t p0 = (size_t)nall * t / T, p1 = (size_t)nall * (t + 1) / T;
       for (size_t p = p0; p < p1; ++p)
-        std::memcpy(tmp.data() + rec * p, xyz + rec * was[p], rec * sizeof(double));
+        fast_copy(tmp + rec * p, xyz + rec * was[p], rec * sizeof(double));
+      fast_copy_fence();
     };
     auto back = [&](int t) {
       const size_t p0 = (size_t)nall * t / T, p1 = (size_t)nall * (t + 1) / T;
-      std::memcpy(xyz + rec * p0, tmp.data() + rec * p0, rec * (p1 - p0) * sizeof(double));
+      const size_t step = (size_t)1 << 17;                  // doubles per copy: 1 MB
+      for (size_t o = rec * p0; o < rec * p1; o += step)
+        fast_copy(xyz + o, tmp + o, std::min(step, rec * p1 - o) * sizeof(double));
+      fast_copy_fence();
     };
     for (int phase = 0; phase < 2; ++phase) {
       std::vector<std::thread> th;
@@ -945,6 +984,7 @@ int crest_cuda_cregen_esort(int nat, int nall, double* xyz, double* energies, do
       phase ? back(0) : part(0);
       for (auto& x : th) x.join();
     }
+    if (tmp != keep) std::free(tmp);
   }
   int nout = nall;
   if (nall > 0) {

@@ -189,3 +189,25 @@ def test_host_esort_matches_oracle(cuda_lib):
         if n:
             assert np.array_equal(xs[order - 1], xyz)          # structure i now sits at order[i]
             assert np.all(np.diff(es) >= 0)
+
+
+def test_host_esort_threads_keep_the_reference_order(cuda_lib):
+    """Large ensembles: sub-ranges of the reference quicksort are sorted by several threads and the
+    geometry is permuted by threads with non-temporal copies (capi.cu) - the permutation, incl. the order of
+    equal energies, is still the serial reference's; the in-place mirror equals the copying one."""
+    import oracle_lib as O
+    from crest_b200 import cregen as cg
+    rng = np.random.default_rng(11)
+    n = 400000
+    en = rng.uniform(0, 6.0, n) / 627.50947428 - 40.0
+    en = np.round(en * 20000) / 20000                  # ~120 000 distinct values: ties everywhere
+    xyz = rng.normal(size=(n, 14, 3))                  # 134 MB: the threaded permutation with kept scratch
+    es_ref, pos_ref, nout_ref = O.esort(en, ewin=4.0)
+    for rep in range(2):                               # second call re-uses the scratch buffer
+        xs, es, order, nout = cg.cregen_esort(xyz, en, 4.0)
+        assert np.array_equal(es, es_ref) and nout == nout_ref
+        assert np.array_equal(order, np.asarray(pos_ref) + (1 - int(np.min(pos_ref))))
+        assert np.array_equal(xs[order - 1], xyz)
+    x2, e2 = xyz.copy(), en.copy()
+    o2, n2 = cg.cregen_esort_inplace(x2, e2, 4.0)
+    assert np.array_equal(x2, xs) and np.array_equal(e2, es) and np.array_equal(o2, order) and n2 == nout
