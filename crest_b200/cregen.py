@@ -349,6 +349,10 @@ class CregenContext:
         _lib.check(self._L.crest_cuda_ctx_upload(self._h, nat, nall, _ip(at), None, _dp(er),
                                                  _ip(mask), rfm))
         self.nall, self.nat = nall, nat
+        if not 1 <= world <= 64:
+            # the device xyz buffer has 64 rows of slack (crest_cuda.h): equal slices of ceil(nall/world) rows
+            # overshoot nall by < world rows
+            raise ValueError(f"upload_rows: world = {world}, the all-gather layout supports 1..64 ranks")
         chunk = (nall + world - 1) // world
         first = min(rank * chunk, nall)
         count = min(chunk, nall - first)
