@@ -306,8 +306,11 @@ int crest_cuda_tf32_items_n(int nall, const double* er, double ethr, int nranks,
 /* Developer knobs (same syntax as the CREST_CUDA_TUNE environment variable; NULL = defaults):
  * "notf32" forces the FP64 (DMMA) pair kernels, "tile" the row-tile kernel, "chunk=<n>" j-groups per
  * work item, "maskmb=<MB>" the candidate-bitmask budget, "forcedense"/"nodense"/"densebudget=<n>" the
- * dense-item policy, "blocks=<n>" equal row blocks of the upload pipeline, "evenblocks" equal blocks where
- * the default is a small first block and growing ones, "nostage" no pinned staging of the whole-CREGEN geometry.  Takes effect at the next ctx_upload. */
+ * dense-item policy, "scanocc=<2|3|4>" resident blocks of the exact scan, "packold" / "packg=-<G>" the
+ * multi-sweep pack kernel / the lanes per conformer of the one-pass one, "blocks=<n>" equal row blocks of the
+ * upload pipeline, "evenblocks", "blockf1=<%>", "blockgain=<%>" its schedule, "nostage" no pinned staging of
+ * the whole-CREGEN geometry, "copythr=<n>" staging threads, "seqgroup" / "groupcap=<n>" the K6 path.
+ * Takes effect at the next ctx_upload. */
 void crest_cuda_set_tune(const char* spec);
 
 const char* crest_cuda_last_error(void);
