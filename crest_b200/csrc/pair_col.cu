@@ -151,11 +151,16 @@ struct ColWarp {
 // Exact pass for the (rare) candidate pairs of a finished unit: second-level FP64 screen, then
 // Newton/Jacobi, float32-threshold emulation, rot gate, atomicMax — identical decisions to
 // pair_tile.cu's pass 2.  Executed by all lanes (ballots for the optional bitmask).
+// SINK is a template parameter on purpose: with the sink call compiled into the CREGEN instantiation the
+// kernel argument struct had to live in local memory (sink_pair takes it by reference, out of line) and the
+// stack frame of pair_col_kernel<8,1,1> grew from 128 to 1248 bytes, spills from 0.1 to 1.5 KB per thread -
+// 178 -> 245 ms on the C3 triangle.  The CREGEN kernels contain no trace of the sink now.
+template <bool SINK>
 __device__ __forceinline__ void unit_exact(const ColArgs& a, const ColWarp& w,
                                            const double (&acc)[2][9][2], const UnitMeta& m,
                                            unsigned cand) {
   const int i = m.i;
-  if (a.sink.mode) {
+  if constexpr (SINK) {
 #pragma unroll 1
     for (int q = 0; q < 4; ++q) {
       if (!((cand >> q) & 1u)) continue;
@@ -225,6 +230,7 @@ __device__ __forceinline__ void unit_exact(const ColArgs& a, const ColWarp& w,
 // Fill the meta of the unit that is about to be multiplied.  Nothing loaded here is consumed before
 // the next step (the xn_i load hides under the DMMA block); only items on the band edge take the
 // slow path that reads energies and gates pair by pair (reference cregen.f90:1275).
+template <bool SINK>
 __device__ __forceinline__ void unit_meta(const ColArgs& a, const ColWarp& w, int unit, int J,
                                           int item_edge, const double (&xnj_item)[2][2],
                                           UnitMeta& m) {
@@ -242,7 +248,7 @@ __device__ __forceinline__ void unit_meta(const ColArgs& a, const ColWarp& w, in
       const int j = m.j0w + nj * 8 + 2 * w.tq + p;
       m.xnj[nj][p] = xnj_item[nj][p];
       // CREGEN and intraconf: the triangle j < i; compare (sink mode 1): the whole rectangle
-      const bool jok = a.sink.mode == 1 ? j < a.sink.nj : j < i;
+      const bool jok = (SINK && a.sink.mode == 1) ? j < a.sink.nj : j < i;
       ok |= ((iok && jok) ? 1u : 0u) << (nj * 2 + p);
     }
   if (item_edge) {
@@ -261,7 +267,7 @@ __device__ __forceinline__ void unit_meta(const ColArgs& a, const ColWarp& w, in
   m.ok = ok;
 }
 
-template <int NKB, bool HALF, bool SCREEN>
+template <int NKB, bool HALF, bool SCREEN, bool SINK>
 __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* smem_raw,
                                               uint64_t* full_bar, uint64_t* empty_bar,
                                               uint64_t& jfull_bar, uint64_t& jempty_bar,
@@ -327,12 +333,12 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
 #pragma unroll
       for (int p = 0; p < 2; ++p) {
         const int j = J * kColJ + w.wj * 16 + nj * 8 + 2 * w.tq + p;
-        xnj_item[nj][p] = a.sink.mode == 1 ? a.sink.xnj[min(j, a.sink.nj - 1)] : a.xn[min(j, a.nall - 1)];
+        xnj_item[nj][p] = (SINK && a.sink.mode == 1) ? a.sink.xnj[min(j, a.sink.nj - 1)] : a.xn[min(j, a.nall - 1)];
       }
     if (is_producer) {
       mbar_wait(&jempty_bar, (jn & 1) ^ 1);      // previous j-tile released by all 8 warps
       mbar_expect_tx(&jfull_bar, 4 * unit_bytes);
-      bulk_g2s(sJ, (a.sink.mode == 1 ? a.sink.Xj : a.X) + (size_t)(4 * J) * unit_doubles, 4 * unit_bytes, &jfull_bar);
+      bulk_g2s(sJ, ((SINK && a.sink.mode == 1) ? a.sink.Xj : a.X) + (size_t)(4 * J) * unit_doubles, 4 * unit_bytes, &jfull_bar);
     }
     __syncwarp();
     mbar_wait(&jfull_bar, jn & 1);
@@ -353,7 +359,7 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
   for (int y = 0; y < 2; ++y)
 #pragma unroll
     for (int p = 0; p < 2; ++p) { mA.xnj[y][p] = 0.0; mB.xnj[y][p] = 0.0; }
-  const bool all_cand = a.rmat != nullptr || a.sink.mode != 0;
+  const bool all_cand = a.rmat != nullptr || SINK;
   const float e2_up = a.g.E2_up;
 
   // one pipeline step: multiply unit (cur) while screening the previous one (prev), then finish prev
@@ -368,7 +374,7 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
     const uint32_t ph = (it / nstage) & 1;
     if (prof) tc = clock64();
     if (is_producer) produce_one();
-    unit_meta(a, w, u, J, item_edge, xnj_item, mc);
+    unit_meta<SINK>(a, w, u, J, item_edge, xnj_item, mc);
     __syncwarp();
     if (prof) { const long long t1 = clock64(); tp += t1 - tc; tc = t1; }
     mbar_wait(&full_bar[st], ph);
@@ -381,7 +387,7 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
     ++it;
     if (prof) { const long long t1 = clock64(); tm += t1 - tc; tc = t1; }
     w.my_pairs += __popc(mp.ok);
-    if (__any_sync(0xffffffffu, cand != 0)) unit_exact(a, w, prev, mp, cand);
+    if (__any_sync(0xffffffffu, cand != 0)) unit_exact<SINK>(a, w, prev, mp, cand);
     if (prof) { const long long t1 = clock64(); te += t1 - tc; tc = t1; }
   };
 
@@ -394,7 +400,7 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
       const unsigned cand = unit_block<NKB, HALF, SCREEN>(accB, accA, sU + w.a_off, sJ + w.b_off0, sJ + w.b_off1,
                                             w.comp, w.comp, mA, e2_up, a.g.enantio, all_cand);
       w.my_pairs += __popc(mA.ok);
-      if (__any_sync(0xffffffffu, cand != 0)) unit_exact(a, w, accA, mA, cand);
+      if (__any_sync(0xffffffffu, cand != 0)) unit_exact<SINK>(a, w, accA, mA, cand);
       mA.ok = 0;
       break;
     }
@@ -405,7 +411,7 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
     const unsigned cand = unit_block<NKB, HALF, SCREEN>(accA, accB, sU + w.a_off, sJ + w.b_off0, sJ + w.b_off1,
                                           w.comp, w.comp, mB, e2_up, a.g.enantio, all_cand);
     w.my_pairs += __popc(mB.ok);
-    if (__any_sync(0xffffffffu, cand != 0)) unit_exact(a, w, accB, mB, cand);
+    if (__any_sync(0xffffffffu, cand != 0)) unit_exact<SINK>(a, w, accB, mB, cand);
   }
   if (prof && w.lane == 0) {
     atomicAdd((unsigned long long*)a.dbg + warp * 4 + 0, (unsigned long long)tp);
@@ -419,7 +425,7 @@ __device__ __forceinline__ void pair_col_body(const ColArgs& a, unsigned char* s
   if (w.lane == 0 && my_pairs) atomicAdd(a.npairs, my_pairs);
 }
 
-template <int NKB, bool HALF, bool SCREEN>
+template <int NKB, bool HALF, bool SCREEN, bool SINK>
 __global__ void __launch_bounds__(kPairThreads, 1)
 pair_col_kernel(const ColArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -438,7 +444,7 @@ pair_col_kernel(const ColArgs a) {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  pair_col_body<NKB, HALF, SCREEN>(a, smem_raw, full_bar, empty_bar, jfull_bar, jempty_bar, item_end);
+  pair_col_body<NKB, HALF, SCREEN, SINK>(a, smem_raw, full_bar, empty_bar, jfull_bar, jempty_bar, item_end);
 }
 
 int col_smem_bytes(int KS, int* nstage_out) {
@@ -451,22 +457,25 @@ int col_smem_bytes(int KS, int* nstage_out) {
   return (int)(unit * (4 + ns));
 }
 
-template <int NKB, bool HALF, bool SCREEN>
+template <int NKB, bool HALF, bool SCREEN, bool SINK>
 static int launch_col_inst(const ColArgs& a, int grid, int smem, cudaStream_t stream) {
-  CREST_CUDA_TRY(cudaFuncSetAttribute(pair_col_kernel<NKB, HALF, SCREEN>,
+  CREST_CUDA_TRY(cudaFuncSetAttribute(pair_col_kernel<NKB, HALF, SCREEN, SINK>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  pair_col_kernel<NKB, HALF, SCREEN><<<grid, kPairThreads, smem, stream>>>(a);
+  pair_col_kernel<NKB, HALF, SCREEN, SINK><<<grid, kPairThreads, smem, stream>>>(a);
   CREST_CUDA_TRY(cudaGetLastError());
   return 0;
 }
 
 template <int NKB>
 static int launch_col_nkb(const ColArgs& a, int half, int grid, int smem, cudaStream_t stream) {
+  if (a.sink.mode != 0)    // compare_blocks / intraconf (blockpair.cu): every valid pair to the sink
+    return half ? launch_col_inst<NKB, true, true, true>(a, grid, smem, stream)
+                : launch_col_inst<NKB, false, true, true>(a, grid, smem, stream);
   if (a.g.debug == 1)      // timing-only variant without the screen (CREST_CUDA_DEBUG=1)
-    return half ? launch_col_inst<NKB, true, false>(a, grid, smem, stream)
-                : launch_col_inst<NKB, false, false>(a, grid, smem, stream);
-  return half ? launch_col_inst<NKB, true, true>(a, grid, smem, stream)
-              : launch_col_inst<NKB, false, true>(a, grid, smem, stream);
+    return half ? launch_col_inst<NKB, true, false, false>(a, grid, smem, stream)
+                : launch_col_inst<NKB, false, false, false>(a, grid, smem, stream);
+  return half ? launch_col_inst<NKB, true, true, false>(a, grid, smem, stream)
+              : launch_col_inst<NKB, false, true, false>(a, grid, smem, stream);
 }
 
 int launch_pair_cols(const PairArgs& pa, const void* d_items, int item_begin, int item_end,
