@@ -31,8 +31,8 @@ def cuda_lib():
     from crest_b200 import _lib
     if not os.path.exists(_lib.LIB_PATH):
         import subprocess
-        subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "crest_b200", "csrc")], check=True,
-                       stdout=subprocess.DEVNULL)
+        subprocess.run(["make", "-s", "-j", str(max(1, os.cpu_count() or 1)), "-C",
+                        os.path.join(ROOT, "crest_b200", "csrc")], check=True, stdout=subprocess.DEVNULL)
     return _lib.lib()
 
 
