@@ -58,6 +58,10 @@ struct TileCursor {
   }
 };
 
+// SINK (compare_blocks / intraconf, blockpair.cu) is a template parameter for the reason given in pair_col.cu:
+// compiled into the CREGEN instantiation, the out-of-line sink call put the argument struct into local memory
+// (stack frame 72 -> 1040 bytes).
+template <bool SINK>
 __global__ void __launch_bounds__(kPairThreads, 1)
 pair_tile_kernel(const PairArgs a, const int nstage) {
   const long long tile_end = a.work_count ? a.tile_begin + (long long)*a.work_count : a.tile_end;
@@ -117,7 +121,7 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
 #pragma unroll
     for (int p = 0; p < kJPanels; ++p)
       bulk_g2s(dst + chunk * (1 + p),
-               (a.sink.mode == 1 ? a.sink.Xj : a.X) + ((size_t)(p_J * kJPanels + p) * L.nslab + p_slab) * chunk,
+               ((SINK && a.sink.mode == 1) ? a.sink.Xj : a.X) + ((size_t)(p_J * kJPanels + p) * L.nslab + p_slab) * chunk,
                chunk_bytes, &full_bar[st]);
     ++p_it;
     if (++p_slab == L.nslab) { p_slab = 0; p_tile += gridDim.x; }
@@ -150,7 +154,7 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
     const int i0 = I * kTileI + wi * 16;       // first i of this warp
     const int j0 = J * kTileJ + wj * 16;       // first j of this warp
     // warp-level activity: any pair with j < i, i < nall
-    const bool active = a.sink.mode == 1 ? (i0 < a.nall) && (j0 < a.sink.nj)
+    const bool active = (SINK && a.sink.mode == 1) ? (i0 < a.nall) && (j0 < a.sink.nj)
                                          : (j0 < i0 + 16) && (i0 < a.nall) && (j0 < a.nall);
 
     double acc[2][2][9][2];
@@ -206,7 +210,7 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
     }
     if (!active || a.g.debug == 1) continue;
     if (prof) tc = clock64();
-    if (a.sink.mode) {
+    if constexpr (SINK) {
       // rmsd() callers beside cregen_CRE (blockpair.cu): every valid pair to the sink
 #pragma unroll 1
       for (int q = 0; q < 8; ++q) {
@@ -239,7 +243,7 @@ pair_tile_kernel(const PairArgs a, const int nstage) {
 #pragma unroll
       for (int p = 0; p < 2; ++p) {
         const int j = j0 + nj * 8 + 2 * tq + p;
-        xnj[nj][p] = a.sink.mode == 1 ? ((j < a.sink.nj) ? a.sink.xnj[j] : 0.0) : ((j < a.nall) ? a.xn[j] : 0.0);
+        xnj[nj][p] = (SINK && a.sink.mode == 1) ? ((j < a.sink.nj) ? a.sink.xnj[j] : 0.0) : ((j < a.nall) ? a.xn[j] : 0.0);
         lam_j[nj][p] = 0.5f * __fsub_rd(f64_to_f32_trunc(xnj[nj][p]) * 0.999998f, e2_up);
       }
     unsigned cand = 0;
@@ -377,10 +381,14 @@ int launch_pair_tiles(const PairArgs& a_in, int nstage, cudaStream_t stream, int
   if (a.dist < 0) a.dist = 0;
   a.skew_clk = 0;          // measured: no gain while all 8 warps share one ring
   if (tune().skew >= 0) a.skew_clk = tune().skew;
-  CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tile_kernel,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, smem_used));
   const int grid = (int)(ntiles < nsm ? ntiles : nsm);   // persistent: one CTA per SM
-  pair_tile_kernel<<<grid, kPairThreads, smem_used, stream>>>(a, ns);
+  if (a.sink.mode != 0) {
+    CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_used));
+    pair_tile_kernel<true><<<grid, kPairThreads, smem_used, stream>>>(a, ns);
+  } else {
+    CREST_CUDA_TRY(cudaFuncSetAttribute(pair_tile_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_used));
+    pair_tile_kernel<false><<<grid, kPairThreads, smem_used, stream>>>(a, ns);
+  }
   CREST_CUDA_TRY(cudaGetLastError());
   if (grid_out) *grid_out = grid;
   if (smem_out) *smem_out = smem_used;
